@@ -1,0 +1,299 @@
+// Memory-bound helpers: optimizer steps, standalone activation kernels (the unfused forms of what the GEMM
+// epilogues do), Philox data generation, casts, a deterministic metric reduction.  All are grid-stride,
+// 16-byte vectorised, sized to a multiple of the SM count.
+#include "common.cuh"
+#include "../include/b200ffn.h"
+#include <curand_kernel.h>
+
+namespace b200 {
+
+constexpr int EW_THREADS = 256;
+
+static inline int ew_grid(long long nvec) {
+    long long blocks = (nvec + EW_THREADS - 1) / EW_THREADS;
+    long long cap = (long long)num_sms() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+    f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+    f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+    uint4 o;
+    o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+    o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+    return o;
+}
+__device__ __forceinline__ void load_grad8(const void* g, long long i8, bool f32, float (&f)[8]) {
+    if (f32) {
+        const float4* p = reinterpret_cast<const float4*>(g) + 2 * i8;
+        float4 a = p[0], b = p[1];
+        f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+    } else {
+        unpack8(reinterpret_cast<const uint4*>(g)[i8], f);
+    }
+}
+
+// ------------------------------------------------------------------ SGD
+__global__ void __launch_bounds__(EW_THREADS) sgd_kernel(__nv_bfloat16* p, const void* g, long long n, float lr, int grad_f32) {
+    const long long n8 = n / 8;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    uint4* pv = reinterpret_cast<uint4*>(p);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+        float w[8], gr[8];
+        unpack8(pv[i], w);
+        load_grad8(g, i, grad_f32 != 0, gr);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) w[j] -= lr * gr[j];
+        pv[i] = pack8(w);
+    }
+    // scalar tail
+    for (long long i = n8 * 8 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float gr = grad_f32 ? reinterpret_cast<const float*>(g)[i] : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(g)[i]);
+        p[i] = __float2bfloat16_rn(__bfloat162float(p[i]) - lr * gr);
+    }
+}
+
+// ------------------------------------------------------------------ Adam
+__global__ void __launch_bounds__(EW_THREADS) adam_kernel(__nv_bfloat16* p, const void* g, float* m, float* v, long long n, float lr,
+                                                          float b1, float b2, float eps, float bc1, float bc2, int grad_f32) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float gr = grad_f32 ? reinterpret_cast<const float*>(g)[i] : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(g)[i]);
+        const float mi = b1 * m[i] + (1.0f - b1) * gr;
+        const float vi = b2 * v[i] + (1.0f - b2) * gr * gr;
+        m[i] = mi;
+        v[i] = vi;
+        const float upd = (mi / bc1) / (sqrtf(vi / bc2) + eps);
+        p[i] = __float2bfloat16_rn(__bfloat162float(p[i]) - lr * upd);
+    }
+}
+
+// ------------------------------------------------------------------ activations / add
+template <int OP>   // 0 relu fwd (out=relu(x)), 1 relu bwd (out=out*(x>0)), 2 add (out=a+b)
+__global__ void __launch_bounds__(EW_THREADS) ew_kernel(__nv_bfloat16* out, const __nv_bfloat16* a, const __nv_bfloat16* b, long long n) {
+    const long long n8 = n / 8;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+        float x[8], y[8];
+        unpack8(reinterpret_cast<const uint4*>(a)[i], x);
+        if (OP == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) y[j] = x[j] > 0.f ? x[j] : 0.f;
+        } else if (OP == 1) {
+            unpack8(reinterpret_cast<const uint4*>(out)[i], y);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) y[j] = x[j] > 0.f ? y[j] : 0.f;
+        } else {
+            unpack8(reinterpret_cast<const uint4*>(b)[i], y);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) y[j] += x[j];
+        }
+        reinterpret_cast<uint4*>(out)[i] = pack8(y);
+    }
+    for (long long i = n8 * 8 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float x = __bfloat162float(a[i]);
+        float y;
+        if (OP == 0) y = x > 0.f ? x : 0.f;
+        else if (OP == 1) y = x > 0.f ? __bfloat162float(out[i]) : 0.f;
+        else y = x + __bfloat162float(b[i]);
+        out[i] = __float2bfloat16_rn(y);
+    }
+}
+
+// ------------------------------------------------------------------ Philox normal generator
+__global__ void __launch_bounds__(EW_THREADS) randn_kernel(__nv_bfloat16* out, long long n, unsigned long long seed, float scale) {
+    const long long n8 = (n + 7) / 8;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+        curandStatePhilox4_32_10_t st;
+        curand_init(seed, /*subsequence=*/(unsigned long long)i, /*offset=*/0, &st);
+        const float4 a = curand_normal4(&st);
+        const float4 b = curand_normal4(&st);
+        const float f[8] = {a.x * scale, a.y * scale, a.z * scale, a.w * scale, b.x * scale, b.y * scale, b.z * scale, b.w * scale};
+        if (i * 8 + 8 <= n) {
+            reinterpret_cast<uint4*>(out)[i] = pack8(f);
+        } else {
+            for (int j = 0; i * 8 + j < n; ++j) out[i * 8 + j] = __float2bfloat16_rn(f[j]);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ casts
+__global__ void __launch_bounds__(EW_THREADS) cast_f32_bf16_kernel(__nv_bfloat16* out, const float* in, long long n) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = __float2bfloat16_rn(in[i]);
+}
+__global__ void __launch_bounds__(EW_THREADS) cast_bf16_f32_kernel(float* out, const __nv_bfloat16* in, long long n) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = __bfloat162float(in[i]);
+}
+
+// ------------------------------------------------------------------ deterministic sum of squares
+constexpr int SUMSQ_MAX_BLOCKS = 1184;   // 148 SMs x 8
+struct SumsqScratch {
+    unsigned int arrived;                // must be 0 on entry; reset to 0 by the finishing CTA
+    unsigned int pad[3];
+    float partial[SUMSQ_MAX_BLOCKS];
+};
+
+__device__ __forceinline__ float block_sum(float v, float* sh) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float r = 0.f;
+    if (threadIdx.x < 32) {
+        r = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+    }
+    __syncthreads();
+    return r;   // valid in thread 0
+}
+
+__device__ __forceinline__ void sumsq_body(float* out, const __nv_bfloat16* x, long long n, SumsqScratch* sc) {
+    __shared__ float sh[EW_THREADS / 32];
+    __shared__ bool is_last;
+    const long long n8 = n / 8;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    float acc = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+        float f[8];
+        unpack8(ld_nc_u4(reinterpret_cast<const uint4*>(x) + i), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc += f[j] * f[j];
+    }
+    for (long long i = n8 * 8 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float f = __bfloat162float(x[i]);
+        acc += f * f;
+    }
+    const float bsum = block_sum(acc, sh);
+    if (threadIdx.x == 0) {
+        sc->partial[blockIdx.x] = bsum;
+        __threadfence();
+        const unsigned int prev = atomicAdd(&sc->arrived, 1u);
+        is_last = (prev == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        float t = 0.f;
+        for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) t += __ldcg(&sc->partial[i]);   // fixed order per thread
+        const float total = block_sum(t, sh);
+        if (threadIdx.x == 0) {
+            out[0] = total;
+            sc->arrived = 0;   // ready for the next call on this scratch
+        }
+    }
+}
+
+__global__ void __launch_bounds__(EW_THREADS) sumsq_kernel(float* out, const __nv_bfloat16* x, long long n, SumsqScratch* sc) {
+    sumsq_body(out, x, n, sc);
+}
+
+__global__ void __launch_bounds__(EW_THREADS) fill_zero_kernel(uint4* buf, long long n16) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) buf[i] = z;
+}
+
+static int check_ptr16(const void* p, const char* name) {
+    if (p == nullptr) { set_last_error("%s: null pointer", name); return B200_ERR_ARG; }
+    if (reinterpret_cast<uintptr_t>(p) & 15) { set_last_error("%s: pointer must be 16-byte aligned", name); return B200_ERR_ARG; }
+    return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+#define ST(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" int b200_sgd_bf16(void* param, const void* grad, long long n, float lr, int grad_f32, void* stream) {
+    if (n <= 0) return 0;
+    if (int rc = check_ptr16(param, "sgd param")) return rc;
+    if (int rc = check_ptr16(grad, "sgd grad")) return rc;
+    sgd_kernel<<<ew_grid(n / 8 + 1), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(param), grad, n, lr, grad_f32);
+    return check_cuda(cudaGetLastError(), "sgd launch");
+}
+
+extern "C" int b200_adam_bf16(void* param, const void* grad, float* m, float* v, long long n, float lr, float beta1, float beta2,
+                              float eps, int step, int grad_f32, void* stream) {
+    if (n <= 0) return 0;
+    if (param == nullptr || grad == nullptr || m == nullptr || v == nullptr || step < 1) { set_last_error("adam: bad arguments"); return B200_ERR_ARG; }
+    const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
+    adam_kernel<<<ew_grid(n), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(param), grad, m, v, n, lr, beta1, beta2, eps, bc1, bc2, grad_f32);
+    return check_cuda(cudaGetLastError(), "adam launch");
+}
+
+extern "C" int b200_relu_bf16(void* out, const void* x, long long n, void* stream) {
+    if (n <= 0) return 0;
+    if (int rc = check_ptr16(out, "relu out")) return rc;
+    if (int rc = check_ptr16(x, "relu x")) return rc;
+    ew_kernel<0><<<ew_grid(n / 8 + 1), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(x), nullptr, n);
+    return check_cuda(cudaGetLastError(), "relu launch");
+}
+
+extern "C" int b200_relu_bwd_bf16(void* dy, const void* x, long long n, void* stream) {
+    if (n <= 0) return 0;
+    if (int rc = check_ptr16(dy, "relu_bwd dy")) return rc;
+    if (int rc = check_ptr16(x, "relu_bwd x")) return rc;
+    ew_kernel<1><<<ew_grid(n / 8 + 1), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(x), nullptr, n);
+    return check_cuda(cudaGetLastError(), "relu_bwd launch");
+}
+
+extern "C" int b200_add_bf16(void* out, const void* a, const void* b, long long n, void* stream) {
+    if (n <= 0) return 0;
+    if (int rc = check_ptr16(out, "add out")) return rc;
+    if (int rc = check_ptr16(a, "add a")) return rc;
+    if (int rc = check_ptr16(b, "add b")) return rc;
+    ew_kernel<2><<<ew_grid(n / 8 + 1), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(a), reinterpret_cast<const __nv_bfloat16*>(b), n);
+    return check_cuda(cudaGetLastError(), "add launch");
+}
+
+extern "C" int b200_randn_bf16(void* out, long long n, unsigned long long seed, float scale, void* stream) {
+    if (n <= 0) return 0;
+    if (int rc = check_ptr16(out, "randn out")) return rc;
+    randn_kernel<<<ew_grid((n + 7) / 8), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(out), n, seed, scale);
+    return check_cuda(cudaGetLastError(), "randn launch");
+}
+
+extern "C" int b200_cast_f32_to_bf16(void* out, const float* in, long long n, void* stream) {
+    if (n <= 0) return 0;
+    if (out == nullptr || in == nullptr) { set_last_error("cast: null pointer"); return B200_ERR_ARG; }
+    cast_f32_bf16_kernel<<<ew_grid(n), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(out), in, n);
+    return check_cuda(cudaGetLastError(), "cast launch");
+}
+
+extern "C" int b200_cast_bf16_to_f32(float* out, const void* in, long long n, void* stream) {
+    if (n <= 0) return 0;
+    if (out == nullptr || in == nullptr) { set_last_error("cast: null pointer"); return B200_ERR_ARG; }
+    cast_bf16_f32_kernel<<<ew_grid(n), EW_THREADS, 0, ST(stream)>>>(out, reinterpret_cast<const __nv_bfloat16*>(in), n);
+    return check_cuda(cudaGetLastError(), "cast launch");
+}
+
+extern "C" long long b200_sumsq_scratch_bytes(void) { return (long long)sizeof(SumsqScratch); }
+
+extern "C" int b200_sumsq_bf16(float* out, const void* x, long long n, void* scratch, long long scratch_bytes, void* stream) {
+    if (out == nullptr || scratch == nullptr) { set_last_error("sumsq: null out/scratch"); return B200_ERR_ARG; }
+    if (n < 0 || (n > 0 && x == nullptr)) { set_last_error("sumsq: bad input"); return B200_ERR_ARG; }
+    if (n > 0) { if (int rc = check_ptr16(x, "sumsq x")) return rc; }
+    if (scratch_bytes < (long long)sizeof(SumsqScratch) || (reinterpret_cast<uintptr_t>(scratch) & 15)) {
+        set_last_error("sumsq: scratch must be 16-byte aligned and hold %lld bytes", (long long)sizeof(SumsqScratch)); return B200_ERR_ARG;
+    }
+    int grid = ew_grid(n / 8 + 1);
+    if (grid > SUMSQ_MAX_BLOCKS) grid = SUMSQ_MAX_BLOCKS;
+    sumsq_kernel<<<grid, EW_THREADS, 0, ST(stream)>>>(out, reinterpret_cast<const __nv_bfloat16*>(x), n, reinterpret_cast<SumsqScratch*>(scratch));
+    return check_cuda(cudaGetLastError(), "sumsq launch");
+}
+
+extern "C" int b200_fill_zero(void* buf, long long bytes, void* stream) {
+    if (bytes <= 0) return 0;
+    if (int rc = check_ptr16(buf, "fill_zero buf")) return rc;
+    if (bytes % 16) { set_last_error("fill_zero: bytes must be a multiple of 16"); return B200_ERR_ARG; }
+    fill_zero_kernel<<<ew_grid(bytes / 16), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<uint4*>(buf), bytes / 16);
+    return check_cuda(cudaGetLastError(), "fill_zero launch");
+}

@@ -1,0 +1,98 @@
+"""Build the in-tree native library ``csrc/*.cu -> distributed_llm_code_samples_b200/_native/libb200ffn.so``.
+
+nvcc cross-compiles sm_100a without a GPU, so this runs on the CPU dev box; the resulting ``.so`` is
+git-ignored but travels with ``gpurun`` snapshots.  Objects are rebuilt only when a source or header is newer.
+
+    python -m distributed_llm_code_samples_b200.build_native [--force] [--verbose]
+"""
+from __future__ import annotations
+
+import argparse
+import concurrent.futures as cf
+import os
+import shutil
+import subprocess
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+CSRC = ROOT / "csrc"
+INCLUDE = ROOT / "include"
+OUT_DIR = Path(__file__).resolve().parent / "_native"
+LIB_PATH = OUT_DIR / "libb200ffn.so"
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-O3", "-std=c++17", "-lineinfo",
+    "-Xcompiler", "-fPIC",
+    "--expt-relaxed-constexpr",
+    "-Xptxas", "-v",
+    "-I", str(INCLUDE), "-I", str(CSRC),
+]
+
+
+def find_nvcc() -> str:
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        raise RuntimeError("nvcc not found (needed to build libb200ffn.so)")
+    return nvcc
+
+
+def _newest_header_mtime() -> float:
+    hs = list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h")) + list(INCLUDE.glob("*.h"))
+    return max((h.stat().st_mtime for h in hs), default=0.0)
+
+
+def _compile_one(nvcc: str, src: Path, obj: Path, verbose: bool) -> str:
+    cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+    p = subprocess.run(cmd, capture_output=True, text=True)
+    log = p.stdout + p.stderr
+    (obj.with_suffix(".ptxas.log")).write_text(log)
+    if p.returncode != 0:
+        raise RuntimeError(f"nvcc failed for {src.name}:\n{log}")
+    if verbose:
+        print(log)
+    return log
+
+
+def build(force: bool = False, verbose: bool = False) -> Path:
+    """Compile every ``csrc/*.cu`` for sm_100a and link ``libb200ffn.so``. Returns the library path."""
+    nvcc = find_nvcc()
+    OUT_DIR.mkdir(parents=True, exist_ok=True)
+    srcs = sorted(CSRC.glob("*.cu"))
+    if not srcs:
+        raise RuntimeError(f"no CUDA sources under {CSRC}")
+    hdr_m = _newest_header_mtime()
+    jobs = []
+    objs = []
+    for src in srcs:
+        obj = OUT_DIR / (src.stem + ".o")
+        objs.append(obj)
+        stale = force or not obj.exists() or obj.stat().st_mtime < max(src.stat().st_mtime, hdr_m)
+        if stale:
+            jobs.append((src, obj))
+    if jobs:
+        with cf.ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
+            futs = [ex.submit(_compile_one, nvcc, s, o, verbose) for s, o in jobs]
+            for f in futs:
+                f.result()
+    if jobs or not LIB_PATH.exists():
+        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(LIB_PATH), *map(str, objs)]
+        p = subprocess.run(cmd, capture_output=True, text=True)
+        if p.returncode != 0:
+            raise RuntimeError(f"link failed:\n{p.stdout}{p.stderr}")
+    return LIB_PATH
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--force", action="store_true")
+    ap.add_argument("--verbose", action="store_true")
+    a = ap.parse_args()
+    path = build(force=a.force, verbose=a.verbose)
+    print(path)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,238 @@
+"""ctypes binding of the in-tree native library (``_native/libb200ffn.so``, C ABI in ``include/b200ffn.h``).
+
+The wrappers take torch CUDA tensors, pass raw device pointers plus the *current* torch stream, and raise
+``NativeError`` with the library's message on failure - there is no silent fallback: on a GPU box a missing
+or broken library is an error, not a reason to run eager PyTorch.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+from pathlib import Path
+from typing import Optional
+
+import torch
+
+_LIB_PATH = Path(__file__).resolve().parent.parent / "_native" / "libb200ffn.so"
+_lib = None
+_lock = threading.Lock()
+
+MAJOR_K = 0
+MAJOR_MN = 1
+
+EPI_STORE, EPI_RELU, EPI_GELU, EPI_RELU_BWD, EPI_GELU_BWD, EPI_ADD, EPI_SGD, EPI_STORE_F32 = range(8)
+
+#: number of kernels this process launched through the native library (bench.py reports it)
+launch_count = 0
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def lib_path() -> Path:
+    return _LIB_PATH
+
+
+def available() -> bool:
+    """True when the shared object exists (it may still fail to run without a B200)."""
+    return _LIB_PATH.exists()
+
+
+def _declare(lib) -> None:
+    vp, ll, i, f = C.c_void_p, C.c_longlong, C.c_int, C.c_float
+    lib.b200_last_error.restype = C.c_char_p
+    lib.b200_version.restype = i
+    lib.b200_num_sms.restype = i
+    lib.b200_device_error.argtypes = [C.POINTER(C.c_uint)]
+    lib.b200_gemm_bf16.argtypes = [vp, ll, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, i, vp]
+    lib.b200_sgd_bf16.argtypes = [vp, vp, ll, f, i, vp]
+    lib.b200_adam_bf16.argtypes = [vp, vp, vp, vp, ll, f, f, f, f, i, i, vp]
+    lib.b200_relu_bf16.argtypes = [vp, vp, ll, vp]
+    lib.b200_relu_bwd_bf16.argtypes = [vp, vp, ll, vp]
+    lib.b200_add_bf16.argtypes = [vp, vp, vp, ll, vp]
+    lib.b200_randn_bf16.argtypes = [vp, ll, C.c_ulonglong, f, vp]
+    lib.b200_cast_f32_to_bf16.argtypes = [vp, vp, ll, vp]
+    lib.b200_cast_bf16_to_f32.argtypes = [vp, vp, ll, vp]
+    lib.b200_sumsq_scratch_bytes.restype = ll
+    lib.b200_sumsq_bf16.argtypes = [vp, vp, ll, vp, ll, vp]
+    lib.b200_fill_zero.argtypes = [vp, ll, vp]
+
+
+def load():
+    """Load (building first if the .so is missing and nvcc is present) and return the ctypes handle."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is None:
+            if not _LIB_PATH.exists():
+                from ..build_native import build
+                build()
+            lib = C.CDLL(str(_LIB_PATH), mode=C.RTLD_GLOBAL)
+            _declare(lib)
+            _optional_declare(lib)
+            _lib = lib
+    return _lib
+
+
+def _optional_declare(lib) -> None:
+    """Symbols added by later translation units (collectives, fused kernels); declared when present."""
+    vp, ll, i, f = C.c_void_p, C.c_longlong, C.c_int, C.c_float
+    table = {
+        "b200_ipc_handle_bytes": ([], i),
+        "b200_symm_alloc": ([C.POINTER(vp), ll], i),
+        "b200_symm_free": ([vp], i),
+        "b200_ipc_get_handle": ([vp, vp], i),
+        "b200_ipc_open_handle": ([C.POINTER(vp), vp], i),
+        "b200_ipc_close_handle": ([vp], i),
+        "b200_enable_peer_access": ([i], i),
+        "b200_barrier": ([vp, i, i, C.c_uint, vp], i),
+        "b200_all_reduce_bf16": ([vp, vp, vp, ll, i, i, C.c_uint, i, vp], i),
+        "b200_all_gather": ([vp, vp, vp, ll, i, i, C.c_uint, i, vp], i),
+        "b200_reduce_scatter_bf16": ([vp, vp, vp, ll, i, i, C.c_uint, i, vp], i),
+        "b200_gemm_allreduce_bf16": None,
+    }
+    for name, sig in table.items():
+        if sig is None or not hasattr(lib, name):
+            continue
+        fn = getattr(lib, name)
+        fn.argtypes, fn.restype = sig
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().b200_last_error().decode(errors="replace")
+        raise NativeError(f"{what} failed (rc={rc}): {msg}")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def device_error() -> tuple[int, int, int, int]:
+    buf = (C.c_uint * 4)()
+    load().b200_device_error(buf)
+    return tuple(int(x) for x in buf)  # type: ignore[return-value]
+
+
+def num_sms() -> int:
+    return int(load().b200_num_sms())
+
+
+# --------------------------------------------------------------------------------------------- GEMM
+def gemm_supported(M: int, N: int, K: int, *lds: int) -> bool:
+    """Shapes the tcgen05 kernel accepts (TMA pitch and the 16-byte epilogue vectors need multiples of 8)."""
+    return M > 0 and N > 0 and K > 0 and N % 8 == 0 and all(ld % 8 == 0 for ld in lds)
+
+
+def gemm(A: torch.Tensor, a_major: int, B: torch.Tensor, b_major: int, out: torch.Tensor, M: int, N: int, K: int,
+         epilogue: int = EPI_STORE, aux: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None,
+         bias: Optional[torch.Tensor] = None, alpha: float = 1.0, max_ctas: int = 0) -> torch.Tensor:
+    """``out[M,N] = epilogue(sum_k A(m,k) B(n,k))``; see include/b200ffn.h for majors and epilogues."""
+    global launch_count
+    assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
+    assert A.stride(-1) == 1 and B.stride(-1) == 1 and out.stride(-1) == 1
+    rc = load().b200_gemm_bf16(
+        A.data_ptr(), A.stride(0), a_major, B.data_ptr(), B.stride(0), b_major, out.data_ptr(), out.stride(0),
+        M, N, K, epilogue, _ptr(aux), aux.stride(0) if aux is not None else 0, _ptr(out2),
+        out2.stride(0) if out2 is not None else 0, _ptr(bias), float(alpha), int(max_ctas), _stream())
+    _check(rc, "b200_gemm_bf16")
+    launch_count += 1
+    return out
+
+
+# --------------------------------------------------------------------------------------------- elementwise
+def sgd_(param: torch.Tensor, grad: torch.Tensor, lr: float) -> None:
+    global launch_count
+    assert param.dtype == torch.bfloat16 and param.is_contiguous() and grad.is_contiguous()
+    _check(load().b200_sgd_bf16(param.data_ptr(), grad.data_ptr(), param.numel(), float(lr),
+                                int(grad.dtype == torch.float32), _stream()), "b200_sgd_bf16")
+    launch_count += 1
+
+
+def adam_(param: torch.Tensor, grad: torch.Tensor, m: torch.Tensor, v: torch.Tensor, lr: float, beta1: float,
+          beta2: float, eps: float, step: int) -> None:
+    global launch_count
+    assert param.dtype == torch.bfloat16 and m.dtype == torch.float32 and v.dtype == torch.float32
+    _check(load().b200_adam_bf16(param.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), param.numel(),
+                                 float(lr), float(beta1), float(beta2), float(eps), int(step),
+                                 int(grad.dtype == torch.float32), _stream()), "b200_adam_bf16")
+    launch_count += 1
+
+
+def relu(x: torch.Tensor) -> torch.Tensor:
+    global launch_count
+    out = torch.empty_like(x)
+    _check(load().b200_relu_bf16(out.data_ptr(), x.data_ptr(), x.numel(), _stream()), "b200_relu_bf16")
+    launch_count += 1
+    return out
+
+
+def relu_bwd_(dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    global launch_count
+    _check(load().b200_relu_bwd_bf16(dy.data_ptr(), x.data_ptr(), x.numel(), _stream()), "b200_relu_bwd_bf16")
+    launch_count += 1
+    return dy
+
+
+def add(a: torch.Tensor, b: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    global launch_count
+    out = torch.empty_like(a) if out is None else out
+    _check(load().b200_add_bf16(out.data_ptr(), a.data_ptr(), b.data_ptr(), a.numel(), _stream()), "b200_add_bf16")
+    launch_count += 1
+    return out
+
+
+def randn_(out: torch.Tensor, seed: int, scale: float = 1.0) -> torch.Tensor:
+    global launch_count
+    assert out.dtype == torch.bfloat16 and out.is_contiguous()
+    _check(load().b200_randn_bf16(out.data_ptr(), out.numel(), int(seed), float(scale), _stream()), "b200_randn_bf16")
+    launch_count += 1
+    return out
+
+
+def cast_to_bf16(x: torch.Tensor) -> torch.Tensor:
+    global launch_count
+    out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    _check(load().b200_cast_f32_to_bf16(out.data_ptr(), x.data_ptr(), x.numel(), _stream()), "b200_cast_f32_to_bf16")
+    launch_count += 1
+    return out
+
+
+def cast_to_f32(x: torch.Tensor) -> torch.Tensor:
+    global launch_count
+    out = torch.empty(x.shape, dtype=torch.float32, device=x.device)
+    _check(load().b200_cast_bf16_to_f32(out.data_ptr(), x.data_ptr(), x.numel(), _stream()), "b200_cast_bf16_to_f32")
+    launch_count += 1
+    return out
+
+
+_sumsq_scratch: dict[int, torch.Tensor] = {}
+
+
+def sumsq(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Deterministic sum of squares (fp32 scalar tensor on the device)."""
+    global launch_count
+    lib = load()
+    dev = x.device.index or 0
+    sc = _sumsq_scratch.get(dev)
+    if sc is None:
+        sc = torch.zeros(int(lib.b200_sumsq_scratch_bytes()), dtype=torch.uint8, device=x.device)
+        _sumsq_scratch[dev] = sc
+    out = torch.empty(1, dtype=torch.float32, device=x.device) if out is None else out
+    _check(lib.b200_sumsq_bf16(out.data_ptr(), x.data_ptr(), x.numel(), sc.data_ptr(), sc.numel(), _stream()),
+           "b200_sumsq_bf16")
+    launch_count += 1
+    return out
+
+
+def fill_zero_(buf: torch.Tensor) -> None:
+    global launch_count
+    _check(load().b200_fill_zero(buf.data_ptr(), buf.numel() * buf.element_size(), _stream()), "b200_fill_zero")
+    launch_count += 1

@@ -1,0 +1,107 @@
+"""Synthetic data: the reference's per-seed CPU generator plus pinned-staging and on-device variants.
+
+Reference: ``mock_data`` (``train_ffns.py:144-151``) - for every seed, reseed a CPU generator and draw
+``x = randn(T, D)`` then ``dloss_dx = 0.1 * randn(T, D)``; the seed vector is
+``randint(100_000, (num_steps,))`` (``:360``); DDP/FSDP give rank ``r`` the seeds ``seeds[r::n]`` (``:182``).
+"""
+from __future__ import annotations
+
+from typing import Iterator, Optional, Sequence, Tuple
+
+import torch
+
+from ..config import DLOSS_DX_COEF, SEED_RANGE
+
+
+def make_seeds(num_steps: int, gen: Optional[torch.Generator]) -> torch.Tensor:
+    return torch.randint(SEED_RANGE, (num_steps,), generator=gen)
+
+
+def split_seeds(seeds: torch.Tensor, world: int) -> list[torch.Tensor]:
+    """Rank r gets ``seeds[r::world]`` (``train_ffns.py:182``). Requires ``len(seeds) % world == 0`` (``:175``)."""
+    if len(seeds) % world != 0:
+        raise ValueError(f"num_steps ({len(seeds)}) must be divisible by world size ({world})")
+    return [t.reshape(-1) for t in seeds.reshape((-1, world)).chunk(world, dim=1)]
+
+
+def mock_batch(seed: int, tokens: int, model_size: int, gen: Optional[torch.Generator] = None):
+    gen = gen or torch.Generator()
+    gen.manual_seed(int(seed))
+    x = torch.randn((tokens, model_size), generator=gen)
+    dloss_dx = DLOSS_DX_COEF * torch.randn((tokens, model_size), generator=gen)
+    return x, dloss_dx
+
+
+def mock_data(seeds: Sequence[int] | torch.Tensor, tokens: int, model_size: int,
+              dtype: torch.dtype = torch.float32, device: Optional[torch.device] = None,
+              pin: bool = False) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+    """Yield ``(x, dloss_dx)`` per seed; bit-identical to the reference on CPU/fp32."""
+    gen = torch.Generator()
+    seed_list = seeds.tolist() if isinstance(seeds, torch.Tensor) else list(seeds)
+    for seed in seed_list:
+        x, dy = mock_batch(seed, tokens, model_size, gen)
+        if dtype != torch.float32:
+            x, dy = x.to(dtype), dy.to(dtype)
+        if pin and torch.cuda.is_available():
+            x, dy = x.pin_memory(), dy.pin_memory()
+        if device is not None and device.type != "cpu":
+            x, dy = x.to(device, non_blocking=pin), dy.to(device, non_blocking=pin)
+        yield x, dy
+
+
+def device_mock_data(seeds: Sequence[int] | torch.Tensor, tokens: int, model_size: int, dtype: torch.dtype,
+                     device: torch.device) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+    """Same contract, generated on the device (Philox): same seed => same batch on every rank, but the values
+    differ from the CPU generator's.  bf16 on CUDA uses the native ``b200_randn_bf16`` kernel."""
+    seed_list = seeds.tolist() if isinstance(seeds, torch.Tensor) else list(seeds)
+    use_native = device.type == "cuda" and dtype == torch.bfloat16
+    if use_native:
+        from ..ops import native as nv
+    for seed in seed_list:
+        if use_native:
+            x = nv.randn_(torch.empty(tokens, model_size, dtype=dtype, device=device), 2 * int(seed), 1.0)
+            dy = nv.randn_(torch.empty(tokens, model_size, dtype=dtype, device=device), 2 * int(seed) + 1, DLOSS_DX_COEF)
+        else:
+            g = torch.Generator(device=device)
+            g.manual_seed(int(seed))
+            x = torch.randn((tokens, model_size), generator=g, device=device).to(dtype)
+            dy = (DLOSS_DX_COEF * torch.randn((tokens, model_size), generator=g, device=device)).to(dtype)
+        yield x, dy
+
+
+class PinnedPrefetcher:
+    """Double-buffered pinned-host -> device staging on a side stream (replaces the reference's synchronous
+    pageable ``.cuda()`` at ``train_ffns.py:106,158,231,294``).  ``next()`` returns device tensors whose copy has
+    been ordered before the current stream."""
+
+    def __init__(self, batches: Iterator[Tuple[torch.Tensor, torch.Tensor]], device: torch.device):
+        self.it = iter(batches)
+        self.device = device
+        self.stream = torch.cuda.Stream(device=device)
+        self._next = None
+        self._preload()
+
+    def _preload(self) -> None:
+        try:
+            x, dy = next(self.it)
+        except StopIteration:
+            self._next = None
+            return
+        if not x.is_pinned():
+            x, dy = x.pin_memory(), dy.pin_memory()
+        with torch.cuda.stream(self.stream):
+            self._next = (x.to(self.device, non_blocking=True), dy.to(self.device, non_blocking=True))
+            self._bytes = x.numel() * x.element_size() + dy.numel() * dy.element_size()
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        if self._next is None:
+            raise StopIteration
+        torch.cuda.current_stream(self.device).wait_stream(self.stream)
+        x, dy = self._next
+        x.record_stream(torch.cuda.current_stream(self.device))
+        dy.record_stream(torch.cuda.current_stream(self.device))
+        self._preload()
+        return x, dy

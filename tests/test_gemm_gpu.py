@@ -1,0 +1,142 @@
+"""tcgen05 GEMM numerics vs a plain fp32 PyTorch reference (all operand layouts, all epilogues, ragged shapes)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from distributed_llm_code_samples_b200.ops import native as nv  # noqa: E402
+
+
+def _rand(shape, dev, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(torch.bfloat16).to(dev)
+
+
+def _check(out, ref, K, what):
+    out = out.float()
+    err = (out - ref).abs().max().item()
+    tol = 2e-2 * max(1.0, ref.abs().max().item()) + 1e-3
+    assert torch.isfinite(out).all(), f"{what}: non-finite output"
+    assert err <= tol, f"{what}: max abs err {err} > {tol} (K={K})"
+
+
+SHAPES = [(128, 256, 64), (256, 512, 256), (200, 264, 136), (384, 768, 1024), (1024, 256, 4096), (130, 8, 72)]
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_gemm_tn(cuda_device, M, N, K):
+    """y = x @ W^T (train_ffns.py:42): both operands K-major."""
+    x, w = _rand((M, K), cuda_device, seed=1), _rand((N, K), cuda_device, 0.1, seed=2)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
+    nv.gemm(x, nv.MAJOR_K, w, nv.MAJOR_K, out, M, N, K)
+    _check(out, x.float() @ w.float().T, K, "TN")
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_gemm_nn(cuda_device, M, N, K):
+    """dx = dy @ W (train_ffns.py:45 'bc,cd->bd'): B is MN-major."""
+    dy, w = _rand((M, K), cuda_device, seed=3), _rand((K, N), cuda_device, 0.1, seed=4)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
+    nv.gemm(dy, nv.MAJOR_K, w, nv.MAJOR_MN, out, M, N, K)
+    _check(out, dy.float() @ w.float(), K, "NN")
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+def test_gemm_nt(cuda_device, M, N, K):
+    """dW = dy^T @ x (train_ffns.py:45 'bc,bd->cd'): both operands MN-major, K = tokens."""
+    if M % 8:
+        pytest.skip("MN-major A needs M % 8 == 0 (TMA pitch)")
+    dy, x = _rand((K, M), cuda_device, seed=5), _rand((K, N), cuda_device, 0.1, seed=6)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
+    nv.gemm(dy, nv.MAJOR_MN, x, nv.MAJOR_MN, out, M, N, K)
+    _check(out, dy.float().T @ x.float(), K, "NT")
+
+
+def test_epilogues(cuda_device):
+    M, N, K = 384, 512, 320
+    x, w = _rand((M, K), cuda_device, seed=7), _rand((N, K), cuda_device, 0.1, seed=8)
+    aux = _rand((M, N), cuda_device, seed=9)
+    bias = torch.randn(N, device=cuda_device)
+    ref = x.float() @ w.float().T
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
+    out2 = torch.empty_like(out)
+
+    nv.gemm(x, 0, w, 0, out, M, N, K, nv.EPI_RELU)
+    _check(out, torch.relu(ref), K, "relu")
+    nv.gemm(x, 0, w, 0, out, M, N, K, nv.EPI_RELU, bias=bias)
+    _check(out, torch.relu(ref + bias), K, "relu+bias")
+    nv.gemm(x, 0, w, 0, out, M, N, K, nv.EPI_GELU, out2=out2)
+    _check(out, torch.nn.functional.gelu(ref), K, "gelu")
+    _check(out2, ref, K, "gelu pre-activation")
+    nv.gemm(x, 0, w, 0, out, M, N, K, nv.EPI_RELU_BWD, aux=aux)
+    _check(out, ref * (aux.float() > 0), K, "relu_bwd")
+    nv.gemm(x, 0, w, 0, out, M, N, K, nv.EPI_GELU_BWD, aux=aux)
+    a = aux.float().requires_grad_(True)
+    torch.nn.functional.gelu(a).sum().backward()
+    _check(out, ref * a.grad, K, "gelu_bwd")
+    nv.gemm(x, 0, w, 0, out, M, N, K, nv.EPI_ADD, aux=aux)
+    _check(out, ref + aux.float(), K, "add")
+    wgt = _rand((M, N), cuda_device, seed=10)
+    w0 = wgt.float().clone()
+    nv.gemm(x, 0, w, 0, wgt, M, N, K, nv.EPI_SGD, alpha=0.05)
+    _check(wgt, w0 - 0.05 * ref, K, "sgd")
+    o32 = torch.empty(M, N, dtype=torch.float32, device=cuda_device)
+    nv.gemm(x, 0, w, 0, o32, M, N, K, nv.EPI_STORE_F32, alpha=0.5)
+    assert (o32 - 0.5 * ref).abs().max().item() < 1e-2
+
+
+def test_gemm_strided_views(cuda_device):
+    """Operands that are column slices of bigger tensors (leading dimension != row length)."""
+    M, N, K = 256, 256, 128
+    xb, wb = _rand((M, 2 * K), cuda_device, seed=11), _rand((N, 3 * K), cuda_device, 0.1, seed=12)
+    x, w = xb[:, K:], wb[:, K:2 * K]
+    outb = torch.zeros(M, 2 * N, dtype=torch.bfloat16, device=cuda_device)
+    nv.gemm(x, 0, w, 0, outb[:, N:], M, N, K)
+    _check(outb[:, N:], x.float() @ w.float().T, K, "strided")
+    assert outb[:, :N].abs().max().item() == 0
+
+
+def test_gemm_rejects_bad_shapes(cuda_device):
+    x = torch.zeros(16, 12, dtype=torch.bfloat16, device=cuda_device)
+    w = torch.zeros(16, 12, dtype=torch.bfloat16, device=cuda_device)
+    out = torch.zeros(16, 16, dtype=torch.bfloat16, device=cuda_device)
+    with pytest.raises(nv.NativeError):
+        nv.gemm(x, 0, w, 0, out, 16, 16, 12)   # pitch 12 elements = 24 bytes: not a TMA-legal stride
+
+
+def test_elementwise(cuda_device):
+    n = 1000003
+    p, g = _rand((n,), cuda_device, seed=13), _rand((n,), cuda_device, seed=14)
+    p0 = p.float().clone()
+    nv.sgd_(p, g, 0.1)
+    assert (p.float() - (p0 - 0.1 * g.float())).abs().max().item() < 2e-2
+    x = _rand((n,), cuda_device, seed=15)
+    assert torch.equal(nv.relu(x), torch.relu(x))
+    dy = _rand((n,), cuda_device, seed=16)
+    ref = dy.clone().masked_fill_(x <= 0, 0)
+    assert torch.equal(nv.relu_bwd_(dy, x), ref)
+    a, b = _rand((n,), cuda_device, seed=17), _rand((n,), cuda_device, seed=18)
+    assert (nv.add(a, b).float() - (a.float() + b.float())).abs().max().item() < 2e-2
+    s = nv.sumsq(x)
+    s2 = nv.sumsq(x)
+    assert torch.equal(s, s2)                                   # deterministic, scratch reusable
+    assert abs(s.item() - (x.float() ** 2).sum().item()) / s.item() < 1e-4
+    r = nv.randn_(torch.empty(1 << 20, dtype=torch.bfloat16, device=cuda_device), seed=1234, scale=2.0)
+    assert abs(r.float().mean().item()) < 0.02 and abs(r.float().std().item() - 2.0) < 0.05
+    f = torch.randn(4099, device=cuda_device)
+    assert torch.equal(nv.cast_to_bf16(f), f.to(torch.bfloat16))
+    assert torch.equal(nv.cast_to_f32(nv.cast_to_bf16(f)), f.to(torch.bfloat16).float())
+
+
+def test_adam(cuda_device):
+    n = 4096
+    p, g = _rand((n,), cuda_device, seed=19), _rand((n,), cuda_device, seed=20)
+    m = torch.zeros(n, device=cuda_device)
+    v = torch.zeros(n, device=cuda_device)
+    pr = torch.nn.Parameter(p.float().clone())
+    opt = torch.optim.Adam([pr], lr=1e-2)
+    for step in range(1, 4):
+        pr.grad = g.float().clone()
+        opt.step()
+        nv.adam_(p, g, m, v, 1e-2, 0.9, 0.999, 1e-8, step)
+    assert (p.float() - pr.detach()).abs().max().item() < 6e-2   # three bf16 roundings at |p|~3
