@@ -82,11 +82,11 @@ __global__ void __launch_bounds__(EW_THREADS) ew_kernel(__nv_bfloat16* out, cons
         unpack8(reinterpret_cast<const uint4*>(a)[i], x);
         if (OP == 0) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) y[j] = x[j] > 0.f ? x[j] : 0.f;
+            for (int j = 0; j < 8; ++j) y[j] = x[j] <= 0.f ? 0.f : x[j];
         } else if (OP == 1) {
             unpack8(reinterpret_cast<const uint4*>(out)[i], y);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) y[j] = x[j] > 0.f ? y[j] : 0.f;
+            for (int j = 0; j < 8; ++j) y[j] = x[j] <= 0.f ? 0.f : y[j];
         } else {
             unpack8(reinterpret_cast<const uint4*>(b)[i], y);
 #pragma unroll
@@ -97,8 +97,8 @@ __global__ void __launch_bounds__(EW_THREADS) ew_kernel(__nv_bfloat16* out, cons
     for (long long i = n8 * 8 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const float x = __bfloat162float(a[i]);
         float y;
-        if (OP == 0) y = x > 0.f ? x : 0.f;
-        else if (OP == 1) y = x > 0.f ? __bfloat162float(out[i]) : 0.f;
+        if (OP == 0) y = x <= 0.f ? 0.f : x;
+        else if (OP == 1) y = x <= 0.f ? 0.f : __bfloat162float(out[i]);
         else y = x + __bfloat162float(b[i]);
         out[i] = __float2bfloat16_rn(y);
     }

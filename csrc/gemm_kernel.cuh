@@ -281,7 +281,7 @@ struct LocalEpi {
             __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C) + (long long)row * p.ldc + col;
             if constexpr (KIND == EPI_RELU) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) f[j] = f[j] > 0.0f ? f[j] : 0.0f;
+                for (int j = 0; j < 8; ++j) f[j] = f[j] <= 0.0f ? 0.0f : f[j];   // NaN stays NaN, like torch.where(x<=0,0,x)
             } else if constexpr (KIND == EPI_GELU) {
                 uint4 pre;
                 pre.x = pack_bf16x2(f[0], f[1]); pre.y = pack_bf16x2(f[2], f[3]);
@@ -296,8 +296,8 @@ struct LocalEpi {
                 for (int j = 0; j < 4; ++j) {
                     const float lo = bf16_lo(aw[j]), hi = bf16_hi(aw[j]);
                     if constexpr (KIND == EPI_RELU_BWD) {
-                        f[2 * j] = lo > 0.0f ? f[2 * j] : 0.0f;
-                        f[2 * j + 1] = hi > 0.0f ? f[2 * j + 1] : 0.0f;
+                        f[2 * j] = lo <= 0.0f ? 0.0f : f[2 * j];            // masked_fill_(x <= 0, 0)
+                        f[2 * j + 1] = hi <= 0.0f ? 0.0f : f[2 * j + 1];
                     } else if constexpr (KIND == EPI_GELU_BWD) {
                         f[2 * j] *= gelu_grad_f(lo);
                         f[2 * j + 1] *= gelu_grad_f(hi);

@@ -44,10 +44,11 @@ class TorchOps:
         if act == "relu":
             dx = dx.masked_fill_(aux <= 0, 0)
         elif act == "gelu":
-            a32 = aux.float()
+            ct = torch.float64 if aux.dtype == torch.float64 else torch.float32
+            a32 = aux.to(ct)
             cdf = 0.5 * (1.0 + torch.erf(a32 * 0.7071067811865476))
             pdf = torch.exp(-0.5 * a32 * a32) * 0.3989422804014327
-            dx = (dx.float() * (cdf + a32 * pdf)).to(dy.dtype)
+            dx = (dx.to(ct) * (cdf + a32 * pdf)).to(dy.dtype)
         if add is not None:
             dx = dx + add
         return dx

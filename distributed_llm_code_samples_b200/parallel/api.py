@@ -1,0 +1,167 @@
+"""Strategy drivers with the reference's uniform signature
+
+    fn(layers_params, seeds, batch_size, model_size) -> layers_params
+
+(``train_1gpu`` ``train_ffns.py:101``, ``train_ddp`` ``:174``, ``train_fsdp`` ``:262``, ``train_tp`` ``:315``;
+``batch_size`` is the token count per step, ``:379``).  Each driver spawns one process per rank, lets every rank
+build ITS OWN replica/shard from the shared CPU parameters (no parent-side CUDA contexts), runs the
+per-rank trainer and writes the result back into CPU shared-memory tensors owned by the parent.
+"""
+from __future__ import annotations
+
+import copy
+from typing import List, Optional, Sequence
+
+import torch
+
+from ..config import TrainConfig
+from ..models.ffn import Params
+from ..ops import get_ops
+from ..utils.data import device_mock_data, mock_data, split_seeds
+from ..utils.profiler import profile_if
+from ..utils.timing import DeviceTimer, max_over_ranks, tokens_per_second
+from .base import fsdp_shard, place, tp_shard, tp_shard_dim
+from .comm import LocalComm, make_comm
+from .ddp import DDPTrainer
+from .fsdp import FSDPTrainer
+from .launcher import launch, pick_backend, pick_device, visible_world
+from .mp import MPTrainer
+from .single import SingleTrainer
+
+METHODS = ("single", "ddp", "fsdp", "mp")
+
+
+def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Sequence[Params], device: torch.device):
+    """Place/shard the full CPU parameters for this rank and return its trainer."""
+    dtype = cfg.torch_dtype
+    r, n = comm.rank, comm.world
+    if method == "single" or n == 1:        # a world of one: every strategy degenerates to the single-device loop
+        return SingleTrainer(ops, cfg, place(layers_params, device, dtype))
+    if method == "ddp":
+        if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg):
+            from .fused import FusedDDPTrainer
+            return FusedDDPTrainer(ops, comm, cfg, layers_params, device)
+        return DDPTrainer(ops, comm, cfg, place(layers_params, device, dtype))
+    if method == "fsdp":
+        shards = [[fsdp_shard(p, r, n) for p in lp] for lp in layers_params]
+        if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg):
+            from .fused import FusedFSDPTrainer
+            return FusedFSDPTrainer(ops, comm, cfg, place(shards, device, dtype), device)
+        return FSDPTrainer(ops, comm, cfg, place(shards, device, dtype))
+    if method == "mp":
+        shards = [[tp_shard(p, j, r, n) for j, p in enumerate(lp)] for lp in layers_params]
+        if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg):
+            from .fused import FusedMPTrainer
+            return FusedMPTrainer(ops, comm, cfg, place(shards, device, dtype), device)
+        return MPTrainer(ops, comm, cfg, place(shards, device, dtype))
+    raise ValueError(f"unknown method {method!r}")
+
+
+def _fused_available(ops, comm, cfg: TrainConfig) -> bool:
+    """The peer-memory fused kernels need the native ops, bf16, >1 rank, SGD, no bias and TMA-legal shapes."""
+    ok = (getattr(ops, "name", "") == "native" and comm.world > 1 and cfg.dtype in ("bf16", "bfloat16")
+          and cfg.optimizer == "sgd" and not cfg.bias and cfg.model_size % 8 == 0 and cfg.ffn_dim % 8 == 0)
+    if not ok:
+        if cfg.comm == "fused":
+            raise RuntimeError("comm=fused needs impl=native, bf16, SGD, no bias, world>1 and dims % 8 == 0")
+        return False
+    try:
+        from . import fused  # noqa: F401
+        return fused.available()
+    except ImportError:
+        if cfg.comm == "fused":
+            raise
+        return False
+
+
+def _write_back(method: str, trainer, comm, out_params: Sequence[Params]) -> None:
+    """Copy this rank's result into the parent's shared CPU tensors (full layout, any strategy)."""
+    r, n = comm.rank, comm.world
+    for i, lp in enumerate(trainer.params if method in ("single", "ddp") else trainer.shards):
+        for j, p in enumerate(lp):
+            dst = out_params[i][j]
+            src = p.detach().to("cpu", dtype=dst.dtype)
+            if method in ("single", "ddp"):
+                if r == 0:
+                    dst.copy_(src)
+            elif method == "fsdp":
+                dst.chunk(n, dim=0)[r].copy_(src)
+            else:
+                dim = tp_shard_dim(j)
+                if dim is None:
+                    if r == 0:
+                        dst.copy_(src)
+                else:
+                    dst.chunk(n, dim=dim)[r].copy_(src)
+
+
+def _rank_main(rank: int, world: int, device: torch.device, method: str, cfg_dict: dict,
+               layers_params: Sequence[Params], seeds: torch.Tensor, tokens: int, model_size: int,
+               out_params: Sequence[Params], stats: torch.Tensor) -> None:
+    cfg = TrainConfig(**cfg_dict)
+    ops = get_ops(cfg.impl, device)
+    comm = make_comm() if world > 1 else LocalComm()
+    trainer = build_trainer(method, ops, comm, cfg, layers_params, device)
+    my_seeds = split_seeds(seeds, world)[rank] if method in ("ddp", "fsdp") else seeds
+    if cfg.data == "device" and device.type == "cuda":
+        batches = device_mock_data(my_seeds, tokens, model_size, cfg.torch_dtype, device)
+    else:
+        batches = mock_data(my_seeds, tokens, model_size, cfg.torch_dtype, device)
+    with profile_if(cfg.profile, rank):
+        with DeviceTimer(device) as t:
+            trainer.run(batches)
+    ms = max_over_ranks(t.ms, comm, device)
+    steps = len(my_seeds)
+    global_tokens = tokens * (world if method in ("ddp", "fsdp") else 1)
+    if rank == 0:
+        stats[0] = ms
+        stats[1] = tokens_per_second(global_tokens, steps, ms)
+    _write_back(method, trainer, comm, out_params)
+
+
+def _run(method: str, layers_params: Sequence[Params], seeds: torch.Tensor, tokens: int, model_size: int,
+         cfg: Optional[TrainConfig]) -> List[Params]:
+    cfg = copy.deepcopy(cfg) if cfg is not None else TrainConfig(model_size=model_size)
+    cfg.model_size = model_size
+    cfg.ffn_dim = layers_params[0][0].shape[0]
+    cfg.bias = len(layers_params[0]) == 4
+    device = pick_device(cfg.device)
+    world = 1 if method == "single" else visible_world(cfg.world_size, device)
+    backend = pick_backend(cfg.backend, device)
+    if method in ("ddp", "fsdp") and len(seeds) % world:
+        raise AssertionError(f"len(seeds)={len(seeds)} must be divisible by the world size {world}")   # :175, :263
+    shared_in = [[p.detach().clone().share_memory_() for p in lp] for lp in layers_params]
+    out = [[torch.empty_like(p).share_memory_() for p in lp] for lp in layers_params]
+    stats = torch.zeros(2, dtype=torch.float64).share_memory_()
+    args = (method, cfg.to_dict(), shared_in, seeds, tokens, model_size, out, stats)
+    if world == 1:
+        dev = torch.device("cuda", 0) if device == "cuda" else torch.device("cpu")
+        _rank_main(0, 1, dev, *args)
+    else:
+        launch(world, _rank_main, args, backend=backend, device=device, port=cfg.master_port if cfg.master_port != 29500 else 0)
+    _run.last_stats = {"ms": float(stats[0]), "tokens_per_s": float(stats[1]), "world": world}
+    return [list(lp) for lp in out]
+
+
+_run.last_stats = {}
+
+
+def last_stats() -> dict:
+    """Device-timed milliseconds (max over ranks) and tokens/s of the most recent driver call."""
+    return dict(_run.last_stats)
+
+
+def train_1gpu(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None):
+    return _run("single", layers_params, seeds, batch_size, model_size, cfg)
+
+
+def train_ddp(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None):
+    return _run("ddp", layers_params, seeds, batch_size, model_size, cfg)
+
+
+def train_fsdp(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None):
+    return _run("fsdp", layers_params, seeds, batch_size, model_size, cfg)
+
+
+def train_tp(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None):
+    return _run("mp", layers_params, seeds, batch_size, model_size, cfg)

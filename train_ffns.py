@@ -1,0 +1,119 @@
+#!/usr/bin/env python
+"""Train a stack of Transformer FFN sub-blocks on synthetic data under 1 GPU / DDP / FSDP / MP.
+
+Same command line as the reference (``train_ffns.py:343-351``):
+
+    python train_ffns.py --num_steps 16 --batch_size 8 --seq_len 1024 --layers 1 --model_size 8192 --method M
+
+``M``: 0 = all methods, 1 = one GPU, 2 = DDP, 3 = FSDP, 4 = MP/TP (``:5-6``).  Extra flags select what the
+reference hard-codes: ``--ffn_dim --dtype --activation --residual --bias --optimizer --lr --world_size --backend
+--device --impl --comm --recompute --mp_mode --save_path --load_path --profile --data``.
+"""
+from __future__ import annotations
+
+import argparse
+import time
+
+import torch
+
+from distributed_llm_code_samples_b200.config import TrainConfig
+from distributed_llm_code_samples_b200.models.ffn import init_stack, num_params
+from distributed_llm_code_samples_b200.parallel import api
+from distributed_llm_code_samples_b200.utils.checkpoint import load_checkpoint, save_checkpoint
+from distributed_llm_code_samples_b200.utils.data import make_seeds
+
+
+def build_parser() -> argparse.ArgumentParser:
+    p = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    p.add_argument('-s', '--num_steps', type=int, default=1)
+    p.add_argument('-bs', '--batch_size', type=int, default=8)
+    p.add_argument('-n', '--seq_len', type=int, default=1024)
+    p.add_argument('-l', '--layers', type=int, default=1)
+    p.add_argument('-d', '--model_size', type=int, default=4)
+    p.add_argument('-m', '--method', type=int, default=0)
+    p.add_argument('-r', '--random_seed', type=int, default=0)   # 0 = unseeded (train_ffns.py:355-358)
+    # extensions
+    p.add_argument('--ffn_dim', type=int, default=None)
+    p.add_argument('--dtype', default='fp32', choices=['fp32', 'bf16'])
+    p.add_argument('--activation', default='relu', choices=['relu', 'gelu'])
+    p.add_argument('--residual', action='store_true')
+    p.add_argument('--bias', action='store_true')
+    p.add_argument('--optimizer', default='sgd', choices=['sgd', 'adam'])
+    p.add_argument('--lr', type=float, default=None)
+    p.add_argument('--grad_scale', type=float, default=1.0)
+    p.add_argument('--world_size', type=int, default=0)
+    p.add_argument('--backend', default='auto', choices=['auto', 'nccl', 'gloo'])
+    p.add_argument('--device', default='auto', choices=['auto', 'cuda', 'cpu'])
+    p.add_argument('--impl', default='auto', choices=['auto', 'native', 'torch'])
+    p.add_argument('--comm', default='auto', choices=['auto', 'fused', 'nccl'])
+    p.add_argument('--recompute', action='store_true')
+    p.add_argument('--mp_mode', default='ar', choices=['ar', 'sp'])
+    p.add_argument('--master_port', type=int, default=29500)
+    p.add_argument('--save_path', default=None)
+    p.add_argument('--load_path', default=None)
+    p.add_argument('--profile', action='store_true')
+    p.add_argument('--data', default='cpu', choices=['cpu', 'device'])
+    return p
+
+
+def main(argv=None) -> int:
+    args = build_parser().parse_args(argv)
+    cfg_kwargs = {k: v for k, v in vars(args).items() if v is not None}
+    cfg = TrainConfig(**cfg_kwargs)
+    ffn = cfg.ffn_dim
+
+    print(f'ARGS:\n num_steps: {args.num_steps}\n BS: {args.batch_size}\n N: {args.seq_len}\n D: {args.model_size}\n FFN: {ffn}\n')
+
+    gen = None
+    if args.random_seed != 0:
+        gen = torch.Generator()
+        gen.manual_seed(args.random_seed)
+
+    seeds = make_seeds(args.num_steps, gen)
+    layers_params = init_stack(args.layers, args.model_size, ffn, gen, bias=args.bias)
+    start_step = 0
+    if args.load_path:
+        ck = load_checkpoint(args.load_path)
+        layers_params = ck["layers_params"]
+        start_step = ck.get("step", 0)
+        if ck.get("seeds") is not None and len(ck["seeds"]) == len(seeds):
+            seeds = ck["seeds"]
+        print(f'resumed from {args.load_path} at step {start_step}')
+
+    n_params = num_params(layers_params)
+    print(f'PARAMS: {n_params:_} (size {4 * n_params / (1024 * 1024 * 1024)} GB)')
+    print('\n')
+    print('initial layers_params[0]', layers_params[0][0].shape, layers_params[0][1].shape)
+    print('initial layers_params[0]', layers_params[0][0][:5, :5], layers_params[0][1][:5, :5])
+
+    fns = [api.train_1gpu, api.train_ddp, api.train_fsdp, api.train_tp]
+    fns_layers_params = []
+    run_seeds = seeds[start_step:] if start_step else seeds
+    for i, fn in enumerate(fns):
+        if args.method == 0 or args.method == i + 1:
+            t0 = time.time()
+            out = fn(layers_params, run_seeds, args.batch_size * args.seq_len, args.model_size, cfg)
+            t1 = time.time()
+            fns_layers_params.append(out)
+            st = api.last_stats()
+            print(f'\n{fn.__name__} takes {t1 - t0} seconds')
+            print(f'{fn.__name__} device time {st.get("ms", 0.0):.3f} ms, {st.get("tokens_per_s", 0.0):.1f} tokens/s '
+                  f'on {st.get("world", 1)} rank(s) (device-timed, max over ranks)')
+            print(f'final {fn.__name__} layers_params[0]', out[0][0].shape, out[0][1].shape)
+            print(f'final {fn.__name__} layers_params[0]', out[0][0][:5, :5], out[0][1][:5, :5])
+            if args.save_path:
+                path = args.save_path if args.method != 0 else f'{args.save_path}.{fn.__name__}'
+                save_checkpoint(path, out, step=len(seeds), args=cfg.to_dict(), seeds=seeds)
+                print(f'saved {path}')
+
+    if args.method == 0:   # compare DDP against FSDP (train_ffns.py:386-391)
+        for l in range(args.layers):
+            for k in range(2):
+                a, b = fns_layers_params[1][l][k], fns_layers_params[2][l][k]
+                if not torch.allclose(a, b):
+                    print(f"SoftAssertionError: L {l} ddp[{k}] {a} fsdp[{k}] {b}")
+    return 0
+
+
+if __name__ == '__main__':
+    raise SystemExit(main())
