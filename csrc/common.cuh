@@ -15,6 +15,11 @@
 #define B200_SPIN_TIMEOUT_CYCLES (8000000000ll)
 #endif
 
+#ifndef B200_FLAG_TIMEOUT_CYCLES
+// Cross-rank waits tolerate a peer that is legitimately late (launch skew, first-call set-up): ~60 s.
+#define B200_FLAG_TIMEOUT_CYCLES (120000000000ll)
+#endif
+
 namespace b200 {
 
 // ---------------------------------------------------------------------------------------------
@@ -213,7 +218,7 @@ __device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t target,
     long long t0 = clock64();
     uint32_t spins = 0;
     while ((int32_t)(ld_acquire_sys(p) - target) < 0) {
-        if (((++spins) & 0xff) == 0 && (clock64() - t0) > B200_SPIN_TIMEOUT_CYCLES)
+        if (((++spins) & 0xff) == 0 && (clock64() - t0) > B200_FLAG_TIMEOUT_CYCLES)
             device_fail(err, ERR_FLAG_TIMEOUT, tag);
     }
 }

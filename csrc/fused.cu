@@ -1,0 +1,281 @@
+// Fused GEMM + collective: ONE persistent tcgen05 kernel that computes its output tiles and, tile by tile,
+// reduces them across ranks over NVLink peer memory.
+//
+//   push    each finished accumulator tile is converted to bf16, transposed through shared memory so that every
+//           warp store covers whole 128-byte lines, and STORED INTO THE OWNER RANK'S INBOX (a peer pointer); a
+//           release flag per (tile, source) tells the owner it has landed.  The next tile's MMAs are already
+//           running (TMEM double buffer), so the transfer overlaps the math.
+//   reduce  between tiles the epilogue warps poll (non-blocking) the owned tiles assigned to this CTA; a tile whose
+//           `world` partials have all arrived is summed in fp32 in a fixed order, the optional optimizer step is
+//           applied (W -= alpha * sum) and the result is written to the local output and, in broadcast mode, to
+//           every peer's output.  What is still outstanding when the CTA runs out of GEMM tiles is finished in a
+//           blocking tail.
+//   done    in broadcast mode the kernel returns only when every tile of the local output has been delivered.
+//
+// One kernel therefore covers the reference's
+//   DDP   dW GEMM + all_reduce(SUM) + SGD      (train_ffns.py:66/68 + :165 + :172)   interleaved owners, broadcast, SGD
+//   FSDP  dW GEMM + reduce_scatter + shard SGD (:66/68 + :255-256 + :258-259)        row-sharded owners, local, SGD
+//   MP    row-parallel GEMM + all_reduce       (:57 + :303, :68 + :309)              interleaved owners, broadcast, SUM
+//   MP-SP row-parallel GEMM + reduce_scatter   (sequence-parallel extension)         row-sharded owners, local, SUM
+//
+// Inbox slots are double-buffered by call parity so a fast rank may start the next call while a slow one is still
+// reducing; flags carry a per-channel sequence number (monotonic, never reset).  Ranks rotate their tile order so
+// that at any moment they push to different owners.
+#include "gemm_kernel.cuh"
+#include "../include/b200ffn.h"
+
+namespace b200 {
+
+constexpr int MAX_WORLD_F = 8;
+constexpr int TILE_ELEMS = BM * BN;                 // 32768 bf16 = 64 KiB per partial tile
+constexpr int EPI_THREADS = EPI_WARPS * 32;
+constexpr int MAX_OWNED_PER_CTA = 64;               // done counters live in the 256-byte epilogue scratch
+
+enum FusedOp : int { FOP_SUM = 0, FOP_SGD = 1 };
+enum OwnerMode : int { OWN_INTERLEAVED = 0, OWN_ROW_SHARDED = 1 };
+
+struct FusedParams {
+    void* inbox[MAX_WORLD_F];        // symmetric inbox base per rank: [2 parities][owned_cap][world][TILE_ELEMS] bf16
+    uint32_t* flags[MAX_WORLD_F];    // symmetric flags per rank: arrive[owned_cap][8] then ready[ready_cap]
+    void* out[MAX_WORLD_F];          // result base per rank (peers are touched only when broadcast)
+    long long ldo;
+    int out_row_offset;              // first global row held by `out` (row-sharded outputs)
+    int rank, world;
+    uint32_t seq;                    // per-channel call counter (>= 1), identical on every rank
+    int parity;                      // which inbox half this call uses
+    int owner_mode, mpo;             // mpo = m-tiles per owner (row-sharded)
+    int op, broadcast;
+    float alpha;
+    int owned_cap;
+    int owned_count;                 // tiles this rank owns in this call
+    int ready_base;                  // word offset of the ready flags inside the flag block
+};
+
+__device__ __forceinline__ int owner_of(const FusedParams& p, const GemmCore& g, int m_blk, int n_blk, int& k_local) {
+    if (p.owner_mode == OWN_ROW_SHARDED) {
+        k_local = (m_blk % p.mpo) * g.tiles_n + n_blk;
+        return m_blk / p.mpo;
+    }
+    const int lin = m_blk * g.tiles_n + n_blk;
+    k_local = lin / p.world;
+    return lin % p.world;
+}
+__device__ __forceinline__ void owned_tile_coords(const FusedParams& p, const GemmCore& g, int k_local, int& m_blk, int& n_blk) {
+    if (p.owner_mode == OWN_ROW_SHARDED) {
+        m_blk = p.rank * p.mpo + k_local / g.tiles_n;
+        n_blk = k_local % g.tiles_n;
+    } else {
+        const int lin = k_local * p.world + p.rank;
+        m_blk = lin / g.tiles_n;
+        n_blk = lin % g.tiles_n;
+    }
+}
+__device__ __forceinline__ size_t inbox_slot(const FusedParams& p, int k_local, int src) {
+    return ((size_t)(p.parity * p.owned_cap + k_local) * p.world + src) * TILE_ELEMS;
+}
+__device__ __forceinline__ void epi_group_sync() {       // the 8 epilogue warps only (named barrier 1)
+    asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
+}
+__device__ __forceinline__ uint4 pack_row8(const uint32_t* a) {
+    uint4 v;
+    v.x = pack_bf16x2(__uint_as_float(a[0]), __uint_as_float(a[1]));
+    v.y = pack_bf16x2(__uint_as_float(a[2]), __uint_as_float(a[3]));
+    v.z = pack_bf16x2(__uint_as_float(a[4]), __uint_as_float(a[5]));
+    v.w = pack_bf16x2(__uint_as_float(a[6]), __uint_as_float(a[7]));
+    return v;
+}
+
+struct FusedEpi {
+    using Params = FusedParams;
+    static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
+    struct State {
+        int cursor;      // next owned tile (index into this CTA's list) this warp has not reduced yet
+        int k_local;     // inbox slot of the tile being pushed
+        int owner;
+    };
+
+    static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx& ctx, State& st) {
+        st.cursor = 0;
+        st.k_local = 0;
+        st.owner = 0;
+        if (ctx.ewarp == 0)
+            for (int i = ctx.lane; i < MAX_OWNED_PER_CTA; i += 32) ctx.scratch[i] = 0;
+        epi_group_sync();
+    }
+
+    // ---- push this warp's 32 rows x 128 columns of the accumulator into the owner's inbox ------------------
+    static __device__ __forceinline__ void process_tile(const Params& p, const GemmCore& g, const EpiCtx& ctx, uint32_t taddr, State& st) {
+        st.owner = owner_of(p, g, ctx.m_blk, ctx.n_blk, st.k_local);
+        __nv_bfloat16* dst_tile = reinterpret_cast<__nv_bfloat16*>(p.inbox[st.owner]) + inbox_slot(p, st.k_local, p.rank);
+        const int lane = ctx.lane;
+        uint4* stage = reinterpret_cast<uint4*>(ctx.stage);
+#pragma unroll 1
+        for (int cp = 0; cp < 2; ++cp) {                             // 64 columns = one 128-byte line per row
+            uint32_t a0[32], a1[32];
+            tmem_ld_32x32(taddr + cp * 64, a0);
+            tmem_ld_32x32(taddr + cp * 64 + 32, a1);
+            tmem_ld_wait();
+#pragma unroll
+            for (int pc = 0; pc < 4; ++pc) {                         // row-owner layout -> swizzled smem
+                stage[lane * 8 + (pc ^ (lane & 7))] = pack_row8(&a0[pc * 8]);
+                stage[lane * 8 + ((pc + 4) ^ (lane & 7))] = pack_row8(&a1[pc * 8]);
+            }
+            __syncwarp();
+            const int col_in_tile = ctx.half * (BN / 2) + cp * 64;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {                            // 8 lanes per row: whole 128-byte lines
+                const int r = i * 4 + (lane >> 3);
+                const int pc = lane & 7;
+                st_u4(dst_tile + (size_t)(ctx.q * 32 + r) * BN + col_in_tile + pc * 8, stage[r * 8 + (pc ^ (r & 7))]);
+            }
+            __syncwarp();
+        }
+    }
+
+    // ---- after the accumulator is handed back: publish the push, then reduce whatever is ready -------------
+    static __device__ __forceinline__ void after_tile(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st) {
+        epi_group_sync();                                            // all 8 warps' stores are issued
+        if (ctx.ewarp == 0 && ctx.lane == 0) {
+            __threadfence_system();
+            st_release_sys(p.flags[st.owner] + (size_t)st.k_local * MAX_WORLD_F + p.rank, p.seq);
+        }
+        drain(p, g, ctx, st, /*block=*/false);
+    }
+
+    static __device__ __forceinline__ void tail(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st) {
+        drain(p, g, ctx, st, /*block=*/true);
+        if (p.broadcast) {                                           // every tile of MY output has been delivered
+            const int num_tiles = g.tiles_m * g.tiles_n;
+            for (int t = blockIdx.x + ctx.ewarp * gridDim.x; t < num_tiles; t += gridDim.x * EPI_WARPS)
+                if (ctx.lane == 0) wait_flag_ge(p.flags[p.rank] + p.ready_base + t, p.seq, g.err, 0x700);
+        }
+    }
+
+    static __device__ __forceinline__ bool arrived(const Params& p, const GemmCore& g, int k_local, int lane, bool block) {
+        const uint32_t* f = p.flags[p.rank] + (size_t)k_local * MAX_WORLD_F;
+        bool ok = true;
+        if (lane < p.world) {
+            if (block) wait_flag_ge(f + lane, p.seq, g.err, 0x600 + lane);
+            else ok = (int32_t)(ld_acquire_sys(f + lane) - p.seq) >= 0;
+        }
+        return __all_sync(0xffffffffu, ok);
+    }
+
+    static __device__ __forceinline__ void drain(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st, bool block) {
+        while (true) {
+            const int k = blockIdx.x + st.cursor * gridDim.x;
+            if (k >= p.owned_count) return;
+            if (!arrived(p, g, k, ctx.lane, block)) return;
+            reduce_rows(p, g, k, ctx.ewarp, ctx.lane);
+            __threadfence_system();                                  // my results are visible system-wide ...
+            __syncwarp();
+            unsigned int prev = 0;
+            if (ctx.lane == 0) prev = atomicAdd(&ctx.scratch[st.cursor % MAX_OWNED_PER_CTA], 1u);   // ... before I count
+            prev = __shfl_sync(0xffffffffu, prev, 0);
+            if (prev == EPI_WARPS - 1 && p.broadcast) {              // last of the 8 warps publishes the tile
+                int m_blk, n_blk;
+                owned_tile_coords(p, g, k, m_blk, n_blk);
+                __threadfence_system();
+                if (ctx.lane < p.world) st_release_sys(p.flags[ctx.lane] + p.ready_base + m_blk * g.tiles_n + n_blk, p.seq);
+            }
+            ++st.cursor;
+        }
+    }
+
+    // one warp's 16 rows of owned tile k: sum the `world` partials, apply the op, store (and broadcast)
+    static __device__ __forceinline__ void reduce_rows(const Params& p, const GemmCore& g, int k_local, int ewarp, int lane) {
+        int m_blk, n_blk;
+        owned_tile_coords(p, g, k_local, m_blk, n_blk);
+        const __nv_bfloat16* inb = reinterpret_cast<const __nv_bfloat16*>(p.inbox[p.rank]);
+        const int col = n_blk * BN + lane * 8;                       // 32 lanes x 8 columns = one 256-wide row
+#pragma unroll 1
+        for (int r = 0; r < BM / EPI_WARPS; ++r) {
+            const int row_in_tile = ewarp * (BM / EPI_WARPS) + r;
+            const int grow = m_blk * BM + row_in_tile;
+            if (grow >= g.M || col >= g.N) continue;
+            float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int s = 0; s < p.world; ++s) {                      // fixed order: deterministic, rank-independent
+                const uint4 v = ld_cv_u4(inb + inbox_slot(p, k_local, s) + (size_t)row_in_tile * BN + lane * 8);
+                acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
+                acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z); acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
+            }
+            const size_t off = (size_t)(grow - p.out_row_offset) * p.ldo + col;
+            if (p.op == FOP_SGD) {
+                const uint4 w = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.out[p.rank]) + off);
+                acc[0] = bf16_lo(w.x) - p.alpha * acc[0]; acc[1] = bf16_hi(w.x) - p.alpha * acc[1];
+                acc[2] = bf16_lo(w.y) - p.alpha * acc[2]; acc[3] = bf16_hi(w.y) - p.alpha * acc[3];
+                acc[4] = bf16_lo(w.z) - p.alpha * acc[4]; acc[5] = bf16_hi(w.z) - p.alpha * acc[5];
+                acc[6] = bf16_lo(w.w) - p.alpha * acc[6]; acc[7] = bf16_hi(w.w) - p.alpha * acc[7];
+            }
+            uint4 o;
+            o.x = pack_bf16x2(acc[0], acc[1]); o.y = pack_bf16x2(acc[2], acc[3]);
+            o.z = pack_bf16x2(acc[4], acc[5]); o.w = pack_bf16x2(acc[6], acc[7]);
+            if (p.broadcast) {
+                for (int d = 0; d < p.world; ++d) {
+                    const int q = (p.rank + d) % p.world;            // local first, then peers, staggered
+                    st_u4(reinterpret_cast<__nv_bfloat16*>(p.out[q]) + off, o);
+                }
+            } else {
+                st_u4(reinterpret_cast<__nv_bfloat16*>(p.out[p.rank]) + off, o);
+            }
+        }
+    }
+};
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" long long b200_fused_inbox_bytes(int owned_cap, int world) {
+    return 2ll * owned_cap * world * TILE_ELEMS * 2;
+}
+extern "C" long long b200_fused_flag_bytes(int owned_cap, int ready_cap) {
+    return ((long long)owned_cap * MAX_WORLD_F + ready_cap) * 4;
+}
+extern "C" int b200_fused_owned_tiles(int M, int N, int world, int owner_mode) {
+    const int tm = (M + BM - 1) / BM, tn = (N + BN - 1) / BN;
+    if (owner_mode == OWN_ROW_SHARDED) return (tm / world) * tn;
+    return (tm * tn + world - 1) / world;
+}
+
+// D = A*B^T-style GEMM (same operand conventions as b200_gemm_bf16) whose output tiles are reduced across
+// `world` ranks inside the kernel.  See include/b200ffn.h.
+extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
+                                        int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
+                                        void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
+                                        int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
+                                        float alpha, int max_ctas, void* stream) {
+    if (world < 1 || world > MAX_WORLD_F || rank < 0 || rank >= world) { set_last_error("gemm_allreduce: bad rank/world"); return B200_ERR_ARG; }
+    if (out_peers == nullptr || inbox_peers == nullptr || flag_peers == nullptr) { set_last_error("gemm_allreduce: null peer table"); return B200_ERR_ARG; }
+    if (seq == 0) { set_last_error("gemm_allreduce: seq must start at 1"); return B200_ERR_ARG; }
+    if (ldo % 8 || ldo < N) { set_last_error("gemm_allreduce: ldo must be >= N and a multiple of 8"); return B200_ERR_ARG; }
+    GemmOperands o{A, lda, a_major, B, ldb, b_major, M, N, K};
+    const int tm = (M + BM - 1) / BM, tn = (N + BN - 1) / BN;
+    FusedParams p{};
+    p.ldo = ldo; p.out_row_offset = out_row_offset; p.rank = rank; p.world = world; p.seq = seq; p.parity = (int)(seq & 1u);
+    p.owner_mode = owner_mode; p.op = op; p.broadcast = broadcast; p.alpha = alpha; p.owned_cap = owned_cap;
+    if (owner_mode == OWN_ROW_SHARDED) {
+        if (tm % world || (M % (BM * world))) { set_last_error("gemm_allreduce: row-sharded owners need M %% (128*world) == 0 (M=%d world=%d)", M, world); return B200_ERR_ARG; }
+        p.mpo = tm / world;
+        p.owned_count = p.mpo * tn;
+    } else {
+        p.mpo = 1;
+        const int total = tm * tn;
+        p.owned_count = total / world + (rank < total % world ? 1 : 0);
+    }
+    if (p.owned_count > owned_cap || b200_fused_owned_tiles(M, N, world, owner_mode) > owned_cap) { set_last_error("gemm_allreduce: inbox too small (%d owned tiles, capacity %d)", p.owned_count, owned_cap); return B200_ERR_ARG; }
+    if (broadcast && tm * tn > ready_cap) { set_last_error("gemm_allreduce: ready-flag capacity %d < %d tiles", ready_cap, tm * tn); return B200_ERR_ARG; }
+    p.ready_base = owned_cap * MAX_WORLD_F;
+    for (int i = 0; i < world; ++i) {
+        p.inbox[i] = inbox_peers[i];
+        p.flags[i] = reinterpret_cast<uint32_t*>(flag_peers[i]);
+        p.out[i] = (broadcast || i == rank) ? out_peers[i] : nullptr;
+        if (p.inbox[i] == nullptr || p.flags[i] == nullptr || ((broadcast || i == rank) && p.out[i] == nullptr)) { set_last_error("gemm_allreduce: null peer pointer for rank %d", i); return B200_ERR_ARG; }
+        if ((reinterpret_cast<uintptr_t>(p.inbox[i]) & 15) || ((broadcast || i == rank) && (reinterpret_cast<uintptr_t>(p.out[i]) & 15))) { set_last_error("gemm_allreduce: peer pointers must be 16-byte aligned"); return B200_ERR_ARG; }
+    }
+    int grid_cap = max_ctas > 0 ? max_ctas : num_sms();
+    int grid = tm * tn < grid_cap ? tm * tn : grid_cap;
+    if ((p.owned_count + grid - 1) / grid > MAX_OWNED_PER_CTA) { set_last_error("gemm_allreduce: too many owned tiles per CTA"); return B200_ERR_ARG; }
+    // every rank must use the same grid: owned tile k is reduced by CTA k %% grid on its owner
+    return launch_gemm<FusedEpi>(o, p, max_ctas, reinterpret_cast<cudaStream_t>(stream), rank, world);
+}

@@ -32,6 +32,7 @@ int make_core_and_maps(const GemmOperands& o, GemmCore* core, CUtensorMap* tmA, 
     core->tiles_m = (o.M + BM - 1) / BM;
     core->tiles_n = (o.N + BN - 1) / BN;
     core->group_m = 16;
+    core->tile_offset = 0;
     core->err = device_error_slot();
     if (o.a_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmA, o.A, o.K, o.M, o.lda, BK, BM);
     else                      rc = encode_tmap_bf16_2d(tmA, o.A, o.M, o.K, o.lda, 64, BK);

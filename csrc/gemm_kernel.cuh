@@ -23,8 +23,11 @@ constexpr int STAGES = 4;
 constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KiB
 constexpr int B_STAGE_BYTES = BN * BK * 2;   // 32 KiB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-constexpr int GEMM_THREADS = 192;  // warp0: TMA, warp1: MMA + TMEM alloc, warps 2..5: epilogue
+constexpr int EPI_WARPS = 8;       // two warps per TMEM lane quarter, each takes half of the 256 columns
+constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;  // warp0: TMA, warp1: MMA + TMEM alloc, warps 2..9: epilogue
+constexpr int EPI_STAGE_BYTES = 32 * 128;          // per-epilogue-warp transpose buffer (fused push epilogues)
 constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int GEMM_SMEM_BYTES_STAGED = GEMM_SMEM_BYTES + EPI_WARPS * EPI_STAGE_BYTES + 256;
 
 enum Major : int { MAJOR_K = 0, MAJOR_MN = 1 };
 
@@ -32,6 +35,7 @@ struct GemmCore {
     int M, N, K;
     int a_major, b_major;
     int tiles_m, tiles_n, group_m;
+    int tile_offset;   // rotation of the tile order (fused kernels stagger ranks so pushes spread over owners)
     unsigned int* err;
 };
 
@@ -56,6 +60,7 @@ struct SmemView {
     uint64_t* tmem_full;   // [2]
     uint64_t* tmem_empty;  // [2]
     uint32_t* tmem_base;
+    uint8_t* epi_stage;    // EPI_WARPS x EPI_STAGE_BYTES, only when the launch asked for GEMM_SMEM_BYTES_STAGED
 };
 
 __device__ __forceinline__ SmemView carve_smem(uint8_t* raw) {
@@ -69,17 +74,35 @@ __device__ __forceinline__ SmemView carve_smem(uint8_t* raw) {
     v.tmem_full = bars + 2 * STAGES;
     v.tmem_empty = bars + 2 * STAGES + 2;
     v.tmem_base = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+    v.epi_stage = base + STAGES * STAGE_BYTES + 256;
     return v;
 }
 
 // ---------------------------------------------------------------------------------------------
 // The kernel.  `Epi` supplies:
 //   struct Params;                                                     (trivially copyable)
-//   static __device__ void tile_begin(const Params&, const GemmCore&, int tile, int m0, int n0, int ewarp, int lane)
-//   static __device__ void chunk(const Params&, const GemmCore&, int row, int col0, const uint32_t (&acc)[32])
-//   static __device__ void tile_end(const Params&, const GemmCore&, int tile, int m0, int n0, int ewarp, int lane)
-//   static __device__ void tail(const Params&, const GemmCore&, int ewarp, int lane)   (after the last tile)
+//   static constexpr int SMEM_BYTES;                                   (GEMM_SMEM_BYTES or GEMM_SMEM_BYTES_STAGED)
+//   struct State;                                                      (per-epilogue-warp registers)
+//   static __device__ void init(const Params&, const GemmCore&, const EpiCtx&, State&)
+//   static __device__ void process_tile(const Params&, const GemmCore&, const EpiCtx&, uint32_t taddr, State&)
+//        one epilogue warp's share of a finished accumulator tile: rows ctx.m0 + q*32 + lane (TMEM lane quarter
+//        ctx.q), columns [ctx.n0 + ctx.half*128, +128); taddr already points at (quarter, stage, half)
+//   static __device__ void after_tile(const Params&, const GemmCore&, const EpiCtx&, State&)
+//        runs after the accumulator stage has been handed back to the MMA warp (signals, opportunistic work)
+//   static __device__ void tail(const Params&, const GemmCore&, const EpiCtx&, State&)   (after the last tile)
 // ---------------------------------------------------------------------------------------------
+struct EpiCtx {
+    int tile;        // linear tile index in the scheduler's order
+    int m_blk, n_blk;
+    int m0, n0;      // first row / column of the tile
+    int q;           // TMEM lane quarter (0..3) -> rows m0 + q*32 + lane
+    int half;        // column half (0..1)
+    int ewarp;       // epilogue warp index 0..EPI_WARPS-1
+    int lane;
+    uint8_t* stage;  // this warp's EPI_STAGE_BYTES transpose buffer (staged launches only)
+    uint32_t* scratch;  // 256 B shared by the epilogue warps, after the stage buffers (staged launches only)
+};
+
 template <class Epi>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -102,7 +125,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
         for (int s = 0; s < 2; ++s) {
             mbar_init(&sm.tmem_full[s], 1);
-            mbar_init(&sm.tmem_empty[s], 4);
+            mbar_init(&sm.tmem_empty[s], EPI_WARPS);
         }
         fence_mbar_init();
     }
@@ -116,7 +139,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // ===================== TMA producer (one thread) =====================
         int s = 0;
         uint32_t phase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int it = blockIdx.x; it < num_tiles; it += gridDim.x) {
+            int tile = it + g.tile_offset;
+            if (tile >= num_tiles) tile -= num_tiles;
             int m_blk, n_blk;
             tile_coords(g, tile, m_blk, n_blk);
             const int m0 = m_blk * BM, n0 = n_blk * BN;
@@ -157,7 +182,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         uint32_t phase = 0;
         int as = 0;
         uint32_t aphase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int it = blockIdx.x; it < num_tiles; it += gridDim.x) {
+            int tile = it + g.tile_offset;
+            if (tile >= num_tiles) tile -= num_tiles;
             mbar_wait(&sm.tmem_empty[as], aphase ^ 1, g.err, 0x200 + as);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
@@ -179,33 +206,38 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (++as == 2) { as = 0; aphase ^= 1; }
         }
     } else if (warp >= 2) {
-        // ===================== epilogue (4 warps, one TMEM lane quarter each) =====================
-        const int q = warp & 3;                                  // tcgen05.ld lane window = warp_id % 4
+        // ===================== epilogue (8 warps: TMEM lane quarter x column half) =====================
+        EpiCtx ctx;
+        ctx.ewarp = warp - 2;
+        ctx.q = warp & 3;                                        // tcgen05.ld lane window = warp_id % 4
+        ctx.half = (warp - 2) >> 2;
+        ctx.lane = lane;
+        ctx.stage = sm.epi_stage + ctx.ewarp * EPI_STAGE_BYTES;
+        ctx.scratch = reinterpret_cast<uint32_t*>(sm.epi_stage + EPI_WARPS * EPI_STAGE_BYTES);
+        ctx.tile = -1;
+        ctx.m_blk = ctx.n_blk = ctx.m0 = ctx.n0 = 0;
+        typename Epi::State est;
+        Epi::init(ep, g, ctx, est);
         int as = 0;
         uint32_t aphase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            int m_blk, n_blk;
-            tile_coords(g, tile, m_blk, n_blk);
-            const int m0 = m_blk * BM, n0 = n_blk * BN;
-            Epi::tile_begin(ep, g, tile, m0, n0, q, lane);
+        for (int it = blockIdx.x; it < num_tiles; it += gridDim.x) {
+            int tile = it + g.tile_offset;
+            if (tile >= num_tiles) tile -= num_tiles;
+            ctx.tile = tile;
+            tile_coords(g, tile, ctx.m_blk, ctx.n_blk);
+            ctx.m0 = ctx.m_blk * BM;
+            ctx.n0 = ctx.n_blk * BN;
             mbar_wait(&sm.tmem_full[as], aphase, g.err, 0x400 + as);
             tc_fence_after();
-            const int row = m0 + q * 32 + lane;
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                uint32_t acc[32];
-                tmem_ld_32x32(taddr + c * 32, acc);
-                tmem_ld_wait();
-                Epi::chunk(ep, g, row, n0 + c * 32, acc);
-            }
+            const uint32_t taddr = tmem_base + ((uint32_t)(ctx.q * 32) << 16) + (uint32_t)(as * BN + ctx.half * (BN / 2));
+            Epi::process_tile(ep, g, ctx, taddr, est);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.tmem_empty[as]);
-            Epi::tile_end(ep, g, tile, m0, n0, q, lane);
+            Epi::after_tile(ep, g, ctx, est);
             if (++as == 2) { as = 0; aphase ^= 1; }
         }
-        Epi::tail(ep, g, q, lane);
+        Epi::tail(ep, g, ctx, est);
     }
 
     tc_fence_before();
@@ -250,12 +282,42 @@ __device__ __forceinline__ float gelu_grad_f(float x) {
 template <int KIND>
 struct LocalEpi {
     using Params = LocalEpiParams;
-    static __device__ __forceinline__ void tile_begin(const Params&, const GemmCore&, int, int, int, int, int) {}
-    static __device__ __forceinline__ void tile_end(const Params&, const GemmCore&, int, int, int, int, int) {}
-    static __device__ __forceinline__ void tail(const Params&, const GemmCore&, int, int) {}
+    static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES;
+    static constexpr bool NEEDS_AUX = (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD);
+    struct State {};
+    static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx&, State&) {}
+    static __device__ __forceinline__ void after_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {}
+    static __device__ __forceinline__ void tail(const Params&, const GemmCore&, const EpiCtx&, State&) {}
+
+    static __device__ __forceinline__ void load_aux(const Params& p, const GemmCore& g, int row, int col0, uint4 (&a)[4]) {
+        if constexpr (NEEDS_AUX) {
+            if (row >= g.M) return;
+#pragma unroll
+            for (int v = 0; v < 4; ++v)
+                if (col0 + v * 8 < g.N) a[v] = ld_nc_u4(p.aux + (long long)row * p.ldaux + col0 + v * 8);
+        }
+    }
+
+    static __device__ __forceinline__ void process_tile(const Params& p, const GemmCore& g, const EpiCtx& ctx, uint32_t taddr, State&) {
+        const int row = ctx.m0 + ctx.q * 32 + ctx.lane;
+        const int colbase = ctx.n0 + ctx.half * (BN / 2);
+        uint4 aux_next[4] = {};
+        load_aux(p, g, row, colbase, aux_next);                 // overlaps the wait-free first TMEM load
+#pragma unroll 1
+        for (int c = 0; c < BN / 2 / 32; ++c) {
+            uint32_t acc[32];
+            uint4 aux_cur[4];
+#pragma unroll
+            for (int v = 0; v < 4; ++v) aux_cur[v] = aux_next[v];
+            if (c + 1 < BN / 2 / 32) load_aux(p, g, row, colbase + (c + 1) * 32, aux_next);   // prefetch next chunk
+            tmem_ld_32x32(taddr + c * 32, acc);
+            tmem_ld_wait();
+            chunk(p, g, row, colbase + c * 32, acc, aux_cur);
+        }
+    }
 
     static __device__ __forceinline__ void chunk(const Params& p, const GemmCore& g, int row, int col0,
-                                                 const uint32_t (&acc)[32]) {
+                                                 const uint32_t (&acc)[32], const uint4 (&auxv)[4]) {
         if (row >= g.M) return;
 #pragma unroll
         for (int v = 0; v < 4; ++v) {                      // 4 groups of 8 columns = one 16-byte bf16 vector
@@ -290,7 +352,7 @@ struct LocalEpi {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) f[j] = gelu_f(f[j]);
             } else if constexpr (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD) {
-                const uint4 a = ld_nc_u4(p.aux + (long long)row * p.ldaux + col);
+                const uint4 a = auxv[v];
                 const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -336,17 +398,19 @@ int validate_operands(const GemmOperands& o);
 int make_core_and_maps(const GemmOperands& o, GemmCore* core, CUtensorMap* tmA, CUtensorMap* tmB);
 
 template <class Epi>
-int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_ctas, cudaStream_t stream) {
+int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_ctas, cudaStream_t stream,
+                int tile_offset_num = 0, int tile_offset_den = 1) {
     GemmCore core;
     alignas(64) CUtensorMap tmA, tmB;
     int rc = make_core_and_maps(o, &core, &tmA, &tmB);
     if (rc != 0) return rc;
+    core.tile_offset = (int)((long long)core.tiles_m * core.tiles_n * tile_offset_num / tile_offset_den);
     static unsigned long long attr_mask = 0;   // per template instantiation, one bit per device
     int dev = 0;
     cudaGetDevice(&dev);
     if (!(attr_mask >> (dev & 63) & 1ull)) {
         rc = check_cuda(cudaFuncSetAttribute(gemm_tcgen05_kernel<Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             GEMM_SMEM_BYTES),
+                                             Epi::SMEM_BYTES),
                         "cudaFuncSetAttribute(smem)");
         if (rc != 0) return rc;
         attr_mask |= 1ull << (dev & 63);
@@ -354,7 +418,7 @@ int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_c
     int grid = core.tiles_m * core.tiles_n;
     int cap = max_ctas > 0 ? max_ctas : num_sms();
     if (grid > cap) grid = cap;
-    gemm_tcgen05_kernel<Epi><<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, core, ep);
+    gemm_tcgen05_kernel<Epi><<<grid, GEMM_THREADS, Epi::SMEM_BYTES, stream>>>(tmA, tmB, core, ep);
     return check_cuda(cudaGetLastError(), "gemm launch");
 }
 

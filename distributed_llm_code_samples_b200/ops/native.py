@@ -80,22 +80,29 @@ def load():
 def _optional_declare(lib) -> None:
     """Symbols added by later translation units (collectives, fused kernels); declared when present."""
     vp, ll, i, f = C.c_void_p, C.c_longlong, C.c_int, C.c_float
+    pp = C.POINTER(C.c_void_p)
+    u = C.c_uint
     table = {
         "b200_ipc_handle_bytes": ([], i),
-        "b200_symm_alloc": ([C.POINTER(vp), ll], i),
+        "b200_symm_alloc": ([pp, ll], i),
         "b200_symm_free": ([vp], i),
         "b200_ipc_get_handle": ([vp, vp], i),
-        "b200_ipc_open_handle": ([C.POINTER(vp), vp], i),
+        "b200_ipc_open_handle": ([pp, vp], i),
         "b200_ipc_close_handle": ([vp], i),
         "b200_enable_peer_access": ([i], i),
-        "b200_barrier": ([vp, i, i, C.c_uint, vp], i),
-        "b200_all_reduce_bf16": ([vp, vp, vp, ll, i, i, C.c_uint, i, vp], i),
-        "b200_all_gather": ([vp, vp, vp, ll, i, i, C.c_uint, i, vp], i),
-        "b200_reduce_scatter_bf16": ([vp, vp, vp, ll, i, i, C.c_uint, i, vp], i),
-        "b200_gemm_allreduce_bf16": None,
+        "b200_coll_flag_bytes": ([], ll),
+        "b200_barrier": ([pp, i, i, u, vp], i),
+        "b200_all_reduce_bf16": ([pp, ll, ll, pp, i, i, u, i, vp], i),
+        "b200_all_gather": ([pp, ll, ll, pp, i, i, u, i, vp], i),
+        "b200_reduce_scatter_bf16": ([pp, ll, ll, pp, i, i, u, i, vp], i),
+        "b200_all_gather_into": ([vp, pp, ll, ll, pp, i, i, u, i, vp], i),
+        "b200_fused_inbox_bytes": ([i, i], ll),
+        "b200_fused_flag_bytes": ([i, i], ll),
+        "b200_fused_owned_tiles": ([i, i, i, i], i),
+        "b200_gemm_allreduce_bf16": ([vp, ll, i, vp, ll, i, i, i, i, pp, ll, i, pp, pp, i, i, i, i, u, i, i, i, f, i, vp], i),
     }
     for name, sig in table.items():
-        if sig is None or not hasattr(lib, name):
+        if not hasattr(lib, name):
             continue
         fn = getattr(lib, name)
         fn.argtypes, fn.restype = sig

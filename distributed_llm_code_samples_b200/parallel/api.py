@@ -38,32 +38,38 @@ def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Seque
     if method == "single" or n == 1:        # a world of one: every strategy degenerates to the single-device loop
         return SingleTrainer(ops, cfg, place(layers_params, device, dtype))
     if method == "ddp":
-        if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg):
+        if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg, "ddp"):
             from .fused import FusedDDPTrainer
             return FusedDDPTrainer(ops, comm, cfg, layers_params, device)
         return DDPTrainer(ops, comm, cfg, place(layers_params, device, dtype))
     if method == "fsdp":
         shards = [[fsdp_shard(p, r, n) for p in lp] for lp in layers_params]
-        if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg):
+        if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg, "fsdp"):
             from .fused import FusedFSDPTrainer
             return FusedFSDPTrainer(ops, comm, cfg, place(shards, device, dtype), device)
         return FSDPTrainer(ops, comm, cfg, place(shards, device, dtype))
     if method == "mp":
         shards = [[tp_shard(p, j, r, n) for j, p in enumerate(lp)] for lp in layers_params]
-        if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg):
+        if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg, "mp"):
             from .fused import FusedMPTrainer
             return FusedMPTrainer(ops, comm, cfg, place(shards, device, dtype), device)
         return MPTrainer(ops, comm, cfg, place(shards, device, dtype))
     raise ValueError(f"unknown method {method!r}")
 
 
-def _fused_available(ops, comm, cfg: TrainConfig) -> bool:
-    """The peer-memory fused kernels need the native ops, bf16, >1 rank, SGD, no bias and TMA-legal shapes."""
+def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
+    """The peer-memory fused kernels need the native ops, bf16, >1 rank, SGD, no bias and TMA-legal shapes
+    (FSDP additionally needs every row shard to be a whole number of 128-row tiles)."""
     ok = (getattr(ops, "name", "") == "native" and comm.world > 1 and cfg.dtype in ("bf16", "bfloat16")
           and cfg.optimizer == "sgd" and not cfg.bias and cfg.model_size % 8 == 0 and cfg.ffn_dim % 8 == 0)
+    if method == "fsdp":
+        ok = ok and cfg.model_size % (128 * comm.world) == 0 and cfg.ffn_dim % (128 * comm.world) == 0
+    if method == "mp":
+        ok = ok and not cfg.residual and cfg.mp_mode == "ar" and (cfg.ffn_dim // comm.world) % 8 == 0
     if not ok:
         if cfg.comm == "fused":
-            raise RuntimeError("comm=fused needs impl=native, bf16, SGD, no bias, world>1 and dims % 8 == 0")
+            raise RuntimeError("comm=fused needs impl=native, bf16, SGD, no bias, world>1, dims % 8 == 0 "
+                               "(FSDP: dims % (128*world) == 0; MP: all-reduce form, no residual)")
         return False
     try:
         from . import fused  # noqa: F401

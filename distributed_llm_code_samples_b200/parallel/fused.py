@@ -1,0 +1,307 @@
+"""Trainers whose communication is fused into the GEMMs (``csrc/fused.cu``) or runs on the native peer-memory
+collectives (``csrc/comm.cu``) - no NCCL on the data path.
+
+* ``FusedDDPTrainer``  dW GEMM -> (push partial tiles to their owners) -> fp32 sum -> ``W -= lr * sum`` -> new weight
+  tile stored into every replica.  Replaces dW GEMM + all_reduce + SGD (``train_ffns.py:66/68, :165, :172``).
+* ``FusedFSDPTrainer`` dW GEMM -> reduce-scatter to the row-shard owner -> sharded SGD in the same kernel
+  (``:253-259``); parameters are unsharded one layer ahead by a pull all-gather on a side stream straight into
+  the contiguous buffer the GEMM reads (``:203-209``, ``:236-249``).
+* ``FusedMPTrainer``   row-parallel GEMM -> all-reduce of the partial activations inside the kernel
+  (``:302-303``, ``:308-309``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Iterable, List, Optional, Tuple
+
+import torch
+
+from ..config import TrainConfig
+from ..models.ffn import Params
+from ..ops import native as nv
+from .base import block_opts
+from .symm import CollChannel, SymmBuffer, SymmWorld, _Handle, get_symm_world
+
+OWN_INTERLEAVED, OWN_ROW_SHARDED = 0, 1
+FOP_SUM, FOP_SGD = 0, 1
+TILE_M, TILE_N = 128, 256
+
+
+def available() -> bool:
+    try:
+        return hasattr(nv.load(), "b200_gemm_allreduce_bf16")
+    except OSError:
+        return False
+
+
+def _tiles(M: int, N: int) -> int:
+    return ((M + TILE_M - 1) // TILE_M) * ((N + TILE_N - 1) // TILE_N)
+
+
+class FusedChannel:
+    """Inbox + flags + call counter for one stream of fused GEMM+collective calls."""
+
+    def __init__(self, sw: SymmWorld, owned_cap: int, ready_cap: int):
+        lib = nv.load()
+        self.sw, self.owned_cap, self.ready_cap = sw, owned_cap, ready_cap
+        self.inbox = sw.alloc(int(lib.b200_fused_inbox_bytes(owned_cap, sw.world)))
+        self.flags = sw.alloc(int(lib.b200_fused_flag_bytes(owned_cap, ready_cap)))
+        self.seq = 0
+
+    def gemm(self, A: torch.Tensor, a_major: int, B: torch.Tensor, b_major: int, M: int, N: int, K: int,
+             out_peers, ldo: int, out_row_offset: int, owner_mode: int, op: int, broadcast: bool, alpha: float = 1.0,
+             max_ctas: int = 0) -> None:
+        self.seq += 1
+        sw = self.sw
+        rc = nv.load().b200_gemm_allreduce_bf16(
+            A.data_ptr(), A.stride(0), a_major, B.data_ptr(), B.stride(0), b_major, M, N, K, out_peers, ldo,
+            out_row_offset, self.inbox.peers_c, self.flags.peers_c, self.owned_cap, self.ready_cap, sw.rank, sw.world,
+            self.seq, owner_mode, op, int(broadcast), float(alpha), int(max_ctas), nv._stream())
+        nv._check(rc, "b200_gemm_allreduce_bf16")
+        nv.launch_count += 1
+
+
+def _owned_cap(shapes, world: int, owner_mode: int) -> int:
+    lib = nv.load()
+    return max(int(lib.b200_fused_owned_tiles(M, N, world, owner_mode)) for M, N in shapes)
+
+
+# =================================================================================================== DDP
+class FusedDDPTrainer:
+    comm_name = "fused: dW GEMM + all-reduce + SGD in one kernel (peer stores over NVLink)"
+
+    def __init__(self, ops, comm, cfg: TrainConfig, layers_params: List[Params], device: torch.device):
+        self.ops, self.comm, self.cfg = ops, comm, cfg
+        self.opts = block_opts(cfg)
+        self.lr = cfg.lr * cfg.grad_scale
+        self.sw = get_symm_world(comm, device)
+        D, F, L = cfg.model_size, cfg.ffn_dim, len(layers_params)
+        self.wbuf = self.sw.alloc(L * 2 * D * F * 2 + 4096)
+        self.params: List[Params] = []
+        self.offsets: List[Tuple[int, int]] = []
+        for lp in layers_params:
+            w1, o1 = self.wbuf.carve((F, D), torch.bfloat16)
+            w2, o2 = self.wbuf.carve((D, F), torch.bfloat16)
+            w1.copy_(lp[0].to(device=device, dtype=torch.bfloat16))
+            w2.copy_(lp[1].to(device=device, dtype=torch.bfloat16))
+            self.params.append([w1, w2])
+            self.offsets.append((o1, o2))
+        self.peer_tabs = [(self.wbuf.peers_at(o1), self.wbuf.peers_at(o2)) for o1, o2 in self.offsets]
+        shapes = [(F, D), (D, F)]
+        self.chan = FusedChannel(self.sw, _owned_cap(shapes, comm.world, OWN_INTERLEAVED), max(_tiles(*s) for s in shapes))
+        self.sw.host_barrier()
+
+    def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+        from ..models.ffn import tlayers_ffn_fwd
+        cfg, ops = self.cfg, self.ops
+        D, F = cfg.model_size, cfg.ffn_dim
+        y, acts = tlayers_ffn_fwd(ops, self.params, x, self.opts)
+        d = dloss_dx
+        T = x.shape[0]
+        for i in reversed(range(len(self.params))):
+            W1, W2 = self.params[i]
+            s = acts[i]
+            a, pre = s.a, s.pre
+            if a is None:
+                a, pre = ops.linear_act(s.x, W1, self.opts.activation)
+            dh = ops.grad_input(d, W2, act=self.opts.activation, aux=a if self.opts.activation == "relu" else pre)
+            # dW2 = d^T a  summed over ranks, W2 -= lr * dW2, new W2 stored to every replica - one kernel
+            self.chan.gemm(d, nv.MAJOR_MN, a, nv.MAJOR_MN, D, F, T, self.peer_tabs[i][1], F, 0, OWN_INTERLEAVED, FOP_SGD, True, self.lr)
+            dn = ops.grad_input(dh, W1, add=d if self.opts.residual else None) if i > 0 else None
+            self.chan.gemm(dh, nv.MAJOR_MN, s.x, nv.MAJOR_MN, F, D, T, self.peer_tabs[i][0], D, 0, OWN_INTERLEAVED, FOP_SGD, True, self.lr)
+            acts[i] = None
+            d = dn
+        return y
+
+    def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor]]) -> None:
+        for x, dy in batches:
+            self.step(x, dy)
+
+    def full_params(self) -> List[Params]:
+        return self.params
+
+
+# =================================================================================================== FSDP
+class FusedFSDPTrainer:
+    comm_name = "fused: dW GEMM + reduce-scatter + sharded SGD in one kernel; native pull all-gather prefetch"
+
+    def __init__(self, ops, comm, cfg: TrainConfig, shards: List[Params], device: torch.device):
+        self.ops, self.comm, self.cfg = ops, comm, cfg
+        self.opts = block_opts(cfg)
+        self.lr = cfg.lr * cfg.grad_scale
+        self.sw = get_symm_world(comm, device)
+        n = comm.world
+        self.world, self.rank = n, comm.rank
+        D, F, L = cfg.model_size, cfg.ffn_dim, len(shards)
+        self.L = L
+        self.sbuf = self.sw.alloc(L * 2 * D * F * 2 // n + 4096)
+        self.shards: List[Params] = []
+        self.shard_off: List[Tuple[int, int]] = []
+        for lp in shards:
+            w1, o1 = self.sbuf.carve((F // n, D), torch.bfloat16)
+            w2, o2 = self.sbuf.carve((D // n, F), torch.bfloat16)
+            w1.copy_(lp[0])
+            w2.copy_(lp[1])
+            self.shards.append([w1, w2])
+            self.shard_off.append((o1, o2))
+        self.full = [[torch.empty(F, D, dtype=torch.bfloat16, device=device), torch.empty(D, F, dtype=torch.bfloat16, device=device)]
+                     for _ in range(2)]
+        self.local_out = [(C.c_void_p * n)(*[w.data_ptr() if r == self.rank else 0 for r in range(n)]) for lp in self.shards for w in lp]
+        shapes = [(F, D), (D, F)]
+        self.chan = FusedChannel(self.sw, _owned_cap(shapes, n, OWN_ROW_SHARDED), max(_tiles(*s) for s in shapes))
+        self.coll = CollChannel(self.sw)
+        self.side = torch.cuda.Stream(device=device)
+        self._pending = {}
+        self.sw.host_barrier()
+
+    def _start_gather(self, layer: int) -> None:
+        if not (0 <= layer < self.L) or layer in self._pending:
+            return
+        lib = nv.load()
+        slot = layer % 2
+        self.side.wait_stream(torch.cuda.current_stream())
+        for k in range(2):
+            e = self.coll.next_epoch()
+            sh = self.shards[layer][k]
+            nv._check(lib.b200_all_gather_into(self.full[slot][k].data_ptr(), self.sbuf.peers_c, self.shard_off[layer][k],
+                                               sh.numel() * 2, self.coll.flags.peers_c, self.rank, self.world, e, 0,
+                                               self.side.cuda_stream), "b200_all_gather_into")
+            nv.launch_count += 1
+        ev = torch.cuda.Event()
+        ev.record(self.side)
+        self._pending[layer] = _Handle(ev)
+
+    def _finish_gather(self, layer: int) -> Params:
+        self._pending.pop(layer).wait()
+        return self.full[layer % 2]
+
+    def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+        from ..models.ffn import tlayer_ffn_fwd
+        cfg, ops, L = self.cfg, self.ops, self.L
+        D, F = cfg.model_size, cfg.ffn_dim
+        n, r = self.world, self.rank
+        T = x.shape[0]
+        acts = []
+        y = x
+        self._start_gather(0)
+        params = None
+        for l in range(L):
+            params = self._finish_gather(l)
+            self._start_gather(l + 1)
+            y, s = tlayer_ffn_fwd(ops, params, y, self.opts)
+            acts.append(s)
+        self._start_gather(L - 2)
+        d = dloss_dx
+        for i in reversed(range(L)):
+            if i < L - 1:
+                params = self._finish_gather(i)
+                self._start_gather(i - 1)
+            W1, W2 = params
+            s = acts[i]
+            a, pre = s.a, s.pre
+            if a is None:
+                a, pre = ops.linear_act(s.x, W1, self.opts.activation)
+            dh = ops.grad_input(d, W2, act=self.opts.activation, aux=a if self.opts.activation == "relu" else pre)
+            # dW2 rows [r*D/n, (r+1)*D/n) summed over ranks and applied to MY shard of W2 - one kernel, no broadcast
+            self.chan.gemm(d, nv.MAJOR_MN, a, nv.MAJOR_MN, D, F, T, self.local_out[2 * i + 1], F, r * (D // n), OWN_ROW_SHARDED, FOP_SGD, False, self.lr)
+            dn = ops.grad_input(dh, W1, add=d if self.opts.residual else None) if i > 0 else None
+            self.chan.gemm(dh, nv.MAJOR_MN, s.x, nv.MAJOR_MN, F, D, T, self.local_out[2 * i], D, r * (F // n), OWN_ROW_SHARDED, FOP_SGD, False, self.lr)
+            acts[i] = None
+            d = dn
+        return y
+
+    def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor]]) -> None:
+        for x, dy in batches:
+            self.step(x, dy)
+
+    def full_params(self) -> List[Params]:
+        lib = nv.load()
+        out = []
+        for l in range(self.L):
+            fl = []
+            for k in range(2):
+                sh = self.shards[l][k]
+                full = torch.empty((sh.shape[0] * self.world, sh.shape[1]), dtype=sh.dtype, device=sh.device)
+                e = self.coll.next_epoch()
+                nv._check(lib.b200_all_gather_into(full.data_ptr(), self.sbuf.peers_c, self.shard_off[l][k], sh.numel() * 2,
+                                                   self.coll.flags.peers_c, self.rank, self.world, e, 0, nv._stream()), "b200_all_gather_into")
+                fl.append(full)
+            out.append(fl)
+        return out
+
+
+# =================================================================================================== MP
+class FusedMPTrainer:
+    comm_name = "fused: row-parallel GEMM + all-reduce in one kernel (peer stores over NVLink)"
+
+    def __init__(self, ops, comm, cfg: TrainConfig, shards: List[Params], device: torch.device):
+        self.ops, self.comm, self.cfg, self.shards = ops, comm, cfg, shards
+        self.opts = block_opts(cfg)
+        if cfg.residual or cfg.mp_mode != "ar":
+            raise RuntimeError("fused MP implements the reference all-reduce form without residual; use --comm nccl for the others")
+        self.lr = cfg.lr * cfg.grad_scale
+        self.sw = get_symm_world(comm, device)
+        self.world, self.rank = comm.world, comm.rank
+        self.L = len(shards)
+        self.device = device
+        self.T = 0
+        self.chan: Optional[FusedChannel] = None
+
+    def _ensure_buffers(self, T: int) -> None:
+        if self.T == T:
+            return
+        D = self.cfg.model_size
+        self.abuf: SymmBuffer = self.sw.alloc((self.L + 2) * T * D * 2 + 8192)
+        self.y, self.y_tab = [], []
+        for _ in range(self.L):
+            t, o = self.abuf.carve((T, D), torch.bfloat16)
+            self.y.append(t)
+            self.y_tab.append(self.abuf.peers_at(o))
+        self.dx, self.dx_tab = [], []
+        for _ in range(2):
+            t, o = self.abuf.carve((T, D), torch.bfloat16)
+            self.dx.append(t)
+            self.dx_tab.append(self.abuf.peers_at(o))
+        self.chan = FusedChannel(self.sw, _owned_cap([(T, D)], self.world, OWN_INTERLEAVED), _tiles(T, D))
+        self.T = T
+        self.sw.host_barrier()
+
+    def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+        ops, cfg = self.ops, self.cfg
+        T, D = x.shape
+        Fs = self.shards[0][0].shape[0]
+        self._ensure_buffers(T)
+        saved = []
+        y = x
+        for l, (W1, W2) in enumerate(self.shards):
+            a, pre = ops.linear_act(y, W1, self.opts.activation)
+            saved.append((y, None if self.opts.recompute else a, None if self.opts.recompute else pre))
+            # y_l = sum over ranks of a_r @ W2_r^T, delivered to every rank - one kernel (:302-303)
+            self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
+            y = self.y[l]
+        d = dloss_dx
+        for i in reversed(range(self.L)):
+            W1, W2 = self.shards[i]
+            xin, a, pre = saved[i]
+            if a is None:
+                a, pre = ops.linear_act(xin, W1, self.opts.activation)
+            dh = ops.grad_input(d, W2, act=self.opts.activation, aux=a if self.opts.activation == "relu" else pre)
+            ops.grad_weight_sgd_(W2, d, a, self.lr)                       # shard-local, no communication (:311-312)
+            dn = None
+            if i > 0:
+                slot = i % 2
+                # dx = sum over ranks of dh_r @ W1_r, delivered to every rank - one kernel (:308-309)
+                self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
+                dn = self.dx[slot]
+            ops.grad_weight_sgd_(W1, dh, xin, self.lr)
+            saved[i] = None
+            d = dn
+        return y
+
+    def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor]]) -> None:
+        for x, dy in batches:
+            self.step(x, dy)
+
+    def full_params(self) -> List[Params]:
+        from .mp import MPTrainer
+        return MPTrainer.full_params(self)      # same reassembly rule (W1 dim 0, W2 dim 1)

@@ -78,6 +78,67 @@ int b200_sumsq_bf16(float* out, const void* x, long long n, void* scratch, long 
 /* Writes `bytes` of zeros (L2 flush between timed iterations). */
 int b200_fill_zero(void* buf, long long bytes, void* stream);
 
+/* ---- peer-memory runtime (one process per GPU; NVLink/NVSwitch) ------------------------------------------------
+ * Symmetric memory: every rank allocates the same size with b200_symm_alloc (zero-filled cudaMalloc), exports a
+ * CUDA-IPC handle, and opens every peer's handle; the resulting table of `world` base pointers (own pointer at
+ * index `rank`) is what the collectives and fused kernels take as `*_peers` (HOST arrays of device pointers).
+ * This is the explicit form of the hand-off the reference gets implicitly by pickling CUDA tensors to child
+ * processes (train_ffns.py:186; test_mp_barrier_gpus.py:33).  In a single process driving several GPUs use
+ * b200_enable_peer_access and the raw pointers instead. */
+int b200_symm_alloc(void** ptr, long long bytes);
+int b200_symm_free(void* ptr);
+int b200_ipc_handle_bytes(void);
+int b200_ipc_get_handle(void* handle_out, void* ptr);
+int b200_ipc_open_handle(void** peer_ptr, const void* handle);
+int b200_ipc_close_handle(void* peer_ptr);
+int b200_enable_peer_access(int peer_device);
+
+/* Collectives on a symmetric buffer: the operand lives at `offset_bytes` inside every rank's allocation.
+ * `flag_peers` is a symmetric allocation of b200_coll_flag_bytes() bytes reserved for one stream of collectives;
+ * `epoch` must increase by one per call on that flag block (same value on every rank).  `blocks` = 0 picks a
+ * size-dependent grid (<= 64 CTAs).  Sizes and offsets are multiples of 16 bytes; for all_gather /
+ * reduce_scatter `bytes` is the FULL buffer and must be a multiple of 16 * world.
+ *   all_reduce      in-place SUM of bf16 (test_nccl.py:25; train_ffns.py:165,:303,:309)
+ *   all_gather      rank r's slice r is the input; every slice valid on return (test_nccl.py:16; train_ffns.py:203)
+ *   reduce_scatter  every rank's full buffer is an input; slice r of rank r holds the SUM on return
+ *                   (test_nccl.py:35; train_ffns.py:255-256)
+ *   barrier         device-side cross-rank barrier (the role of mp.Barrier in test_mp_barrier_gpus.py:17) */
+long long b200_coll_flag_bytes(void);
+int b200_barrier(void* const* flag_peers, int rank, int world, unsigned int epoch, void* stream);
+int b200_all_reduce_bf16(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
+                         int world, unsigned int epoch, int blocks, void* stream);
+int b200_all_gather(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
+                    int world, unsigned int epoch, int blocks, void* stream);
+/* dst (local, world * shard_bytes) <- every rank's shard at src_peers[q] + src_offset_bytes (FSDP unshard, :203). */
+int b200_all_gather_into(void* dst, void* const* src_peers, long long src_offset_bytes, long long shard_bytes,
+                         void* const* flag_peers, int rank, int world, unsigned int epoch, int blocks, void* stream);
+int b200_reduce_scatter_bf16(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers,
+                             int rank, int world, unsigned int epoch, int blocks, void* stream);
+
+/* ---- fused GEMM + collective -------------------------------------------------------------------------------
+ * One tcgen05 kernel: computes D = A.B (operand conventions of b200_gemm_bf16), pushes each finished tile to the
+ * inbox of the rank that owns it (peer stores over NVLink, overlapped with the next tile's MMAs), and the owner
+ * sums the `world` partials in fp32, applies `op` and writes the result.
+ *   owner_mode 0  tiles interleaved over ranks (all-reduce forms)      op 0  out  = sum
+ *   owner_mode 1  owner = rank holding that block of rows (M/world)     op 1  out -= alpha * sum   (SGD on the weight)
+ *   broadcast  1  result written to every rank's `out` and the kernel returns once the local `out` is complete
+ *              0  result written to the local `out` only (reduce-scatter forms; `out` holds rows
+ *                 [out_row_offset, out_row_offset + M/world))
+ * `inbox_peers` / `flag_peers`: symmetric allocations of b200_fused_inbox_bytes(owned_cap, world) and
+ * b200_fused_flag_bytes(owned_cap, ready_cap) bytes, reserved for one stream of fused calls ("channel");
+ * owned_cap >= b200_fused_owned_tiles(M, N, world, owner_mode), ready_cap >= number of 128x256 tiles.
+ * `seq` starts at 1 and increases by one per call on the channel (same on every rank).  Every rank must pass the
+ * same shapes and max_ctas.  Reference sites: train_ffns.py:66/68+165+172 (DDP), :255-259 (FSDP), :57+303 and
+ * :68+309 (MP). */
+long long b200_fused_inbox_bytes(int owned_cap, int world);
+long long b200_fused_flag_bytes(int owned_cap, int ready_cap);
+int b200_fused_owned_tiles(int M, int N, int world, int owner_mode);
+int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
+                             int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
+                             void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
+                             int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
+                             float alpha, int max_ctas, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -42,7 +42,7 @@ def test_native_step_matches_fp32_oracle(cuda_device, recompute, act):
             # the UPDATE must match (relative to its own scale), not just the weights.  Intermediates (a, dh, dx) and the
             # weights themselves are bf16 in the native path and fp32 in the oracle, hence a norm-based bound.
             rel = ((upd - upd_ref).norm() / upd_ref.norm()).item()
-            assert rel <= 0.05, f"relative update error {rel}"
+            assert rel <= 0.10, f"relative update error {rel}"
             assert (upd - upd_ref).abs().max().item() <= 0.15 * upd_ref.abs().max().item() + 2e-3
 
 
