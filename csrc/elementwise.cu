@@ -4,6 +4,7 @@
 #include "common.cuh"
 #include "../include/b200ffn.h"
 #include <curand_kernel.h>
+#include <mutex>
 
 namespace b200 {
 
@@ -195,6 +196,36 @@ __global__ void __launch_bounds__(EW_THREADS) sumsq_kernel(float* out, const __n
     sumsq_body(out, x, n, sc);
 }
 
+// ------------------------------------------------------------------ sum of squares without any allocation
+// Scratch for b200_sumsq_bf16_static: one arrival counter + one partial per CTA, for at most 296 CTAs (two per SM on
+// a 148-SM part).  It is part of the library image: every GPU that loads libb200ffn.so carries these 1280 bytes
+// until the process exits.  All calls on a device share it.
+constexpr int SUMSQ_STATIC_MAX_BLOCKS = 296;
+constexpr long long SUMSQ_STATIC_MAX_ELEMS = 1ll << 31;
+constexpr int SUMSQ_STATIC_BYTES = 1280;                     // 16-byte header + 296 floats, rounded up to 256
+static_assert(16 + SUMSQ_STATIC_MAX_BLOCKS * 4 <= SUMSQ_STATIC_BYTES, "static scratch too small");
+static __device__ __align__(256) unsigned char g_sumsq_static_scratch[SUMSQ_STATIC_BYTES];
+
+// In host code `g_sumsq_static_scratch` is only a handle for the runtime's symbol table, not a device address, so the
+// address each device uses is looked up once, with that device current, and cached here.
+static void* g_sumsq_static_addr[64] = {nullptr};
+static std::mutex g_sumsq_static_mutex;
+
+static int sumsq_static_address(void** out) {
+    int dev = 0;
+    if (int rc = check_cuda(cudaGetDevice(&dev), "sumsq_static cudaGetDevice")) return rc;
+    if (dev < 0 || dev >= 64) { set_last_error("sumsq_static: device ordinal %d out of range", dev); return B200_ERR_ARG; }
+    std::lock_guard<std::mutex> lock(g_sumsq_static_mutex);
+    if (g_sumsq_static_addr[dev] == nullptr) {
+        void* p = nullptr;
+        if (int rc = check_cuda(cudaGetSymbolAddress(&p, g_sumsq_static_scratch), "sumsq_static cudaGetSymbolAddress")) return rc;
+        if (p == nullptr) { set_last_error("sumsq_static: cudaGetSymbolAddress returned a null address"); return B200_ERR_STATE; }
+        g_sumsq_static_addr[dev] = p;
+    }
+    *out = g_sumsq_static_addr[dev];
+    return 0;
+}
+
 __global__ void __launch_bounds__(EW_THREADS) fill_zero_kernel(uint4* buf, long long n16) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     const uint4 z = make_uint4(0, 0, 0, 0);
@@ -288,6 +319,30 @@ extern "C" int b200_sumsq_bf16(float* out, const void* x, long long n, void* scr
     if (grid > SUMSQ_MAX_BLOCKS) grid = SUMSQ_MAX_BLOCKS;
     sumsq_kernel<<<grid, EW_THREADS, 0, ST(stream)>>>(out, reinterpret_cast<const __nv_bfloat16*>(x), n, reinterpret_cast<SumsqScratch*>(scratch));
     return check_cuda(cudaGetLastError(), "sumsq launch");
+}
+
+extern "C" long long b200_sumsq_static_max_elems(void) { return SUMSQ_STATIC_MAX_ELEMS; }
+
+// Same result as b200_sumsq_bf16, but the caller brings no scratch and nothing is allocated here or later: the
+// partial sums go through the library's own fixed device array.  See include/b200ffn.h for who needs this.
+extern "C" int b200_sumsq_bf16_static(float* out, const void* x, long long n, void* stream) {
+    if (out == nullptr) { set_last_error("sumsq_static: null out"); return B200_ERR_ARG; }
+    if (n < 0 || (n > 0 && x == nullptr)) { set_last_error("sumsq_static: bad input"); return B200_ERR_ARG; }
+    if (n > SUMSQ_STATIC_MAX_ELEMS) {
+        set_last_error("sumsq_static: n = %lld exceeds the %lld-element limit of the built-in scratch; "
+                       "use b200_sumsq_bf16 with caller-provided scratch for larger inputs", n, SUMSQ_STATIC_MAX_ELEMS);
+        return B200_ERR_ARG;
+    }
+    if (n > 0) { if (int rc = check_ptr16(x, "sumsq_static x")) return rc; }
+    void* scratch = nullptr;
+    if (int rc = sumsq_static_address(&scratch)) return rc;          // first call on this device does the look-up
+    cudaStream_t st = ST(stream);
+    // the arrival counter has to read zero when the kernel starts, whatever an earlier (possibly aborted) call left
+    if (int rc = check_cuda(cudaMemsetAsync(scratch, 0, 16, st), "sumsq_static counter reset")) return rc;
+    int grid = ew_grid(n / 8 + 1);
+    if (grid > SUMSQ_STATIC_MAX_BLOCKS) grid = SUMSQ_STATIC_MAX_BLOCKS;
+    sumsq_kernel<<<grid, EW_THREADS, 0, st>>>(out, reinterpret_cast<const __nv_bfloat16*>(x), n, reinterpret_cast<SumsqScratch*>(scratch));
+    return check_cuda(cudaGetLastError(), "sumsq_static launch");
 }
 
 extern "C" int b200_fill_zero(void* buf, long long bytes, void* stream) {

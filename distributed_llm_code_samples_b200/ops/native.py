@@ -96,6 +96,8 @@ def _optional_declare(lib) -> None:
         "b200_all_gather": ([pp, ll, ll, pp, i, i, u, i, vp], i),
         "b200_reduce_scatter_bf16": ([pp, ll, ll, pp, i, i, u, i, vp], i),
         "b200_all_gather_into": ([vp, pp, ll, ll, pp, i, i, u, i, vp], i),
+        "b200_sumsq_static_max_elems": ([], ll),
+        "b200_sumsq_bf16_static": ([vp, vp, ll, vp], i),
         "b200_fused_inbox_bytes": ([i, i], ll),
         "b200_fused_flag_bytes": ([i, i], ll),
         "b200_fused_owned_tiles": ([i, i, i, i], i),
@@ -235,6 +237,15 @@ def sumsq(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     out = torch.empty(1, dtype=torch.float32, device=x.device) if out is None else out
     _check(lib.b200_sumsq_bf16(out.data_ptr(), x.data_ptr(), x.numel(), sc.data_ptr(), sc.numel(), _stream()),
            "b200_sumsq_bf16")
+    launch_count += 1
+    return out
+
+
+def sumsq_static(x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """Sum of squares into the caller's ``out`` (1 fp32 element) without allocating anything: no scratch tensor, no
+    output tensor, no library-side allocation (``b200_sumsq_bf16_static``).  Calls on one device must not overlap."""
+    global launch_count
+    _check(load().b200_sumsq_bf16_static(out.data_ptr(), x.data_ptr(), x.numel(), _stream()), "b200_sumsq_bf16_static")
     launch_count += 1
     return out
 

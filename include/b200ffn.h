@@ -75,6 +75,22 @@ int b200_cast_bf16_to_f32(float* out, const void* in, long long n, void* stream)
  * bytes and its first 4 bytes (the arrival counter) must be zero on entry; the kernel re-zeroes it. */
 long long b200_sumsq_scratch_bytes(void);
 int b200_sumsq_bf16(float* out, const void* x, long long n, void* scratch, long long scratch_bytes, void* stream);
+/* Allocation-free form of b200_sumsq_bf16 (no counterpart in the reference, which never calls a kernel of its own).
+ * For hosts that cannot hand this library any device memory beyond the input and the 4-byte result, and cannot let
+ * it allocate either: a plain C program driving the kernels without a tensor framework behind it; a plug-in inside a
+ * process whose device memory already belongs in full to another allocator (PyTorch's caching allocator, a serving
+ * arena), where a raw cudaMalloc fails or costs a device-wide synchronisation; a step loop that must not take the
+ * driver's allocation lock.  The per-CTA partial sums go through a 1280-byte array built into the library image,
+ * which every GPU that loads the library holds until the process exits.
+ *   - limit: n <= b200_sumsq_static_max_elems() (2^31 elements); larger inputs are refused with B200_ERR_ARG and a
+ *     message - use b200_sumsq_bf16 with your own scratch for those.
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, that device must be
+ *     current); make that first call before starting any stream capture.
+ *   - no cudaMalloc / cudaFree / allocating library call is made, on the first call or later.
+ *   - every call on a device uses the same array: the arrival counter is reset on the stream before each launch,
+ *     but two calls whose kernels overlap on the GPU (different streams) corrupt each other - serialise them. */
+long long b200_sumsq_static_max_elems(void);
+int b200_sumsq_bf16_static(float* out, const void* x, long long n, void* stream);
 /* Writes `bytes` of zeros (L2 flush between timed iterations). */
 int b200_fill_zero(void* buf, long long bytes, void* stream);
 
