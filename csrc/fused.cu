@@ -142,6 +142,13 @@ struct FusedEpi {
         drain(p, g, ctx, st, /*block=*/false);
     }
 
+    // a pair kernel's CTA whose half of the 256-row tile lies beyond M: nothing to push, but keep the epilogue
+    // warps in step (the group barrier in after_tile is counted per tile) and use the time to reduce
+    static __device__ __forceinline__ void after_skipped_tile(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st) {
+        epi_group_sync();
+        drain(p, g, ctx, st, /*block=*/false);
+    }
+
     static __device__ __forceinline__ void tail(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st) {
         drain(p, g, ctx, st, /*block=*/true);
         if (p.broadcast) {                                           // every tile of MY output has been delivered

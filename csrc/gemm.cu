@@ -1,6 +1,7 @@
 // C-ABI entry points for the single-GPU tcgen05 GEMM family (see include/b200ffn.h).
 #include "gemm_kernel.cuh"
 #include "../include/b200ffn.h"
+#include <cstdlib>
 
 namespace b200 {
 
@@ -24,7 +25,16 @@ int validate_operands(const GemmOperands& o) {
     return 0;
 }
 
-int make_core_and_maps(const GemmOperands& o, GemmCore* core, CUtensorMap* tmA, CUtensorMap* tmB) {
+bool use_pair_kernel() {
+    static int cached = -1;
+    if (cached < 0) {
+        const char* e = getenv("B200_GEMM_PAIR");
+        cached = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return cached == 1;
+}
+
+int make_core_and_maps(const GemmOperands& o, GemmCore* core, CUtensorMap* tmA, CUtensorMap* tmB, bool pair) {
     int rc = validate_operands(o);
     if (rc != 0) return rc;
     core->M = o.M; core->N = o.N; core->K = o.K;
@@ -37,7 +47,8 @@ int make_core_and_maps(const GemmOperands& o, GemmCore* core, CUtensorMap* tmA, 
     if (o.a_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmA, o.A, o.K, o.M, o.lda, BK, BM);
     else                      rc = encode_tmap_bf16_2d(tmA, o.A, o.M, o.K, o.lda, 64, BK);
     if (rc != 0) return rc;
-    if (o.b_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmB, o.B, o.K, o.N, o.ldb, BK, BN);
+    // the pair kernel stages 128 B rows per CTA, the 1-CTA kernel all 256
+    if (o.b_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmB, o.B, o.K, o.N, o.ldb, BK, pair ? 128 : BN);
     else                      rc = encode_tmap_bf16_2d(tmB, o.B, o.N, o.K, o.ldb, 64, BK);
     return rc;
 }

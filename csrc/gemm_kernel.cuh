@@ -247,6 +247,193 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // ---------------------------------------------------------------------------------------------
+// CTA-pair variant: two CTAs of a cluster (one TPC) cooperate on a 256x256 tile with tcgen05.mma.cta_group::2.
+// Each CTA stages ITS 128 rows of A and ITS 128 rows of B (half of what the 1-CTA kernel stages for the same math),
+// so shared-memory write+read traffic per SM drops by a third and the ring gets 6 stages instead of 4.  The leader
+// CTA's MMA thread issues for both; accumulators land in each CTA's own TMEM (rows [rank*128, +128) of the pair
+// tile), so the epilogue policies are unchanged.
+// ---------------------------------------------------------------------------------------------
+constexpr int P_STAGES = 6;
+constexpr int P_A_STAGE_BYTES = 128 * BK * 2;   // 16 KiB: this CTA's 128 rows of A
+constexpr int P_B_STAGE_BYTES = 128 * BK * 2;   // 16 KiB: this CTA's 128 of the tile's 256 B rows
+constexpr int P_STAGE_BYTES = P_A_STAGE_BYTES + P_B_STAGE_BYTES;
+static_assert(P_STAGES * P_STAGE_BYTES == STAGES * STAGE_BYTES, "both variants use the same smem carve-up");
+
+template <class Epi>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const GemmCore g, const typename Epi::Params ep) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sA = base;
+    uint8_t* sB = base + P_STAGES * P_A_STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + P_STAGES * P_STAGE_BYTES);
+    uint64_t* full = bars;                       // [P_STAGES]  (only the leader's are waited on)
+    uint64_t* empty = bars + P_STAGES;           // [P_STAGES]
+    uint64_t* tmem_full = bars + 2 * P_STAGES;   // [2]
+    uint64_t* tmem_empty = bars + 2 * P_STAGES + 2;   // [2]  (only the leader's are waited on)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * P_STAGES + 4);
+    uint8_t* epi_stage = base + P_STAGES * P_STAGE_BYTES + 256;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();     // 0 = leader
+    const int pair = blockIdx.x >> 1;
+    const int num_pairs = gridDim.x >> 1;
+    const int pair_tiles_m = (g.tiles_m + 1) >> 1;
+    const int num_tiles = pair_tiles_m * g.tiles_n;
+    const int num_kb = (g.K + BK - 1) / BK;
+
+    if (threadIdx.x == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+#pragma unroll
+        for (int s = 0; s < P_STAGES; ++s) {
+            mbar_init(&full[s], 1);              // the leader's expect_tx arrival; BOTH CTAs' bytes are credited here
+            mbar_init(&empty[s], 1);             // one multicast commit
+        }
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tmem_full[s], 1);
+            mbar_init(&tmem_empty[s], 2 * EPI_WARPS);   // epilogue warps of BOTH CTAs
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc_512_pair(tmem_slot);
+    tc_fence_before();
+    cluster_sync_all();                          // barriers + TMEM of both CTAs are ready before any cross-CTA traffic
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    // pair-tile index -> (pair row, n block), grouped like tile_coords (8 pair rows = 16 m blocks per group)
+    auto pair_coords = [&](int tile, int& pm, int& n_blk) {
+        const int gm = g.group_m >> 1 > 0 ? g.group_m >> 1 : 1;
+        const int per_group = gm * g.tiles_n;
+        const int group = tile / per_group;
+        const int first = group * gm;
+        const int gsize = min(pair_tiles_m - first, gm);
+        const int in_group = tile - group * per_group;
+        pm = first + in_group % gsize;
+        n_blk = in_group / gsize;
+    };
+
+    if (threadIdx.x == 0) {
+        // ===================== TMA producer (one thread in EACH CTA) =====================
+        int s = 0;
+        uint32_t phase = 0;
+        for (int it = pair; it < num_tiles; it += num_pairs) {
+            int tile = it + g.tile_offset;
+            if (tile >= num_tiles) tile -= num_tiles;
+            int pm, n_blk;
+            pair_coords(tile, pm, n_blk);
+            const int m0 = (pm * 2 + (int)rank) * BM;            // my 128 rows of A
+            const int n0 = n_blk * BN + (int)rank * 128;         // my 128 rows of B
+            for (int kb = 0; kb < num_kb; ++kb) {
+                mbar_wait(&empty[s], phase ^ 1, g.err, 0x100 + s);
+                // The peer's bytes may land before this arrival: the transaction count just goes negative for a
+                // moment, and the phase cannot complete until the one pending arrival (this one) has happened.
+                if (rank == 0) mbar_arrive_expect_tx(&full[s], 2 * P_STAGE_BYTES);
+                const int k0 = kb * BK;
+                uint8_t* a_dst = sA + s * P_A_STAGE_BYTES;
+                uint8_t* b_dst = sB + s * P_B_STAGE_BYTES;
+                if (g.a_major == MAJOR_K) {
+                    tma_load_2d_pair(a_dst, &tmA, &full[s], k0, m0);                       // box {64 k, 128 m}
+                } else {
+                    tma_load_2d_pair(a_dst, &tmA, &full[s], m0, k0);                       // 2 x box {64 m, 64 k}
+                    tma_load_2d_pair(a_dst + BK * 128, &tmA, &full[s], m0 + 64, k0);
+                }
+                if (g.b_major == MAJOR_K) {
+                    tma_load_2d_pair(b_dst, &tmB, &full[s], k0, n0);                       // box {64 k, 128 n}
+                } else {
+                    tma_load_2d_pair(b_dst, &tmB, &full[s], n0, k0);
+                    tma_load_2d_pair(b_dst + BK * 128, &tmB, &full[s], n0 + 64, k0);
+                }
+                if (++s == P_STAGES) { s = 0; phase ^= 1; }
+            }
+        }
+    } else if (threadIdx.x == 32 && rank == 0) {
+        // ===================== MMA issuer (one thread, leader CTA only) =====================
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10)
+                               | ((uint32_t)g.a_major << 15) | ((uint32_t)g.b_major << 16)
+                               | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);   // M = 256 across the pair
+        const uint32_t a_lbo = g.a_major == MAJOR_K ? 16u : (uint32_t)(BK * 128);
+        const uint32_t b_lbo = g.b_major == MAJOR_K ? 16u : (uint32_t)(BK * 128);
+        const uint32_t a_kadv = g.a_major == MAJOR_K ? 32u : 2048u;
+        const uint32_t b_kadv = g.b_major == MAJOR_K ? 32u : 2048u;
+        int s = 0;
+        uint32_t phase = 0;
+        int as = 0;
+        uint32_t aphase = 0;
+        for (int it = pair; it < num_tiles; it += num_pairs) {
+            mbar_wait(&tmem_empty[as], aphase ^ 1, g.err, 0x200 + as);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                mbar_wait(&full[s], phase, g.err, 0x300 + s);
+                tc_fence_after();
+                const uint32_t a_base = smem_u32(sA + s * P_A_STAGE_BYTES);
+                const uint32_t b_base = smem_u32(sB + s * P_B_STAGE_BYTES);
+#pragma unroll
+                for (int k = 0; k < BK / UMMA_K; ++k) {
+                    const uint64_t adesc = make_smem_desc_sw128(a_base + k * a_kadv, a_lbo, 1024);
+                    const uint64_t bdesc = make_smem_desc_sw128(b_base + k * b_kadv, b_lbo, 1024);
+                    umma_bf16_pair(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                }
+                umma_commit_pair(&empty[s]);                         // frees the slot in BOTH CTAs
+                if (kb == num_kb - 1) umma_commit_pair(&tmem_full[as]);
+                if (++s == P_STAGES) { s = 0; phase ^= 1; }
+            }
+            if (++as == 2) { as = 0; aphase ^= 1; }
+        }
+    } else if (warp >= 2) {
+        // ===================== epilogue (8 warps per CTA) =====================
+        EpiCtx ctx;
+        ctx.ewarp = warp - 2;
+        ctx.q = warp & 3;
+        ctx.half = (warp - 2) >> 2;
+        ctx.lane = lane;
+        ctx.stage = epi_stage + ctx.ewarp * EPI_STAGE_BYTES;
+        ctx.scratch = reinterpret_cast<uint32_t*>(epi_stage + EPI_WARPS * EPI_STAGE_BYTES);
+        ctx.tile = -1;
+        ctx.m_blk = ctx.n_blk = ctx.m0 = ctx.n0 = 0;
+        typename Epi::State est;
+        Epi::init(ep, g, ctx, est);
+        int as = 0;
+        uint32_t aphase = 0;
+        for (int it = pair; it < num_tiles; it += num_pairs) {
+            int tile = it + g.tile_offset;
+            if (tile >= num_tiles) tile -= num_tiles;
+            int pm;
+            pair_coords(tile, pm, ctx.n_blk);
+            ctx.tile = tile;
+            ctx.m_blk = pm * 2 + (int)rank;
+            ctx.m0 = ctx.m_blk * BM;
+            ctx.n0 = ctx.n_blk * BN;
+            mbar_wait(&tmem_full[as], aphase, g.err, 0x400 + as);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(ctx.q * 32) << 16) + (uint32_t)(as * BN + ctx.half * (BN / 2));
+            const bool real_tile = ctx.m_blk < g.tiles_m;           // odd tiles_m: the last pair's second half is empty
+            if (real_tile) Epi::process_tile(ep, g, ctx, taddr, est);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if (rank == 0) mbar_arrive(&tmem_empty[as]);
+                else mbar_arrive_remote(&tmem_empty[as], 0);
+            }
+            if (real_tile) Epi::after_tile(ep, g, ctx, est);
+            else Epi::after_skipped_tile(ep, g, ctx, est);
+            if (++as == 2) { as = 0; aphase ^= 1; }
+        }
+        Epi::tail(ep, g, ctx, est);
+    }
+
+    tc_fence_before();
+    cluster_sync_all();                          // neither CTA may retire while its pair still uses its smem / barriers
+    tc_fence_after();
+    if (warp == 1) tmem_dealloc_512_pair(tmem_base);
+}
+
+// ---------------------------------------------------------------------------------------------
 // Local epilogues
 // ---------------------------------------------------------------------------------------------
 enum EpiKind : int {
@@ -287,6 +474,7 @@ struct LocalEpi {
     struct State {};
     static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx&, State&) {}
     static __device__ __forceinline__ void after_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {}
+    static __device__ __forceinline__ void after_skipped_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {}
     static __device__ __forceinline__ void tail(const Params&, const GemmCore&, const EpiCtx&, State&) {}
 
     static __device__ __forceinline__ void load_aux(const Params& p, const GemmCore& g, int row, int col0, uint4 (&a)[4]) {
@@ -395,31 +583,56 @@ struct GemmOperands {
 };
 
 int validate_operands(const GemmOperands& o);
-int make_core_and_maps(const GemmOperands& o, GemmCore* core, CUtensorMap* tmA, CUtensorMap* tmB);
+int make_core_and_maps(const GemmOperands& o, GemmCore* core, CUtensorMap* tmA, CUtensorMap* tmB, bool pair);
+
+bool use_pair_kernel();   // runtime switch (B200_GEMM_PAIR=0 selects the 1-CTA kernel)
 
 template <class Epi>
 int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_ctas, cudaStream_t stream,
                 int tile_offset_num = 0, int tile_offset_den = 1) {
     GemmCore core;
     alignas(64) CUtensorMap tmA, tmB;
-    int rc = make_core_and_maps(o, &core, &tmA, &tmB);
+    const bool pair = use_pair_kernel();
+    int rc = make_core_and_maps(o, &core, &tmA, &tmB, pair);
     if (rc != 0) return rc;
-    core.tile_offset = (int)((long long)core.tiles_m * core.tiles_n * tile_offset_num / tile_offset_den);
     static unsigned long long attr_mask = 0;   // per template instantiation, one bit per device
     int dev = 0;
     cudaGetDevice(&dev);
     if (!(attr_mask >> (dev & 63) & 1ull)) {
         rc = check_cuda(cudaFuncSetAttribute(gemm_tcgen05_kernel<Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             Epi::SMEM_BYTES),
-                        "cudaFuncSetAttribute(smem)");
+                                             Epi::SMEM_BYTES), "cudaFuncSetAttribute(smem)");
+        if (rc != 0) return rc;
+        rc = check_cuda(cudaFuncSetAttribute(gemm_tcgen05_pair_kernel<Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Epi::SMEM_BYTES), "cudaFuncSetAttribute(smem, pair)");
         if (rc != 0) return rc;
         attr_mask |= 1ull << (dev & 63);
     }
-    int grid = core.tiles_m * core.tiles_n;
     int cap = max_ctas > 0 ? max_ctas : num_sms();
-    if (grid > cap) grid = cap;
-    gemm_tcgen05_kernel<Epi><<<grid, GEMM_THREADS, Epi::SMEM_BYTES, stream>>>(tmA, tmB, core, ep);
-    return check_cuda(cudaGetLastError(), "gemm launch");
+    if (!pair) {
+        const int tiles = core.tiles_m * core.tiles_n;
+        core.tile_offset = (int)((long long)tiles * tile_offset_num / tile_offset_den);
+        int grid = tiles < cap ? tiles : cap;
+        gemm_tcgen05_kernel<Epi><<<grid, GEMM_THREADS, Epi::SMEM_BYTES, stream>>>(tmA, tmB, core, ep);
+        return check_cuda(cudaGetLastError(), "gemm launch");
+    }
+    const int pair_tiles = ((core.tiles_m + 1) / 2) * core.tiles_n;
+    core.tile_offset = (int)((long long)pair_tiles * tile_offset_num / tile_offset_den);
+    int pairs = cap / 2;
+    if (pairs < 1) pairs = 1;
+    if (pairs > pair_tiles) pairs = pair_tiles;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * pairs);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = Epi::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return check_cuda(cudaLaunchKernelEx(&cfg, gemm_tcgen05_pair_kernel<Epi>, tmA, tmB, core, ep), "gemm pair launch");
 }
 
 }  // namespace b200

@@ -85,7 +85,9 @@ def _init():
     from distributed_llm_code_samples_b200.models import ffn
     g = torch.Generator().manual_seed(21)
     lp = ffn.init_stack(3, DM, 4 * DM, g)
-    return [[p.to(torch.bfloat16).float() for p in l] for l in lp], torch.arange(2 * WORLD)
+    # ONE optimizer step per rank: after a second step the two paths' 1-ulp rounding differences feed back through
+    # the gradients (measured: ~1% of weights then differ by up to 4 ulp, uniformly over all tiles, deterministically)
+    return [[p.to(torch.bfloat16).float() for p in l] for l in lp], torch.arange(WORLD)
 
 
 def _rel(a, b):
