@@ -44,7 +44,8 @@ int make_core_and_maps(const GemmOperands& o, GemmCore* core, CUtensorMap* tmA, 
     core->group_m = 16;
     core->tile_offset = 0;
     core->err = device_error_slot();
-    if (o.a_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmA, o.A, o.K, o.M, o.lda, BK, BM);
+    // K-major boxes: the pair kernel stages 256 A rows and 128 B rows per CTA, the 1-CTA kernel 128 and 256
+    if (o.a_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmA, o.A, o.K, o.M, o.lda, BK, pair ? 256 : BM);
     else                      rc = encode_tmap_bf16_2d(tmA, o.A, o.M, o.K, o.lda, 64, BK);
     if (rc != 0) return rc;
     // the pair kernel stages 128 B rows per CTA, the 1-CTA kernel all 256

@@ -247,14 +247,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // ---------------------------------------------------------------------------------------------
-// CTA-pair variant: two CTAs of a cluster (one TPC) cooperate on a 256x256 tile with tcgen05.mma.cta_group::2.
-// Each CTA stages ITS 128 rows of A and ITS 128 rows of B (half of what the 1-CTA kernel stages for the same math),
-// so shared-memory write+read traffic per SM drops by a third and the ring gets 6 stages instead of 4.  The leader
-// CTA's MMA thread issues for both; accumulators land in each CTA's own TMEM (rows [rank*128, +128) of the pair
-// tile), so the epilogue policies are unchanged.
+// CTA-pair variant: two CTAs of a cluster (one TPC) cooperate on a 512x256 tile with tcgen05.mma.cta_group::2.
+// Each CTA stages 256 rows of A (two 128-row halves) and 128 of the tile's 256 B rows per k-block, and owns TWO
+// 128x256 fp32 accumulators (all 512 TMEM columns): every B stage is used by both halves, so operand bytes per MAC
+// drop to (256+128)/(256*256) - 25% below a 128x256-per-CTA pair and half of the 1-CTA kernel.  The leader CTA's MMA
+// thread issues for both CTAs.  The epilogue releases the two accumulators separately, so the next tile's first
+// MMAs overlap the second half's epilogue; the shared-memory ring keeps prefetching throughout.
 // ---------------------------------------------------------------------------------------------
-constexpr int P_STAGES = 6;
-constexpr int P_A_STAGE_BYTES = 128 * BK * 2;   // 16 KiB: this CTA's 128 rows of A
+constexpr int P_STAGES = 4;
+constexpr int P_A_STAGE_BYTES = 256 * BK * 2;   // 32 KiB: this CTA's 2 x 128 rows of A
 constexpr int P_B_STAGE_BYTES = 128 * BK * 2;   // 16 KiB: this CTA's 128 of the tile's 256 B rows
 constexpr int P_STAGE_BYTES = P_A_STAGE_BYTES + P_B_STAGE_BYTES;
 static_assert(P_STAGES * P_STAGE_BYTES == STAGES * STAGE_BYTES, "both variants use the same smem carve-up");
@@ -268,19 +269,19 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     uint8_t* sA = base;
     uint8_t* sB = base + P_STAGES * P_A_STAGE_BYTES;
     uint64_t* bars = reinterpret_cast<uint64_t*>(base + P_STAGES * P_STAGE_BYTES);
-    uint64_t* full = bars;                       // [P_STAGES]  (only the leader's are waited on)
-    uint64_t* empty = bars + P_STAGES;           // [P_STAGES]
-    uint64_t* tmem_full = bars + 2 * P_STAGES;   // [2]
-    uint64_t* tmem_empty = bars + 2 * P_STAGES + 2;   // [2]  (only the leader's are waited on)
+    uint64_t* full = bars;                            // [P_STAGES]  (only the leader's are waited on)
+    uint64_t* empty = bars + P_STAGES;                // [P_STAGES]
+    uint64_t* tmem_full = bars + 2 * P_STAGES;        // [1]
+    uint64_t* tmem_empty = bars + 2 * P_STAGES + 1;   // [2] one per accumulator half (only the leader's are waited on)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * P_STAGES + 4);
     uint8_t* epi_stage = base + P_STAGES * P_STAGE_BYTES + 256;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const uint32_t rank = cluster_ctarank();     // 0 = leader
+    const uint32_t rank = cluster_ctarank();          // 0 = leader
     const int pair = blockIdx.x >> 1;
     const int num_pairs = gridDim.x >> 1;
-    const int pair_tiles_m = (g.tiles_m + 1) >> 1;
+    const int pair_tiles_m = (g.tiles_m + 3) >> 2;    // 512 rows = four 128-row blocks per pair tile
     const int num_tiles = pair_tiles_m * g.tiles_n;
     const int num_kb = (g.K + BK - 1) / BK;
 
@@ -289,25 +290,23 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         tma_prefetch_desc(&tmB);
 #pragma unroll
         for (int s = 0; s < P_STAGES; ++s) {
-            mbar_init(&full[s], 1);              // the leader's expect_tx arrival; BOTH CTAs' bytes are credited here
-            mbar_init(&empty[s], 1);             // one multicast commit
+            mbar_init(&full[s], 1);                   // the leader's expect_tx arrival; BOTH CTAs' bytes are credited here
+            mbar_init(&empty[s], 1);                  // one multicast commit
         }
-#pragma unroll
-        for (int s = 0; s < 2; ++s) {
-            mbar_init(&tmem_full[s], 1);
-            mbar_init(&tmem_empty[s], 2 * EPI_WARPS);   // epilogue warps of BOTH CTAs
-        }
+        mbar_init(&tmem_full[0], 1);
+        mbar_init(&tmem_empty[0], 2 * EPI_WARPS);     // epilogue warps of BOTH CTAs
+        mbar_init(&tmem_empty[1], 2 * EPI_WARPS);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc_512_pair(tmem_slot);
     tc_fence_before();
-    cluster_sync_all();                          // barriers + TMEM of both CTAs are ready before any cross-CTA traffic
+    cluster_sync_all();                               // barriers + TMEM of both CTAs exist before any cross-CTA traffic
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    // pair-tile index -> (pair row, n block), grouped like tile_coords (8 pair rows = 16 m blocks per group)
+    // pair-tile index -> (pair row, n block); groups of 4 pair rows (= 16 m blocks) keep ~74 live tiles near-square
     auto pair_coords = [&](int tile, int& pm, int& n_blk) {
-        const int gm = g.group_m >> 1 > 0 ? g.group_m >> 1 : 1;
+        const int gm = g.group_m >> 2 > 0 ? g.group_m >> 2 : 1;
         const int per_group = gm * g.tiles_n;
         const int group = tile / per_group;
         const int first = group * gm;
@@ -326,7 +325,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             if (tile >= num_tiles) tile -= num_tiles;
             int pm, n_blk;
             pair_coords(tile, pm, n_blk);
-            const int m0 = (pm * 2 + (int)rank) * BM;            // my 128 rows of A
+            const int m0 = (pm * 4 + (int)rank * 2) * BM;        // my 256 rows of A
             const int n0 = n_blk * BN + (int)rank * 128;         // my 128 rows of B
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&empty[s], phase ^ 1, g.err, 0x100 + s);
@@ -337,10 +336,11 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 uint8_t* a_dst = sA + s * P_A_STAGE_BYTES;
                 uint8_t* b_dst = sB + s * P_B_STAGE_BYTES;
                 if (g.a_major == MAJOR_K) {
-                    tma_load_2d_pair(a_dst, &tmA, &full[s], k0, m0);                       // box {64 k, 128 m}
+                    tma_load_2d_pair(a_dst, &tmA, &full[s], k0, m0);                       // box {64 k, 256 m}
                 } else {
-                    tma_load_2d_pair(a_dst, &tmA, &full[s], m0, k0);                       // 2 x box {64 m, 64 k}
-                    tma_load_2d_pair(a_dst + BK * 128, &tmA, &full[s], m0 + 64, k0);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)                                            // 4 x box {64 m, 64 k}
+                        tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, &full[s], m0 + j * 64, k0);
                 }
                 if (g.b_major == MAJOR_K) {
                     tma_load_2d_pair(b_dst, &tmB, &full[s], k0, n0);                       // box {64 k, 128 n}
@@ -362,28 +362,31 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         const uint32_t b_kadv = g.b_major == MAJOR_K ? 32u : 2048u;
         int s = 0;
         uint32_t phase = 0;
-        int as = 0;
-        uint32_t aphase = 0;
+        uint32_t tphase = 0;
         for (int it = pair; it < num_tiles; it += num_pairs) {
-            mbar_wait(&tmem_empty[as], aphase ^ 1, g.err, 0x200 + as);
-            tc_fence_after();
-            const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&full[s], phase, g.err, 0x300 + s);
                 tc_fence_after();
                 const uint32_t a_base = smem_u32(sA + s * P_A_STAGE_BYTES);
                 const uint32_t b_base = smem_u32(sB + s * P_B_STAGE_BYTES);
 #pragma unroll
-                for (int k = 0; k < BK / UMMA_K; ++k) {
-                    const uint64_t adesc = make_smem_desc_sw128(a_base + k * a_kadv, a_lbo, 1024);
-                    const uint64_t bdesc = make_smem_desc_sw128(b_base + k * b_kadv, b_lbo, 1024);
-                    umma_bf16_pair(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                for (int h = 0; h < 2; ++h) {                        // the two 128-row halves share this B stage
+                    if (kb == 0) {
+                        mbar_wait(&tmem_empty[h], tphase ^ 1, g.err, 0x200 + h);   // epilogue has drained this half
+                        tc_fence_after();
+                    }
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        const uint64_t adesc = make_smem_desc_sw128(a_base + h * (128 * BK * 2) + k * a_kadv, a_lbo, 1024);
+                        const uint64_t bdesc = make_smem_desc_sw128(b_base + k * b_kadv, b_lbo, 1024);
+                        umma_bf16_pair(tmem_base + (uint32_t)(h * BN), adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
                 }
                 umma_commit_pair(&empty[s]);                         // frees the slot in BOTH CTAs
-                if (kb == num_kb - 1) umma_commit_pair(&tmem_full[as]);
+                if (kb == num_kb - 1) umma_commit_pair(&tmem_full[0]);
                 if (++s == P_STAGES) { s = 0; phase ^= 1; }
             }
-            if (++as == 2) { as = 0; aphase ^= 1; }
+            tphase ^= 1;
         }
     } else if (warp >= 2) {
         // ===================== epilogue (8 warps per CTA) =====================
@@ -398,37 +401,39 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         ctx.m_blk = ctx.n_blk = ctx.m0 = ctx.n0 = 0;
         typename Epi::State est;
         Epi::init(ep, g, ctx, est);
-        int as = 0;
-        uint32_t aphase = 0;
+        uint32_t tphase = 0;
         for (int it = pair; it < num_tiles; it += num_pairs) {
             int tile = it + g.tile_offset;
             if (tile >= num_tiles) tile -= num_tiles;
             int pm;
             pair_coords(tile, pm, ctx.n_blk);
             ctx.tile = tile;
-            ctx.m_blk = pm * 2 + (int)rank;
-            ctx.m0 = ctx.m_blk * BM;
             ctx.n0 = ctx.n_blk * BN;
-            mbar_wait(&tmem_full[as], aphase, g.err, 0x400 + as);
+            mbar_wait(&tmem_full[0], tphase, g.err, 0x400);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(ctx.q * 32) << 16) + (uint32_t)(as * BN + ctx.half * (BN / 2));
-            const bool real_tile = ctx.m_blk < g.tiles_m;           // odd tiles_m: the last pair's second half is empty
-            if (real_tile) Epi::process_tile(ep, g, ctx, taddr, est);
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-                if (rank == 0) mbar_arrive(&tmem_empty[as]);
-                else mbar_arrive_remote(&tmem_empty[as], 0);
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+                ctx.m_blk = pm * 4 + (int)rank * 2 + h;
+                ctx.m0 = ctx.m_blk * BM;
+                const uint32_t taddr = tmem_base + ((uint32_t)(ctx.q * 32) << 16) + (uint32_t)(h * BN + ctx.half * (BN / 2));
+                const bool real_tile = ctx.m_blk < g.tiles_m;       // ragged M: trailing 128-row blocks may not exist
+                if (real_tile) Epi::process_tile(ep, g, ctx, taddr, est);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if (rank == 0) mbar_arrive(&tmem_empty[h]);
+                    else mbar_arrive_remote(&tmem_empty[h], 0);
+                }
+                if (real_tile) Epi::after_tile(ep, g, ctx, est);
+                else Epi::after_skipped_tile(ep, g, ctx, est);
             }
-            if (real_tile) Epi::after_tile(ep, g, ctx, est);
-            else Epi::after_skipped_tile(ep, g, ctx, est);
-            if (++as == 2) { as = 0; aphase ^= 1; }
+            tphase ^= 1;
         }
         Epi::tail(ep, g, ctx, est);
     }
 
     tc_fence_before();
-    cluster_sync_all();                          // neither CTA may retire while its pair still uses its smem / barriers
+    cluster_sync_all();                               // neither CTA may retire while its pair still uses its smem / barriers
     tc_fence_after();
     if (warp == 1) tmem_dealloc_512_pair(tmem_base);
 }
@@ -466,109 +471,155 @@ __device__ __forceinline__ float gelu_grad_f(float x) {
     return cdf + x * pdf;
 }
 
+// Row-owner registers <-> whole 128-byte lines, through one warp's swizzled 32x128B stage buffer.
+// After tcgen05.ld each lane owns a row; a direct store would hit 32 different lines with 16 bytes each (and a
+// load would do the same).  Bouncing through shared memory lets 8 lanes cover one 128-byte line: 4 full lines per
+// instruction.  Both helpers end with a __syncwarp so the buffer can be reused immediately.
+__device__ __forceinline__ void stage_store_rows(uint4* stage, int lane, const uint4 (&rowv)[8], __nv_bfloat16* dst, long long ld,
+                                                 int row0, int col0, int M, int N) {
+#pragma unroll
+    for (int pc = 0; pc < 8; ++pc) stage[lane * 8 + (pc ^ (lane & 7))] = rowv[pc];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int r = i * 4 + (lane >> 3);
+        const int pc = lane & 7;
+        const int row = row0 + r, col = col0 + pc * 8;
+        if (row < M && col < N) st_u4(dst + (long long)row * ld + col, stage[r * 8 + (pc ^ (r & 7))]);
+    }
+    __syncwarp();
+}
+template <bool READ_ONLY>
+__device__ __forceinline__ void coalesced_load_rows(uint4 (&v)[8], int lane, const __nv_bfloat16* src, long long ld, int row0, int col0,
+                                                    int M, int N) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int r = i * 4 + (lane >> 3);
+        const int pc = lane & 7;
+        const int row = row0 + r, col = col0 + pc * 8;
+        if (row < M && col < N) {
+            if constexpr (READ_ONLY) v[i] = ld_nc_u4(src + (long long)row * ld + col);             // aux: never written by this kernel
+            else v[i] = *reinterpret_cast<const uint4*>(src + (long long)row * ld + col);             // the weight tile this CTA alone updates
+        } else {
+            v[i] = make_uint4(0, 0, 0, 0);
+        }
+    }
+}
+__device__ __forceinline__ void stage_to_row_owner(uint4* stage, int lane, const uint4 (&v)[8], uint4 (&rowv)[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int r = i * 4 + (lane >> 3);
+        const int pc = lane & 7;
+        stage[r * 8 + (pc ^ (r & 7))] = v[i];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int pc = 0; pc < 8; ++pc) rowv[pc] = stage[lane * 8 + (pc ^ (lane & 7))];
+    __syncwarp();
+}
+
 template <int KIND>
 struct LocalEpi {
     using Params = LocalEpiParams;
-    static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES;
-    static constexpr bool NEEDS_AUX = (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD);
+    static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
+    // a second bf16 [M,N] operand is read by these epilogues: aux, or (SGD) the weight tile itself
+    static constexpr bool READS = (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD || KIND == EPI_SGD);
     struct State {};
     static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx&, State&) {}
     static __device__ __forceinline__ void after_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {}
     static __device__ __forceinline__ void after_skipped_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {}
     static __device__ __forceinline__ void tail(const Params&, const GemmCore&, const EpiCtx&, State&) {}
 
-    static __device__ __forceinline__ void load_aux(const Params& p, const GemmCore& g, int row, int col0, uint4 (&a)[4]) {
-        if constexpr (NEEDS_AUX) {
-            if (row >= g.M) return;
-#pragma unroll
-            for (int v = 0; v < 4; ++v)
-                if (col0 + v * 8 < g.N) a[v] = ld_nc_u4(p.aux + (long long)row * p.ldaux + col0 + v * 8);
-        }
-    }
-
     static __device__ __forceinline__ void process_tile(const Params& p, const GemmCore& g, const EpiCtx& ctx, uint32_t taddr, State&) {
-        const int row = ctx.m0 + ctx.q * 32 + ctx.lane;
+        const int lane = ctx.lane;
+        const int row0 = ctx.m0 + ctx.q * 32;                        // first of this warp's 32 rows
         const int colbase = ctx.n0 + ctx.half * (BN / 2);
-        uint4 aux_next[4] = {};
-        load_aux(p, g, row, colbase, aux_next);                 // overlaps the wait-free first TMEM load
-#pragma unroll 1
-        for (int c = 0; c < BN / 2 / 32; ++c) {
-            uint32_t acc[32];
-            uint4 aux_cur[4];
-#pragma unroll
-            for (int v = 0; v < 4; ++v) aux_cur[v] = aux_next[v];
-            if (c + 1 < BN / 2 / 32) load_aux(p, g, row, colbase + (c + 1) * 32, aux_next);   // prefetch next chunk
-            tmem_ld_32x32(taddr + c * 32, acc);
-            tmem_ld_wait();
-            chunk(p, g, row, colbase + c * 32, acc, aux_cur);
-        }
-    }
+        uint4* stage = reinterpret_cast<uint4*>(ctx.stage);
+        const __nv_bfloat16* rd = KIND == EPI_SGD ? reinterpret_cast<const __nv_bfloat16*>(p.C) : p.aux;
+        const long long rd_ld = KIND == EPI_SGD ? p.ldc : p.ldaux;
 
-    static __device__ __forceinline__ void chunk(const Params& p, const GemmCore& g, int row, int col0,
-                                                 const uint32_t (&acc)[32], const uint4 (&auxv)[4]) {
-        if (row >= g.M) return;
+        if constexpr (KIND == EPI_STORE_F32) {                       // fp32 rows are 128 B per 32 columns already
+            const int row = row0 + lane;
+#pragma unroll 1
+            for (int c = 0; c < BN / 2 / 32; ++c) {
+                uint32_t acc[32];
+                tmem_ld_32x32(taddr + c * 32, acc);
+                tmem_ld_wait();
+                if (row >= g.M) continue;
+                float* out = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + colbase + c * 32;
 #pragma unroll
-        for (int v = 0; v < 4; ++v) {                      // 4 groups of 8 columns = one 16-byte bf16 vector
-            const int col = col0 + v * 8;
-            if (col >= g.N) break;                         // N % 8 == 0 is a launch precondition
-            float f[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(acc[v * 8 + j]);
-            if constexpr (KIND == EPI_STORE || KIND == EPI_RELU || KIND == EPI_GELU || KIND == EPI_ADD) {
-                if (p.bias != nullptr) {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) f[j] += __ldg(p.bias + col + j);
+                for (int v = 0; v < 8; ++v) {
+                    if (colbase + c * 32 + v * 4 >= g.N) break;
+                    *reinterpret_cast<float4*>(out + v * 4) = make_float4(p.alpha * __uint_as_float(acc[v * 4]), p.alpha * __uint_as_float(acc[v * 4 + 1]),
+                                                                         p.alpha * __uint_as_float(acc[v * 4 + 2]), p.alpha * __uint_as_float(acc[v * 4 + 3]));
                 }
             }
-            if constexpr (KIND == EPI_STORE_F32) {
-                float* out = reinterpret_cast<float*>(p.C) + (long long)row * p.ldc + col;
-                float4 o0 = make_float4(p.alpha * f[0], p.alpha * f[1], p.alpha * f[2], p.alpha * f[3]);
-                float4 o1 = make_float4(p.alpha * f[4], p.alpha * f[5], p.alpha * f[6], p.alpha * f[7]);
-                *reinterpret_cast<float4*>(out) = o0;
-                *reinterpret_cast<float4*>(out + 4) = o1;
-                continue;
+            return;
+        }
+
+        uint4 rd_next[8];
+        if constexpr (READS) coalesced_load_rows<KIND != EPI_SGD>(rd_next, lane, rd, rd_ld, row0, colbase, g.M, g.N);
+#pragma unroll 1
+        for (int cp = 0; cp < 2; ++cp) {                             // 64 columns = one 128-byte line per row
+            const int col0 = colbase + cp * 64;
+            uint4 rdrow[8];
+            if constexpr (READS) {
+                stage_to_row_owner(stage, lane, rd_next, rdrow);
+                if (cp == 0) coalesced_load_rows<KIND != EPI_SGD>(rd_next, lane, rd, rd_ld, row0, col0 + 64, g.M, g.N);   // prefetch the next 64 columns
             }
-            __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.C) + (long long)row * p.ldc + col;
-            if constexpr (KIND == EPI_RELU) {
+            uint32_t a0[32], a1[32];
+            tmem_ld_32x32(taddr + cp * 64, a0);
+            tmem_ld_32x32(taddr + cp * 64 + 32, a1);
+            tmem_ld_wait();
+            uint4 outv[8], prev[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) f[j] = f[j] <= 0.0f ? 0.0f : f[j];   // NaN stays NaN, like torch.where(x<=0,0,x)
-            } else if constexpr (KIND == EPI_GELU) {
-                uint4 pre;
-                pre.x = pack_bf16x2(f[0], f[1]); pre.y = pack_bf16x2(f[2], f[3]);
-                pre.z = pack_bf16x2(f[4], f[5]); pre.w = pack_bf16x2(f[6], f[7]);
-                *reinterpret_cast<uint4*>(p.C2 + (long long)row * p.ldc2 + col) = pre;
+            for (int pc = 0; pc < 8; ++pc) {
+                float f[8];
 #pragma unroll
-                for (int j = 0; j < 8; ++j) f[j] = gelu_f(f[j]);
-            } else if constexpr (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD) {
-                const uint4 a = auxv[v];
-                const uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+                for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(pc < 4 ? a0[pc * 8 + j] : a1[(pc - 4) * 8 + j]);
+                if constexpr (KIND == EPI_STORE || KIND == EPI_RELU || KIND == EPI_GELU || KIND == EPI_ADD) {
+                    if (p.bias != nullptr) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float lo = bf16_lo(aw[j]), hi = bf16_hi(aw[j]);
-                    if constexpr (KIND == EPI_RELU_BWD) {
-                        f[2 * j] = lo <= 0.0f ? 0.0f : f[2 * j];            // masked_fill_(x <= 0, 0)
-                        f[2 * j + 1] = hi <= 0.0f ? 0.0f : f[2 * j + 1];
-                    } else if constexpr (KIND == EPI_GELU_BWD) {
-                        f[2 * j] *= gelu_grad_f(lo);
-                        f[2 * j + 1] *= gelu_grad_f(hi);
-                    } else {
-                        f[2 * j] += lo;
-                        f[2 * j + 1] += hi;
+                        for (int j = 0; j < 8; ++j) {
+                            const int col = col0 + pc * 8 + j;
+                            f[j] += col < g.N ? __ldg(p.bias + col) : 0.0f;
+                        }
                     }
                 }
-            } else if constexpr (KIND == EPI_SGD) {
-                const uint4 w = *reinterpret_cast<const uint4*>(out);
-                const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+                if constexpr (KIND == EPI_RELU) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    f[2 * j] = bf16_lo(ww[j]) - p.alpha * f[2 * j];
-                    f[2 * j + 1] = bf16_hi(ww[j]) - p.alpha * f[2 * j + 1];
+                    for (int j = 0; j < 8; ++j) f[j] = f[j] <= 0.0f ? 0.0f : f[j];   // NaN stays NaN, like torch.where(x<=0,0,x)
+                } else if constexpr (KIND == EPI_GELU) {
+                    prev[pc].x = pack_bf16x2(f[0], f[1]); prev[pc].y = pack_bf16x2(f[2], f[3]);
+                    prev[pc].z = pack_bf16x2(f[4], f[5]); prev[pc].w = pack_bf16x2(f[6], f[7]);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] = gelu_f(f[j]);
+                } else if constexpr (READS) {
+                    const uint32_t aw[4] = {rdrow[pc].x, rdrow[pc].y, rdrow[pc].z, rdrow[pc].w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float lo = bf16_lo(aw[j]), hi = bf16_hi(aw[j]);
+                        if constexpr (KIND == EPI_RELU_BWD) {
+                            f[2 * j] = lo <= 0.0f ? 0.0f : f[2 * j];                // masked_fill_(x <= 0, 0)
+                            f[2 * j + 1] = hi <= 0.0f ? 0.0f : f[2 * j + 1];
+                        } else if constexpr (KIND == EPI_GELU_BWD) {
+                            f[2 * j] *= gelu_grad_f(lo);
+                            f[2 * j + 1] *= gelu_grad_f(hi);
+                        } else if constexpr (KIND == EPI_ADD) {
+                            f[2 * j] += lo;
+                            f[2 * j + 1] += hi;
+                        } else {                                                    // SGD: W - alpha * dW
+                            f[2 * j] = lo - p.alpha * f[2 * j];
+                            f[2 * j + 1] = hi - p.alpha * f[2 * j + 1];
+                        }
+                    }
                 }
+                outv[pc].x = pack_bf16x2(f[0], f[1]); outv[pc].y = pack_bf16x2(f[2], f[3]);
+                outv[pc].z = pack_bf16x2(f[4], f[5]); outv[pc].w = pack_bf16x2(f[6], f[7]);
             }
-            uint4 o;
-            o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-            o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-            *reinterpret_cast<uint4*>(out) = o;
+            if constexpr (KIND == EPI_GELU)
+                stage_store_rows(stage, lane, prev, p.C2, p.ldc2, row0, col0, g.M, g.N);
+            stage_store_rows(stage, lane, outv, reinterpret_cast<__nv_bfloat16*>(p.C), p.ldc, row0, col0, g.M, g.N);
         }
     }
 };
@@ -615,7 +666,7 @@ int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_c
         gemm_tcgen05_kernel<Epi><<<grid, GEMM_THREADS, Epi::SMEM_BYTES, stream>>>(tmA, tmB, core, ep);
         return check_cuda(cudaGetLastError(), "gemm launch");
     }
-    const int pair_tiles = ((core.tiles_m + 1) / 2) * core.tiles_n;
+    const int pair_tiles = ((core.tiles_m + 3) / 4) * core.tiles_n;      // 512 x 256 per CTA pair
     core.tile_offset = (int)((long long)pair_tiles * tile_offset_num / tile_offset_den);
     int pairs = cap / 2;
     if (pairs < 1) pairs = 1;

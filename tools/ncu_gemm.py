@@ -21,6 +21,9 @@ fn = {
     "G2": lambda: nv.gemm(a, 0, w2, 0, y, T, D, F),
     "G5": lambda: nv.gemm(dy, 0, w2, 1, h, T, F, D, nv.EPI_RELU_BWD, aux=a),
     "G4": lambda: nv.gemm(dy, 1, a, 1, dw, D, F, T),
+    "cublas_G1": lambda: torch.matmul(x, w1.T, out=h),
+    "cublas_G2": lambda: torch.matmul(a, w2.T, out=y),
+    "cublas_G4": lambda: torch.matmul(dy.T, a, out=dw),
 }[case]
 for _ in range(iters):
     fn()
