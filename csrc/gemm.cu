@@ -73,6 +73,12 @@ extern "C" int b200_gemm_bf16(const void* A, long long lda, int a_major, const v
     if (epilogue == EPI_GELU && (C2 == nullptr || (reinterpret_cast<uintptr_t>(C2) & 15) || (ldc2 % 8) || ldc2 < N)) {
         set_last_error("gemm: GELU epilogue needs a second output C2[M,N] for the pre-activation"); return B200_ERR_ARG;
     }
+    if (epilogue == EPI_RELU_MASK && (C2 == nullptr || (reinterpret_cast<uintptr_t>(C2) & 15) || (ldc2 % 16) || ldc2 * 8 < ((N + 127) / 128) * 128)) {
+        set_last_error("gemm: RELU_MASK needs C2 = uint8 mask[M, ldc2] with ldc2 %% 16 == 0 and ldc2 >= ceil(N/128)*16 bytes"); return B200_ERR_ARG;
+    }
+    if (epilogue == EPI_RELU_BWD_MASK && (aux == nullptr || (reinterpret_cast<uintptr_t>(aux) & 15) || (ldaux % 16) || ldaux * 8 < ((N + 127) / 128) * 128)) {
+        set_last_error("gemm: RELU_BWD_MASK needs aux = uint8 mask[M, ldaux] with ldaux %% 16 == 0 and ldaux >= ceil(N/128)*16 bytes"); return B200_ERR_ARG;
+    }
     LocalEpiParams ep{C, ldc, reinterpret_cast<const __nv_bfloat16*>(aux), ldaux, reinterpret_cast<__nv_bfloat16*>(C2), ldc2, bias, alpha};
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (epilogue) {
@@ -84,6 +90,8 @@ extern "C" int b200_gemm_bf16(const void* A, long long lda, int a_major, const v
         case EPI_ADD:       return launch_gemm<LocalEpi<EPI_ADD>>(o, ep, max_ctas, st);
         case EPI_SGD:       return launch_gemm<LocalEpi<EPI_SGD>>(o, ep, max_ctas, st);
         case EPI_STORE_F32: return launch_gemm<LocalEpi<EPI_STORE_F32>>(o, ep, max_ctas, st);
+        case EPI_RELU_MASK: return launch_gemm<LocalEpi<EPI_RELU_MASK>>(o, ep, max_ctas, st);
+        case EPI_RELU_BWD_MASK: return launch_gemm<LocalEpi<EPI_RELU_BWD_MASK>>(o, ep, max_ctas, st);
         default: set_last_error("gemm: unknown epilogue %d", epilogue); return B200_ERR_ARG;
     }
 }

@@ -450,7 +450,9 @@ enum EpiKind : int {
     EPI_ADD = 5,        // C = acc + aux (+bias)      residual / gradient accumulation
     EPI_SGD = 6,        // C = C - alpha * acc        in-place optimizer step on the weight tile (:114,:172)
     EPI_STORE_F32 = 7,  // C(fp32) = alpha * acc
-    EPI_COUNT = 8,
+    EPI_RELU_MASK = 8,      // RELU, plus a packed sign mask (1 bit per element, C2 as uint8 [M, ldc2 bytes]) for the backward
+    EPI_RELU_BWD_MASK = 9,  // C = acc where the mask bit is set, else 0 (aux = the uint8 mask, ldaux in bytes)
+    EPI_COUNT = 10,
 };
 
 struct LocalEpiParams {
@@ -557,6 +559,15 @@ struct LocalEpi {
             return;
         }
 
+        // packed ReLU sign mask: this lane's row, this warp's 128 columns = 16 bytes at mask[row][colbase / 8]
+        uint32_t mbits[4] = {0u, 0u, 0u, 0u};
+        const bool mrow_ok = (row0 + lane) < g.M;
+        if constexpr (KIND == EPI_RELU_BWD_MASK) {
+            if (mrow_ok) {
+                const uint4 mv = ld_nc_u4(reinterpret_cast<const uint8_t*>(p.aux) + (long long)(row0 + lane) * p.ldaux + colbase / 8);
+                mbits[0] = mv.x; mbits[1] = mv.y; mbits[2] = mv.z; mbits[3] = mv.w;
+            }
+        }
         uint4 rd_next[8];
         if constexpr (READS) coalesced_load_rows<KIND != EPI_SGD>(rd_next, lane, rd, rd_ld, row0, colbase, g.M, g.N);
 #pragma unroll 1
@@ -577,7 +588,7 @@ struct LocalEpi {
                 float f[8];
 #pragma unroll
                 for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(pc < 4 ? a0[pc * 8 + j] : a1[(pc - 4) * 8 + j]);
-                if constexpr (KIND == EPI_STORE || KIND == EPI_RELU || KIND == EPI_GELU || KIND == EPI_ADD) {
+                if constexpr (KIND == EPI_STORE || KIND == EPI_RELU || KIND == EPI_RELU_MASK || KIND == EPI_GELU || KIND == EPI_ADD) {
                     if (p.bias != nullptr) {
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
@@ -586,9 +597,17 @@ struct LocalEpi {
                         }
                     }
                 }
-                if constexpr (KIND == EPI_RELU) {
+                if constexpr (KIND == EPI_RELU || KIND == EPI_RELU_MASK) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) f[j] = f[j] <= 0.0f ? 0.0f : f[j];   // NaN stays NaN, like torch.where(x<=0,0,x)
+                    for (int j = 0; j < 8; ++j) {
+                        const bool keep = !(f[j] <= 0.0f);                           // NaN stays NaN, like torch.where(x<=0,0,x)
+                        if constexpr (KIND == EPI_RELU_MASK) mbits[cp * 2 + (pc >> 2)] |= (keep ? 1u : 0u) << ((pc & 3) * 8 + j);
+                        f[j] = keep ? f[j] : 0.0f;
+                    }
+                } else if constexpr (KIND == EPI_RELU_BWD_MASK) {
+                    const uint32_t w = mbits[cp * 2 + (pc >> 2)] >> ((pc & 3) * 8);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) f[j] = ((w >> j) & 1u) ? f[j] : 0.0f;   // masked_fill_(x <= 0, 0)
                 } else if constexpr (KIND == EPI_GELU) {
                     prev[pc].x = pack_bf16x2(f[0], f[1]); prev[pc].y = pack_bf16x2(f[2], f[3]);
                     prev[pc].z = pack_bf16x2(f[4], f[5]); prev[pc].w = pack_bf16x2(f[6], f[7]);
@@ -620,6 +639,10 @@ struct LocalEpi {
             if constexpr (KIND == EPI_GELU)
                 stage_store_rows(stage, lane, prev, p.C2, p.ldc2, row0, col0, g.M, g.N);
             stage_store_rows(stage, lane, outv, reinterpret_cast<__nv_bfloat16*>(p.C), p.ldc, row0, col0, g.M, g.N);
+        }
+        if constexpr (KIND == EPI_RELU_MASK) {
+            if (mrow_ok)
+                st_u4(reinterpret_cast<uint8_t*>(p.C2) + (long long)(row0 + lane) * p.ldc2 + colbase / 8, make_uint4(mbits[0], mbits[1], mbits[2], mbits[3]));
         }
     }
 };

@@ -142,7 +142,8 @@ def tlayer_ffn_bkwd(ops, dy: torch.Tensor, p: Params, saved: Saved, opts: BlockO
     a, pre = saved.a, saved.pre
     if a is None:                                   # recompute policy (:63, :66)
         a, pre = ops.linear_act(x, p[0], opts.activation, _bias(p, 0))
-    aux = a if opts.activation == "relu" else pre
+    # ReLU backward needs only the sign of h: the native ops hand back a packed bitmask in `pre`, else use `a` itself
+    aux = (pre if pre is not None else a) if opts.activation == "relu" else pre
     dh = ops.grad_input(dy, p[1], act=opts.activation, aux=aux)            # da then activation backward (:66-67)
     has_bias = len(p) == 4
     fused = update_lr is not None and not has_bias

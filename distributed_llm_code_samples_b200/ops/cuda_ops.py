@@ -21,6 +21,7 @@ class CudaOps(TorchOps):
         nv.load()
         self.max_ctas = max_ctas
         self.fallbacks = 0
+        self.relu_mask = True
 
     # ---- helpers -----------------------------------------------------------------------------------------
     @staticmethod
@@ -46,6 +47,11 @@ class CudaOps(TorchOps):
         a = torch.empty(T, N, dtype=torch.bfloat16, device=x.device)
         b32 = None if bias is None else bias.float().contiguous()
         if act == "relu":
+            if self.relu_mask and N % 128 == 0:
+                # also emit the packed sign mask (1 bit/element): the backward reads 1/16 of the bytes of `a`
+                mask = torch.empty(T, N // 8, dtype=torch.uint8, device=x.device)
+                nv.gemm(x, nv.MAJOR_K, W, nv.MAJOR_K, a, T, N, K, nv.EPI_RELU_MASK, out2=mask, bias=b32, max_ctas=self.max_ctas)
+                return a, mask
             nv.gemm(x, nv.MAJOR_K, W, nv.MAJOR_K, a, T, N, K, nv.EPI_RELU, bias=b32, max_ctas=self.max_ctas)
             return a, None
         pre = torch.empty_like(a)
@@ -69,10 +75,15 @@ class CudaOps(TorchOps):
     def grad_input(self, dy, W, act=None, aux=None, add=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         T, K = dy.shape           # K = out features of the layer
         N = W.shape[1]            # in features
-        if not self._ok(dy, W, aux, add) or N % 8 or (act is not None and add is not None):
+        mask_aux = aux is not None and aux.dtype == torch.uint8
+        if not self._ok(dy, W, None if mask_aux else aux, add) or N % 8 or (act is not None and add is not None):
+            if mask_aux:
+                raise nv.NativeError("grad_input: a packed ReLU mask can only be consumed by the native kernel")
             return self._fb().grad_input(dy, W, act, aux, add)
         dx = torch.empty(T, N, dtype=torch.bfloat16, device=dy.device) if out is None else out
-        if act == "relu":
+        if act == "relu" and aux.dtype == torch.uint8:
+            nv.gemm(dy, nv.MAJOR_K, W, nv.MAJOR_MN, dx, T, N, K, nv.EPI_RELU_BWD_MASK, aux=aux, max_ctas=self.max_ctas)
+        elif act == "relu":
             nv.gemm(dy, nv.MAJOR_K, W, nv.MAJOR_MN, dx, T, N, K, nv.EPI_RELU_BWD, aux=aux, max_ctas=self.max_ctas)
         elif act == "gelu":
             nv.gemm(dy, nv.MAJOR_K, W, nv.MAJOR_MN, dx, T, N, K, nv.EPI_GELU_BWD, aux=aux, max_ctas=self.max_ctas)

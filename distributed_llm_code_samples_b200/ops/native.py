@@ -21,7 +21,7 @@ _lock = threading.Lock()
 MAJOR_K = 0
 MAJOR_MN = 1
 
-EPI_STORE, EPI_RELU, EPI_GELU, EPI_RELU_BWD, EPI_GELU_BWD, EPI_ADD, EPI_SGD, EPI_STORE_F32 = range(8)
+EPI_STORE, EPI_RELU, EPI_GELU, EPI_RELU_BWD, EPI_GELU_BWD, EPI_ADD, EPI_SGD, EPI_STORE_F32, EPI_RELU_MASK, EPI_RELU_BWD_MASK = range(10)
 
 #: number of kernels this process launched through the native library (bench.py reports it)
 launch_count = 0
@@ -147,6 +147,7 @@ def gemm(A: torch.Tensor, a_major: int, B: torch.Tensor, b_major: int, out: torc
     global launch_count
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
     assert A.stride(-1) == 1 and B.stride(-1) == 1 and out.stride(-1) == 1
+    # (for the mask epilogues aux / out2 are uint8 [M, bytes]: stride(0) is then a pitch in bytes, as the C ABI wants)
     rc = load().b200_gemm_bf16(
         A.data_ptr(), A.stride(0), a_major, B.data_ptr(), B.stride(0), b_major, out.data_ptr(), out.stride(0),
         M, N, K, epilogue, _ptr(aux), aux.stride(0) if aux is not None else 0, _ptr(out2),

@@ -104,7 +104,7 @@ class FusedDDPTrainer:
             a, pre = s.a, s.pre
             if a is None:
                 a, pre = ops.linear_act(s.x, W1, self.opts.activation)
-            dh = ops.grad_input(d, W2, act=self.opts.activation, aux=a if self.opts.activation == "relu" else pre)
+            dh = ops.grad_input(d, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
             # dW2 = d^T a  summed over ranks, W2 -= lr * dW2, new W2 stored to every replica - one kernel
             self.chan.gemm(d, nv.MAJOR_MN, a, nv.MAJOR_MN, D, F, T, self.peer_tabs[i][1], F, 0, OWN_INTERLEAVED, FOP_SGD, True, self.lr)
             dn = ops.grad_input(dh, W1, add=d if self.opts.residual else None) if i > 0 else None
@@ -201,7 +201,7 @@ class FusedFSDPTrainer:
             a, pre = s.a, s.pre
             if a is None:
                 a, pre = ops.linear_act(s.x, W1, self.opts.activation)
-            dh = ops.grad_input(d, W2, act=self.opts.activation, aux=a if self.opts.activation == "relu" else pre)
+            dh = ops.grad_input(d, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
             # dW2 rows [r*D/n, (r+1)*D/n) summed over ranks and applied to MY shard of W2 - one kernel, no broadcast
             self.chan.gemm(d, nv.MAJOR_MN, a, nv.MAJOR_MN, D, F, T, self.local_out[2 * i + 1], F, r * (D // n), OWN_ROW_SHARDED, FOP_SGD, False, self.lr)
             dn = ops.grad_input(dh, W1, add=d if self.opts.residual else None) if i > 0 else None
@@ -285,7 +285,7 @@ class FusedMPTrainer:
             xin, a, pre = saved[i]
             if a is None:
                 a, pre = ops.linear_act(xin, W1, self.opts.activation)
-            dh = ops.grad_input(d, W2, act=self.opts.activation, aux=a if self.opts.activation == "relu" else pre)
+            dh = ops.grad_input(d, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
             ops.grad_weight_sgd_(W2, d, a, self.lr)                       # shard-local, no communication (:311-312)
             dn = None
             if i > 0:

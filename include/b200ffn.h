@@ -42,6 +42,9 @@ int b200_num_sms(void);
  *   1 RELU       C = relu(acc + bias)                 5 ADD       C = acc + aux (+bias)
  *   2 GELU       C = gelu(acc+bias), C2 = acc+bias    6 SGD       C = C - alpha*acc   (in place on the weight)
  *   3 RELU_BWD   C = acc * (aux > 0)                  7 STORE_F32 C(fp32) = alpha*acc
+ *   8 RELU_MASK      as RELU, and C2 (uint8 [M, ldc2 BYTES], ldc2 % 16 == 0) receives one sign bit per element
+ *   9 RELU_BWD_MASK  C = acc where the bit in aux (that mask, ldaux in BYTES) is set, else 0 - the backward of
+ *                    ReLU (:50-52) from 1 bit/element instead of re-reading the bf16 activation
  * Preconditions: 16-byte aligned bases; lda, ldb, ldc, ldaux, ldc2 and N multiples of 8 elements.
  * max_ctas: 0 = one CTA per SM; >0 caps the persistent grid (leaves SMs for a concurrent comm kernel). */
 #define B200_EPI_STORE 0
@@ -52,6 +55,8 @@ int b200_num_sms(void);
 #define B200_EPI_ADD 5
 #define B200_EPI_SGD 6
 #define B200_EPI_STORE_F32 7
+#define B200_EPI_RELU_MASK 8
+#define B200_EPI_RELU_BWD_MASK 9
 int b200_gemm_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
                    void* C, long long ldc, int M, int N, int K, int epilogue, const void* aux, long long ldaux,
                    void* C2, long long ldc2, const float* bias, float alpha, int max_ctas, void* stream);

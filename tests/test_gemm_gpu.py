@@ -85,6 +85,23 @@ def test_epilogues(cuda_device):
     assert (o32 - 0.5 * ref).abs().max().item() < 1e-2
 
 
+@pytest.mark.parametrize("M,N,K", [(384, 512, 320), (200, 384, 136), (1024, 1280, 512)])
+def test_relu_bitmask_epilogues(cuda_device, M, N, K):
+    """ReLU forward that also packs the sign mask (1 bit/element) and the backward that consumes it (:47-52)."""
+    x, w = _rand((M, K), cuda_device, seed=31), _rand((N, K), cuda_device, 0.1, seed=32)
+    ref = x.float() @ w.float().T
+    a = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
+    mask = torch.zeros(M, N // 8, dtype=torch.uint8, device=cuda_device)
+    nv.gemm(x, 0, w, 0, a, M, N, K, nv.EPI_RELU_MASK, out2=mask)
+    _check(a, torch.relu(ref), K, "relu+mask")
+    bits = ((mask.unsqueeze(-1) >> torch.arange(8, device=cuda_device, dtype=torch.uint8)) & 1).reshape(M, N).bool()
+    assert torch.equal(bits, a > 0)
+    dy, w2 = _rand((M, K), cuda_device, seed=33), _rand((K, N), cuda_device, 0.1, seed=34)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
+    nv.gemm(dy, 0, w2, 1, out, M, N, K, nv.EPI_RELU_BWD_MASK, aux=mask)
+    _check(out, (dy.float() @ w2.float()) * bits, K, "relu_bwd from mask")
+
+
 def test_gemm_strided_views(cuda_device):
     """Operands that are column slices of bigger tensors (leading dimension != row length)."""
     M, N, K = 256, 256, 128
