@@ -38,8 +38,8 @@ __device__ __forceinline__ void block_barrier(const PeerTable& flags, int rank, 
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(32) barrier_kernel(PeerTable flags, int rank, int world, uint32_t epoch, unsigned int* err) {
-    block_barrier(flags, rank, world, 3 * epoch + 1, err);
+__global__ void __launch_bounds__(32) barrier_kernel(PeerTable flags, int rank, int world, uint32_t value, unsigned int* err) {
+    block_barrier(flags, rank, world, value, err);
 }
 
 __device__ __forceinline__ void add8(float (&acc)[8], const uint4& v) {
@@ -51,6 +51,25 @@ __device__ __forceinline__ uint4 pack8f(const float (&f)[8]) {
     o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
     o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
     return o;
+}
+
+// Copy vectors [lo, hi) with CU independent 16-byte loads in flight per thread (peer reads have ~2 us latency: one
+// load at a time would cap a 32-CTA kernel near 50 GB/s).
+constexpr int CU = 8;
+__device__ __forceinline__ void copy_batched(uint4* dst, const uint4* src, long long lo, long long hi, long long t0, long long tstride) {
+    for (long long i = lo + t0; i < hi; i += tstride * CU) {
+        uint4 v[CU];
+#pragma unroll
+        for (int u = 0; u < CU; ++u) {
+            const long long idx = i + u * tstride;
+            if (idx < hi) v[u] = ld_cv_u4(src + idx);
+        }
+#pragma unroll
+        for (int u = 0; u < CU; ++u) {
+            const long long idx = i + u * tstride;
+            if (idx < hi) st_u4(dst + idx, v[u]);
+        }
+    }
 }
 
 // slice s of V 16-byte vectors split over `world` ranks
@@ -92,14 +111,26 @@ __global__ void __launch_bounds__(COLL_THREADS) coll_kernel(PeerTable buf, long 
     if (MODE == 0 || MODE == 1) {
         long long lo, hi;
         slice_bounds(V, world, rank, lo, hi);
-        for (long long i = lo + t0; i < hi; i += tstride) {
-            float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#pragma unroll 4
-            for (int q = 0; q < world; ++q) {                  // fixed order: deterministic sum
-                const uint4* src = reinterpret_cast<const uint4*>(sbuf[q] + offset_bytes);
-                add8(acc, ld_cv_u4(src + i));
+        constexpr int RU = 2;
+        for (long long i = lo + t0; i < hi; i += tstride * RU) {
+            uint4 v[RU][MAX_WORLD];
+#pragma unroll
+            for (int u = 0; u < RU; ++u) {
+                const long long idx = i + u * tstride;
+#pragma unroll
+                for (int q = 0; q < MAX_WORLD; ++q)
+                    if (q < world && idx < hi) v[u][q] = ld_cv_u4(reinterpret_cast<const uint4*>(sbuf[q] + offset_bytes) + idx);
             }
-            st_u4(mine + i, pack8f(acc));
+#pragma unroll
+            for (int u = 0; u < RU; ++u) {
+                const long long idx = i + u * tstride;
+                if (idx >= hi) continue;
+                float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+                for (int q = 0; q < MAX_WORLD; ++q)            // fixed order: deterministic sum
+                    if (q < world) add8(acc, v[u][q]);
+                st_u4(mine + idx, pack8f(acc));
+            }
         }
     }
     if (MODE == 0) block_barrier(flags, rank, world, 3 * epoch + 2, err);   // all slices reduced and visible
@@ -109,7 +140,7 @@ __global__ void __launch_bounds__(COLL_THREADS) coll_kernel(PeerTable buf, long 
             long long lo, hi;
             slice_bounds(V, world, q, lo, hi);
             const uint4* src = reinterpret_cast<const uint4*>(sbuf[q] + offset_bytes);
-            for (long long i = lo + t0; i < hi; i += tstride) st_u4(mine + i, ld_cv_u4(src + i));
+            copy_batched(mine, src, lo, hi, t0, tstride);
         }
     }
     block_barrier(flags, rank, world, 3 * epoch + 3, err);     // peers are done reading my buffer
@@ -130,7 +161,7 @@ __global__ void __launch_bounds__(COLL_THREADS) gather_into_kernel(uint4* dst, P
         const int q = (rank + dq) % world;
         const uint4* s = reinterpret_cast<const uint4*>(sbuf[q] + src_offset_bytes);
         uint4* d = dst + (long long)q * Vs;
-        for (long long i = t0; i < Vs; i += tstride) st_u4(d + i, ld_cv_u4(s + i));
+        copy_batched(d, s, 0, Vs, t0, tstride);
     }
     block_barrier(flags, rank, world, 3 * epoch + 3, err);     // peers have finished reading my shard
 }
@@ -153,8 +184,8 @@ static int coll_launch(int mode, void* const* peers, long long offset_bytes, lon
     if (bytes <= 0 || (bytes % 16) || (offset_bytes % 16) || offset_bytes < 0) { set_last_error("%s: offset and size must be multiples of 16 bytes", what); return B200_ERR_ARG; }
     const long long V = bytes / 16;
     if (blocks <= 0) {
-        const long long want = (V / world + COLL_THREADS - 1) / COLL_THREADS;
-        blocks = (int)(want < 1 ? 1 : (want > 32 ? 32 : want));
+        const long long want = (V / world + COLL_THREADS * 4 - 1) / (COLL_THREADS * 4);
+        blocks = (int)(want < 1 ? 1 : (want > COLL_MAX_BLOCKS ? COLL_MAX_BLOCKS : want));
     }
     if (blocks > COLL_MAX_BLOCKS) blocks = COLL_MAX_BLOCKS;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
@@ -214,7 +245,7 @@ extern "C" int b200_enable_peer_access(int peer_device) {
 extern "C" int b200_barrier(void* const* flag_peers, int rank, int world, unsigned int epoch, void* stream) {
     PeerTable flags;
     if (int rc = make_table(&flags, flag_peers, world, "barrier")) return rc;
-    barrier_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(flags, rank, world, epoch, device_error_slot());
+    barrier_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(flags, rank, world, 3 * epoch + 1, device_error_slot());
     return check_cuda(cudaGetLastError(), "barrier launch");
 }
 extern "C" int b200_all_reduce_bf16(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
@@ -240,12 +271,36 @@ extern "C" int b200_all_gather_into(void* dst, void* const* src_peers, long long
     if (rank < 0 || rank >= world) { set_last_error("all_gather_into: bad rank"); return B200_ERR_ARG; }
     const long long Vs = shard_bytes / 16;
     if (blocks <= 0) {
-        const long long want = (Vs + COLL_THREADS - 1) / COLL_THREADS;
-        blocks = (int)(want < 1 ? 1 : (want > 32 ? 32 : want));
+        const long long want = (Vs + COLL_THREADS * 4 - 1) / (COLL_THREADS * 4);
+        blocks = (int)(want < 1 ? 1 : (want > COLL_MAX_BLOCKS ? COLL_MAX_BLOCKS : want));
     }
     if (blocks > COLL_MAX_BLOCKS) blocks = COLL_MAX_BLOCKS;
     gather_into_kernel<<<blocks, COLL_THREADS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(reinterpret_cast<uint4*>(dst), src, src_offset_bytes, Vs,
                                                                                            flags, rank, world, epoch, device_error_slot());
     return check_cuda(cudaGetLastError(), "all_gather_into launch");
+}
+// Same contract as b200_all_gather_into, but the bytes move on the COPY ENGINES (peer-to-peer DMA over NVLink): no SM
+// is used, so the gather overlaps a GEMM that owns every SM's registers and shared memory.  Two one-warp barrier
+// kernels order it against the peers: before (every peer's shard is final) and after (every peer has finished
+// reading mine).  This is the FSDP parameter prefetch (train_ffns.py:203, :236-249).
+extern "C" int b200_all_gather_into_dma(void* dst, void* const* src_peers, long long src_offset_bytes, long long shard_bytes,
+                                        void* const* flag_peers, int rank, int world, unsigned int epoch, void* stream) {
+    PeerTable src, flags;
+    if (int rc = make_table(&src, src_peers, world, "all_gather_into_dma")) return rc;
+    if (int rc = make_table(&flags, flag_peers, world, "all_gather_into_dma")) return rc;
+    if (dst == nullptr || shard_bytes <= 0 || src_offset_bytes < 0) { set_last_error("all_gather_into_dma: bad arguments"); return B200_ERR_ARG; }
+    if (rank < 0 || rank >= world) { set_last_error("all_gather_into_dma: bad rank"); return B200_ERR_ARG; }
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    unsigned int* err = device_error_slot();
+    barrier_kernel<<<1, 32, 0, st>>>(flags, rank, world, 3 * epoch + 1, err);
+    if (int rc = check_cuda(cudaGetLastError(), "all_gather_into_dma barrier")) return rc;
+    for (int dq = 0; dq < world; ++dq) {
+        const int q = (rank + dq) % world;                 // staggered: ranks pull from different peers at any moment
+        const char* s = reinterpret_cast<const char*>(src.p[q]) + src_offset_bytes;
+        char* d = reinterpret_cast<char*>(dst) + (long long)q * shard_bytes;
+        if (int rc = check_cuda(cudaMemcpyAsync(d, s, (size_t)shard_bytes, cudaMemcpyDeviceToDevice, st), "all_gather_into_dma copy")) return rc;
+    }
+    barrier_kernel<<<1, 32, 0, st>>>(flags, rank, world, 3 * epoch + 3, err);
+    return check_cuda(cudaGetLastError(), "all_gather_into_dma barrier");
 }
 extern "C" long long b200_coll_flag_bytes(void) { return (long long)COLL_MAX_BLOCKS * MAX_WORLD * 4; }

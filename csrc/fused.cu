@@ -88,19 +88,15 @@ __device__ __forceinline__ uint4 pack_row8(const uint32_t* a) {
 struct FusedEpi {
     using Params = FusedParams;
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
+    static constexpr int EXTRA_WARPS = 2;      // the two spare warps of warpgroup 0 reduce owned tiles under the MMAs
     struct State {
-        int cursor;      // next owned tile (index into this CTA's list) this warp has not reduced yet
-        int k_local;     // inbox slot of the tile being pushed
+        int k_local;               // inbox slot of the tile being pushed
         int owner;
     };
 
-    static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx& ctx, State& st) {
-        st.cursor = 0;
+    static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx&, State& st) {
         st.k_local = 0;
         st.owner = 0;
-        if (ctx.ewarp == 0)
-            for (int i = ctx.lane; i < MAX_OWNED_PER_CTA; i += 32) ctx.scratch[i] = 0;
-        epi_group_sync();
     }
 
     // ---- push this warp's 32 rows x 128 columns of the accumulator into the owner's inbox ------------------
@@ -139,18 +135,15 @@ struct FusedEpi {
             __threadfence_system();
             st_release_sys(p.flags[st.owner] + (size_t)st.k_local * MAX_WORLD_F + p.rank, p.seq);
         }
-        drain(p, g, ctx, st, /*block=*/false);
     }
 
     // a pair kernel's CTA whose half of the 256-row tile lies beyond M: nothing to push, but keep the epilogue
     // warps in step (the group barrier in after_tile is counted per tile) and use the time to reduce
-    static __device__ __forceinline__ void after_skipped_tile(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st) {
+    static __device__ __forceinline__ void after_skipped_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {
         epi_group_sync();
-        drain(p, g, ctx, st, /*block=*/false);
     }
 
-    static __device__ __forceinline__ void tail(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st) {
-        drain(p, g, ctx, st, /*block=*/true);
+    static __device__ __forceinline__ void tail(const Params& p, const GemmCore& g, const EpiCtx& ctx, State&) {
         if (p.broadcast) {                                           // every tile of MY output has been delivered
             const int num_tiles = g.tiles_m * g.tiles_n;
             for (int t = blockIdx.x + ctx.ewarp * gridDim.x; t < num_tiles; t += gridDim.x * EPI_WARPS)
@@ -168,62 +161,104 @@ struct FusedEpi {
         return __all_sync(0xffffffffu, ok);
     }
 
-    static __device__ __forceinline__ void drain(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st, bool block) {
-        while (true) {
-            const int k = blockIdx.x + st.cursor * gridDim.x;
-            if (k >= p.owned_count) return;
-            if (!arrived(p, g, k, ctx.lane, block)) return;
-            reduce_rows(p, g, k, ctx.ewarp, ctx.lane);
-            __threadfence_system();                                  // my results are visible system-wide ...
-            __syncwarp();
-            unsigned int prev = 0;
-            if (ctx.lane == 0) prev = atomicAdd(&ctx.scratch[st.cursor % MAX_OWNED_PER_CTA], 1u);   // ... before I count
-            prev = __shfl_sync(0xffffffffu, prev, 0);
-            if (prev == EPI_WARPS - 1 && p.broadcast) {              // last of the 8 warps publishes the tile
-                int m_blk, n_blk;
-                owned_tile_coords(p, g, k, m_blk, n_blk);
-                __threadfence_system();
-                if (ctx.lane < p.world) st_release_sys(p.flags[ctx.lane] + p.ready_base + m_blk * g.tiles_n + n_blk, p.seq);
+    // Side warps: reduce this CTA's owned tiles as their partials land - in ANY order (ranks may walk their tiles in
+    // different orders), concurrently with the TMA/MMA/epilogue warps.  Returns when all of them are done.
+    static __device__ __forceinline__ void side_loop(const Params& p, const GemmCore& g, int swarp, int lane, uint32_t* scratch) {
+        const int n_mine = (int)blockIdx.x < p.owned_count ? (p.owned_count - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+        unsigned long long done = 0ull;
+        int remaining = n_mine;
+        long long t0 = clock64();
+        while (remaining > 0) {
+            bool progressed = false;
+            for (int j = 0; j < n_mine; ++j) {
+                if ((done >> j) & 1ull) continue;
+                const int k = blockIdx.x + j * gridDim.x;
+                if (!arrived(p, g, k, lane, /*block=*/false)) continue;
+                reduce_rows(p, g, k, swarp, lane);
+                done |= 1ull << j;
+                --remaining;
+                progressed = true;
+                __threadfence_system();                              // my results are visible system-wide ...
+                __syncwarp();
+                unsigned int prev = 0;
+                if (lane == 0) prev = atomicAdd(&scratch[j], 1u);    // ... before I count
+                prev = __shfl_sync(0xffffffffu, prev, 0);
+                if (prev == EXTRA_WARPS - 1 && p.broadcast) {        // the last side warp to finish the tile publishes it
+                    int m_blk, n_blk;
+                    owned_tile_coords(p, g, k, m_blk, n_blk);
+                    __threadfence_system();
+                    if (lane < p.world) st_release_sys(p.flags[lane] + p.ready_base + m_blk * g.tiles_n + n_blk, p.seq);
+                }
             }
-            ++st.cursor;
+            if (!progressed) {
+                __nanosleep(200);
+                if ((clock64() - t0) > B200_FLAG_TIMEOUT_CYCLES) device_fail(g.err, ERR_FLAG_TIMEOUT, 0x680);
+            } else {
+                t0 = clock64();
+            }
         }
     }
 
-    // one warp's 16 rows of owned tile k: sum the `world` partials, apply the op, store (and broadcast)
-    static __device__ __forceinline__ void reduce_rows(const Params& p, const GemmCore& g, int k_local, int ewarp, int lane) {
+    // one side warp's 64 rows of owned tile k: sum the `world` partials, apply the op, store (and broadcast).
+    // Two rows at a time with every source's load issued before the first add, so up to 2*world 16-byte loads are
+    // in flight per lane instead of one.
+    static __device__ __forceinline__ void reduce_rows(const Params& p, const GemmCore& g, int k_local, int swarp, int lane) {
+        constexpr int ROWS = BM / EXTRA_WARPS;
         int m_blk, n_blk;
         owned_tile_coords(p, g, k_local, m_blk, n_blk);
         const __nv_bfloat16* inb = reinterpret_cast<const __nv_bfloat16*>(p.inbox[p.rank]);
         const int col = n_blk * BN + lane * 8;                       // 32 lanes x 8 columns = one 256-wide row
+        if (col >= g.N) return;
+        constexpr int RB = 2;
 #pragma unroll 1
-        for (int r = 0; r < BM / EPI_WARPS; ++r) {
-            const int row_in_tile = ewarp * (BM / EPI_WARPS) + r;
-            const int grow = m_blk * BM + row_in_tile;
-            if (grow >= g.M || col >= g.N) continue;
-            float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-            for (int s = 0; s < p.world; ++s) {                      // fixed order: deterministic, rank-independent
-                const uint4 v = ld_cv_u4(inb + inbox_slot(p, k_local, s) + (size_t)row_in_tile * BN + lane * 8);
-                acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
-                acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z); acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
+        for (int r0 = 0; r0 < ROWS; r0 += RB) {
+            uint4 v[RB][MAX_WORLD_F];
+#pragma unroll
+            for (int rr = 0; rr < RB; ++rr) {
+                const int row_in_tile = swarp * ROWS + r0 + rr;
+#pragma unroll
+                for (int s = 0; s < MAX_WORLD_F; ++s)
+                    if (s < p.world) v[rr][s] = ld_cv_u4(inb + inbox_slot(p, k_local, s) + (size_t)row_in_tile * BN + lane * 8);
             }
-            const size_t off = (size_t)(grow - p.out_row_offset) * p.ldo + col;
-            if (p.op == FOP_SGD) {
-                const uint4 w = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.out[p.rank]) + off);
-                acc[0] = bf16_lo(w.x) - p.alpha * acc[0]; acc[1] = bf16_hi(w.x) - p.alpha * acc[1];
-                acc[2] = bf16_lo(w.y) - p.alpha * acc[2]; acc[3] = bf16_hi(w.y) - p.alpha * acc[3];
-                acc[4] = bf16_lo(w.z) - p.alpha * acc[4]; acc[5] = bf16_hi(w.z) - p.alpha * acc[5];
-                acc[6] = bf16_lo(w.w) - p.alpha * acc[6]; acc[7] = bf16_hi(w.w) - p.alpha * acc[7];
+            uint4 w[RB];
+#pragma unroll
+            for (int rr = 0; rr < RB; ++rr) {
+                const int grow = m_blk * BM + swarp * ROWS + r0 + rr;
+                if (p.op == FOP_SGD && grow < g.M)
+                    w[rr] = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.out[p.rank]) + (size_t)(grow - p.out_row_offset) * p.ldo + col);
             }
-            uint4 o;
-            o.x = pack_bf16x2(acc[0], acc[1]); o.y = pack_bf16x2(acc[2], acc[3]);
-            o.z = pack_bf16x2(acc[4], acc[5]); o.w = pack_bf16x2(acc[6], acc[7]);
-            if (p.broadcast) {
-                for (int d = 0; d < p.world; ++d) {
-                    const int q = (p.rank + d) % p.world;            // local first, then peers, staggered
-                    st_u4(reinterpret_cast<__nv_bfloat16*>(p.out[q]) + off, o);
+#pragma unroll
+            for (int rr = 0; rr < RB; ++rr) {
+                const int grow = m_blk * BM + swarp * ROWS + r0 + rr;
+                if (grow >= g.M) continue;
+                float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+                for (int s = 0; s < MAX_WORLD_F; ++s) {              // fixed order: deterministic, rank-independent
+                    if (s < p.world) {
+                        const uint4 x = v[rr][s];
+                        acc[0] += bf16_lo(x.x); acc[1] += bf16_hi(x.x); acc[2] += bf16_lo(x.y); acc[3] += bf16_hi(x.y);
+                        acc[4] += bf16_lo(x.z); acc[5] += bf16_hi(x.z); acc[6] += bf16_lo(x.w); acc[7] += bf16_hi(x.w);
+                    }
                 }
-            } else {
-                st_u4(reinterpret_cast<__nv_bfloat16*>(p.out[p.rank]) + off, o);
+                const size_t off = (size_t)(grow - p.out_row_offset) * p.ldo + col;
+                if (p.op == FOP_SGD) {
+                    const uint4 ww = w[rr];
+                    acc[0] = bf16_lo(ww.x) - p.alpha * acc[0]; acc[1] = bf16_hi(ww.x) - p.alpha * acc[1];
+                    acc[2] = bf16_lo(ww.y) - p.alpha * acc[2]; acc[3] = bf16_hi(ww.y) - p.alpha * acc[3];
+                    acc[4] = bf16_lo(ww.z) - p.alpha * acc[4]; acc[5] = bf16_hi(ww.z) - p.alpha * acc[5];
+                    acc[6] = bf16_lo(ww.w) - p.alpha * acc[6]; acc[7] = bf16_hi(ww.w) - p.alpha * acc[7];
+                }
+                uint4 o;
+                o.x = pack_bf16x2(acc[0], acc[1]); o.y = pack_bf16x2(acc[2], acc[3]);
+                o.z = pack_bf16x2(acc[4], acc[5]); o.w = pack_bf16x2(acc[6], acc[7]);
+                if (p.broadcast) {
+                    for (int d = 0; d < p.world; ++d) {
+                        const int q = (p.rank + d) % p.world;        // local first, then peers, staggered
+                        st_u4(reinterpret_cast<__nv_bfloat16*>(p.out[q]) + off, o);
+                    }
+                } else {
+                    st_u4(reinterpret_cast<__nv_bfloat16*>(p.out[p.rank]) + off, o);
+                }
             }
         }
     }
@@ -284,5 +319,8 @@ extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_majo
     int grid = tm * tn < grid_cap ? tm * tn : grid_cap;
     if ((p.owned_count + grid - 1) / grid > MAX_OWNED_PER_CTA) { set_last_error("gemm_allreduce: too many owned tiles per CTA"); return B200_ERR_ARG; }
     // every rank must use the same grid: owned tile k is reduced by CTA k %% grid on its owner
-    return launch_gemm<FusedEpi>(o, p, max_ctas, reinterpret_cast<cudaStream_t>(stream), rank, world);
+    // Interleaved owners already spread consecutive tiles over ranks; row-sharded owners would make every rank push to
+    // the same owner at once, so there each rank starts its walk at a different offset.
+    const int rot = owner_mode == OWN_ROW_SHARDED ? rank : 0;
+    return launch_gemm<FusedEpi>(o, p, max_ctas, reinterpret_cast<cudaStream_t>(stream), rot, world);
 }

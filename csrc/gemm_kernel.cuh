@@ -90,6 +90,10 @@ __device__ __forceinline__ SmemView carve_smem(uint8_t* raw) {
 //   static __device__ void after_tile(const Params&, const GemmCore&, const EpiCtx&, State&)
 //        runs after the accumulator stage has been handed back to the MMA warp (signals, opportunistic work)
 //   static __device__ void tail(const Params&, const GemmCore&, const EpiCtx&, State&)   (after the last tile)
+//   (with EXTRA_WARPS > 0 the launch bound is one warp larger than the launch, which caps registers at 152/thread and
+//    leaves room on every SM for a one-warp barrier kernel of a concurrent stream)
+//   static constexpr int EXTRA_WARPS;  static __device__ void side_loop(Params, GemmCore, side_warp, lane, scratch)
+//        extra warps (between the MMA warp and the epilogue warps) that run side_loop concurrently with the GEMM
 // ---------------------------------------------------------------------------------------------
 struct EpiCtx {
     int tile;        // linear tile index in the scheduler's order
@@ -104,7 +108,7 @@ struct EpiCtx {
 };
 
 template <class Epi>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + (Epi::EXTRA_WARPS ? 32 : 0), 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmCore g, const typename Epi::Params ep) {
     extern __shared__ uint8_t smem_raw[];
@@ -129,6 +133,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
         fence_mbar_init();
     }
+    if (threadIdx.x >= 64 && threadIdx.x < 128)       // 256-byte scratch shared by epilogue / side warps starts at zero
+        reinterpret_cast<uint32_t*>(sm.epi_stage + EPI_WARPS * EPI_STAGE_BYTES)[threadIdx.x - 64] = 0u;
     if (warp == 1) tmem_alloc_512(sm.tmem_base);
     tc_fence_before();
     __syncthreads();
@@ -205,12 +211,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             if (++as == 2) { as = 0; aphase ^= 1; }
         }
-    } else if (warp >= 2) {
+    } else if (warp >= 2 && warp < 2 + Epi::EXTRA_WARPS) {
+        // ===================== side warps (policy-defined work that runs under the MMAs) =====================
+        Epi::side_loop(ep, g, warp - 2, lane, reinterpret_cast<uint32_t*>(sm.epi_stage + EPI_WARPS * EPI_STAGE_BYTES));
+    } else if (warp >= 2 + Epi::EXTRA_WARPS) {
         // ===================== epilogue (8 warps: TMEM lane quarter x column half) =====================
         EpiCtx ctx;
-        ctx.ewarp = warp - 2;
+        ctx.ewarp = warp - 2 - Epi::EXTRA_WARPS;
         ctx.q = warp & 3;                                        // tcgen05.ld lane window = warp_id % 4
-        ctx.half = (warp - 2) >> 2;
+        ctx.half = ctx.ewarp >> 2;
         ctx.lane = lane;
         ctx.stage = sm.epi_stage + ctx.ewarp * EPI_STAGE_BYTES;
         ctx.scratch = reinterpret_cast<uint32_t*>(sm.epi_stage + EPI_WARPS * EPI_STAGE_BYTES);
@@ -261,7 +270,7 @@ constexpr int P_STAGE_BYTES = P_A_STAGE_BYTES + P_B_STAGE_BYTES;
 static_assert(P_STAGES * P_STAGE_BYTES == STAGES * STAGE_BYTES, "both variants use the same smem carve-up");
 
 template <class Epi>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + (Epi::EXTRA_WARPS ? 32 : 0), 1)
 gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const GemmCore g, const typename Epi::Params ep) {
     extern __shared__ uint8_t smem_raw[];
@@ -298,6 +307,8 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         mbar_init(&tmem_empty[1], 2 * EPI_WARPS);
         fence_mbar_init();
     }
+    if (threadIdx.x >= 64 && threadIdx.x < 128)       // 256-byte scratch shared by epilogue / side warps starts at zero
+        reinterpret_cast<uint32_t*>(epi_stage + EPI_WARPS * EPI_STAGE_BYTES)[threadIdx.x - 64] = 0u;
     if (warp == 1) tmem_alloc_512_pair(tmem_slot);
     tc_fence_before();
     cluster_sync_all();                               // barriers + TMEM of both CTAs exist before any cross-CTA traffic
@@ -388,12 +399,15 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             }
             tphase ^= 1;
         }
-    } else if (warp >= 2) {
+    } else if (warp >= 2 && warp < 2 + Epi::EXTRA_WARPS) {
+        // ===================== side warps (policy-defined work that runs under the MMAs) =====================
+        Epi::side_loop(ep, g, warp - 2, lane, reinterpret_cast<uint32_t*>(epi_stage + EPI_WARPS * EPI_STAGE_BYTES));
+    } else if (warp >= 2 + Epi::EXTRA_WARPS) {
         // ===================== epilogue (8 warps per CTA) =====================
         EpiCtx ctx;
-        ctx.ewarp = warp - 2;
+        ctx.ewarp = warp - 2 - Epi::EXTRA_WARPS;
         ctx.q = warp & 3;
-        ctx.half = (warp - 2) >> 2;
+        ctx.half = ctx.ewarp >> 2;
         ctx.lane = lane;
         ctx.stage = epi_stage + ctx.ewarp * EPI_STAGE_BYTES;
         ctx.scratch = reinterpret_cast<uint32_t*>(epi_stage + EPI_WARPS * EPI_STAGE_BYTES);
@@ -524,6 +538,8 @@ template <int KIND>
 struct LocalEpi {
     using Params = LocalEpiParams;
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
+    static constexpr int EXTRA_WARPS = 0;
+    static __device__ __forceinline__ void side_loop(const Params&, const GemmCore&, int, int, uint32_t*) {}
     // a second bf16 [M,N] operand is read by these epilogues: aux, or (SGD) the weight tile itself
     static constexpr bool READS = (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD || KIND == EPI_SGD);
     struct State {};
@@ -663,10 +679,13 @@ bool use_pair_kernel();   // runtime switch (B200_GEMM_PAIR=0 selects the 1-CTA 
 
 template <class Epi>
 int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_ctas, cudaStream_t stream,
-                int tile_offset_num = 0, int tile_offset_den = 1) {
+                int tile_offset_num = 0, int tile_offset_den = 1, bool overlap_epilogue = false) {
     GemmCore core;
     alignas(64) CUtensorMap tmA, tmB;
-    const bool pair = use_pair_kernel();
+    // overlap_epilogue: the epilogue is long (peer-memory pushes, cross-rank reduction), so use the kernel whose two
+    // 128x256 accumulator stages let it run under the next tile's MMAs, rather than the 256x256-per-CTA pair kernel
+    // whose single accumulator set leaves the epilogue exposed.
+    const bool pair = use_pair_kernel() && !overlap_epilogue;
     int rc = make_core_and_maps(o, &core, &tmA, &tmB, pair);
     if (rc != 0) return rc;
     static unsigned long long attr_mask = 0;   // per template instantiation, one bit per device
@@ -686,7 +705,7 @@ int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_c
         const int tiles = core.tiles_m * core.tiles_n;
         core.tile_offset = (int)((long long)tiles * tile_offset_num / tile_offset_den);
         int grid = tiles < cap ? tiles : cap;
-        gemm_tcgen05_kernel<Epi><<<grid, GEMM_THREADS, Epi::SMEM_BYTES, stream>>>(tmA, tmB, core, ep);
+        gemm_tcgen05_kernel<Epi><<<grid, GEMM_THREADS + 32 * Epi::EXTRA_WARPS, Epi::SMEM_BYTES, stream>>>(tmA, tmB, core, ep);
         return check_cuda(cudaGetLastError(), "gemm launch");
     }
     const int pair_tiles = ((core.tiles_m + 3) / 4) * core.tiles_n;      // 512 x 256 per CTA pair
@@ -696,7 +715,7 @@ int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_c
     if (pairs > pair_tiles) pairs = pair_tiles;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(2 * pairs);
-    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.blockDim = dim3(GEMM_THREADS + 32 * Epi::EXTRA_WARPS);
     cfg.dynamicSmemBytes = Epi::SMEM_BYTES;
     cfg.stream = stream;
     cudaLaunchAttribute at[1];

@@ -98,6 +98,7 @@ def _optional_declare(lib) -> None:
         "b200_all_gather_into": ([vp, pp, ll, ll, pp, i, i, u, i, vp], i),
         "b200_sumsq_static_max_elems": ([], ll),
         "b200_sumsq_bf16_static": ([vp, vp, ll, vp], i),
+        "b200_all_gather_into_dma": ([vp, pp, ll, ll, pp, i, i, u, vp], i),
         "b200_fused_inbox_bytes": ([i, i], ll),
         "b200_fused_flag_bytes": ([i, i], ll),
         "b200_fused_owned_tiles": ([i, i, i, i], i),

@@ -12,6 +12,7 @@ collectives (``csrc/comm.cu``) - no NCCL on the data path.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Iterable, List, Optional, Tuple
 
 import torch
@@ -123,7 +124,7 @@ class FusedDDPTrainer:
 
 # =================================================================================================== FSDP
 class FusedFSDPTrainer:
-    comm_name = "fused: dW GEMM + reduce-scatter + sharded SGD in one kernel; native pull all-gather prefetch"
+    comm_name = "fused: dW GEMM + reduce-scatter + sharded SGD in one kernel; P2P-DMA all-gather prefetch"
 
     def __init__(self, ops, comm, cfg: TrainConfig, shards: List[Params], device: torch.device):
         self.ops, self.comm, self.cfg = ops, comm, cfg
@@ -157,16 +158,20 @@ class FusedFSDPTrainer:
     def _start_gather(self, layer: int) -> None:
         if not (0 <= layer < self.L) or layer in self._pending:
             return
+        if os.environ.get("B200_DEBUG_SKIP_GATHER") == "1":      # timing experiments only: parameters go stale
+            self._pending[layer] = _Handle(None)
+            return
         lib = nv.load()
         slot = layer % 2
         self.side.wait_stream(torch.cuda.current_stream())
         for k in range(2):
             e = self.coll.next_epoch()
             sh = self.shards[layer][k]
-            nv._check(lib.b200_all_gather_into(self.full[slot][k].data_ptr(), self.sbuf.peers_c, self.shard_off[layer][k],
-                                               sh.numel() * 2, self.coll.flags.peers_c, self.rank, self.world, e, 0,
-                                               self.side.cuda_stream), "b200_all_gather_into")
-            nv.launch_count += 1
+            # copy engines, not SMs: the GEMMs running meanwhile own every SM's registers and shared memory
+            nv._check(lib.b200_all_gather_into_dma(self.full[slot][k].data_ptr(), self.sbuf.peers_c, self.shard_off[layer][k],
+                                                   sh.numel() * 2, self.coll.flags.peers_c, self.rank, self.world, e,
+                                                   self.side.cuda_stream), "b200_all_gather_into_dma")
+            nv.launch_count += 2
         ev = torch.cuda.Event()
         ev.record(self.side)
         self._pending[layer] = _Handle(ev)

@@ -133,6 +133,10 @@ int b200_all_gather(void* const* peers, long long offset_bytes, long long bytes,
 /* dst (local, world * shard_bytes) <- every rank's shard at src_peers[q] + src_offset_bytes (FSDP unshard, :203). */
 int b200_all_gather_into(void* dst, void* const* src_peers, long long src_offset_bytes, long long shard_bytes,
                          void* const* flag_peers, int rank, int world, unsigned int epoch, int blocks, void* stream);
+/* Same, moved by the copy engines (P2P DMA) between two one-warp barrier kernels: uses no SM, so it overlaps GEMMs that
+ * fill every SM.  The FSDP prefetch path. */
+int b200_all_gather_into_dma(void* dst, void* const* src_peers, long long src_offset_bytes, long long shard_bytes,
+                             void* const* flag_peers, int rank, int world, unsigned int epoch, void* stream);
 int b200_reduce_scatter_bf16(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers,
                              int rank, int world, unsigned int epoch, int blocks, void* stream);
 
