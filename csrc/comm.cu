@@ -29,7 +29,7 @@ __device__ __forceinline__ void block_barrier(const PeerTable& flags, int rank, 
                                               unsigned int* err) {
     __syncthreads();                                    // every thread's prior writes are issued
     if (threadIdx.x < world) {
-        __threadfence_system();                         // ... and ordered before the signal
+        fence_acq_rel_sys();                         // ... and ordered before the signal
         uint32_t* dst = reinterpret_cast<uint32_t*>(flags.p[threadIdx.x]) + blockIdx.x * MAX_WORLD + rank;
         st_release_sys(dst, value);
         const uint32_t* mine = reinterpret_cast<const uint32_t*>(flags.p[rank]) + blockIdx.x * MAX_WORLD + threadIdx.x;

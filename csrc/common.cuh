@@ -252,6 +252,10 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uin
 // ---------------------------------------------------------------------------------------------
 // system-scope flag protocol (peer memory over NVLink)
 // ---------------------------------------------------------------------------------------------
+// acquire-release fence at system scope: orders this thread's (and, after a CTA/warp barrier, its siblings') prior
+// writes before later ones for every observer including peer GPUs.  __threadfence_system() emits the much heavier
+// sequentially-consistent MEMBAR.SC.SYS.
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }

@@ -132,7 +132,7 @@ struct FusedEpi {
     static __device__ __forceinline__ void after_tile(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st) {
         epi_group_sync();                                            // all 8 warps' stores are issued
         if (ctx.ewarp == 0 && ctx.lane == 0) {
-            __threadfence_system();
+            fence_acq_rel_sys();
             st_release_sys(p.flags[st.owner] + (size_t)st.k_local * MAX_WORLD_F + p.rank, p.seq);
         }
     }
@@ -178,15 +178,17 @@ struct FusedEpi {
                 done |= 1ull << j;
                 --remaining;
                 progressed = true;
-                __threadfence_system();                              // my results are visible system-wide ...
-                __syncwarp();
+                __syncwarp();                                        // every lane's result stores are issued ...
                 unsigned int prev = 0;
-                if (lane == 0) prev = atomicAdd(&scratch[j], 1u);    // ... before I count
+                if (lane == 0) {
+                    fence_acq_rel_sys();                             // ... and ordered system-wide before I count
+                    prev = atomicAdd(&scratch[j], 1u);
+                }
                 prev = __shfl_sync(0xffffffffu, prev, 0);
                 if (prev == EXTRA_WARPS - 1 && p.broadcast) {        // the last side warp to finish the tile publishes it
                     int m_blk, n_blk;
                     owned_tile_coords(p, g, k, m_blk, n_blk);
-                    __threadfence_system();
+                    fence_acq_rel_sys();
                     if (lane < p.world) st_release_sys(p.flags[lane] + p.ready_base + m_blk * g.tiles_n + n_blk, p.seq);
                 }
             }

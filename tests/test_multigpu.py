@@ -106,6 +106,8 @@ def test_fused_trainer_matches_nccl_trainer(method):
     lp, seeds = _init()
     T = 128 * WORLD if method == "fsdp" else 512
     fn = {"ddp": api.train_ddp, "fsdp": api.train_fsdp, "mp": api.train_tp}[method]
+    if method == "mp":
+        seeds = seeds[:1]          # MP gives every rank ALL the seeds (train_ffns.py:324): keep it to one step as well
     fused = fn(lp, seeds, T, DM, _cfg(comm="fused"))
     nccl = fn(lp, seeds, T, DM, _cfg(comm="nccl"))
     upd_f = [[p - q for p, q in zip(a, b)] for a, b in zip(fused, lp)]
@@ -118,5 +120,7 @@ def test_fused_trainer_matches_nccl_trainer(method):
         for p, q, u in zip(la, lb, lu):
             ulp = torch.exp2(torch.floor(torch.log2(q.float().abs().clamp_min(2.0 ** -20))) - 7)
             excess = (p.float() - q.float()).abs() - (3 * ulp + 0.05 * u.abs())
-            assert (excess > 0).float().mean().item() < 1e-3, (excess.max().item(), (excess > 0).float().mean().item())
+            # the NCCL path rounds to bf16 after every hop of its ring (world - 1 roundings), the fused path once
+            assert (excess > 0).float().mean().item() < 5e-4 * WORLD, (excess.max().item(), (excess > 0).float().mean().item())
+    assert all(torch.isfinite(u).all() for l in upd_f for u in l) and all(torch.isfinite(u).all() for l in upd_n for u in l)
     assert max(u.abs().max().item() for l in upd_f for u in l) > 0

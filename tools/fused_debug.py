@@ -10,10 +10,10 @@ if __name__ == "__main__":
     WORLD = torch.cuda.device_count()
     method = sys.argv[1] if len(sys.argv) > 1 else "ddp"
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 1
-    DM = max(256, 128 * WORLD)
+    DM = int(os.environ.get("DM", max(256, 128 * WORLD)))
     g = torch.Generator().manual_seed(21)
     lp = [[p.to(torch.bfloat16).float() for p in l] for l in ffn.init_stack(3, DM, 4 * DM, g)]
-    seeds = torch.arange(steps * WORLD)
+    seeds = torch.arange(steps * WORLD) if method != "mp" else torch.arange(steps)
     T = 512
     def cfg(comm):
         return TrainConfig(model_size=DM, ffn_dim=4 * DM, layers=3, device="cuda", backend="nccl", world_size=WORLD, dtype="bf16", impl="native", lr=0.02, comm=comm)
@@ -34,6 +34,6 @@ if __name__ == "__main__":
                 for j in range(tn):
                     fr = ex[i * 128:(i + 1) * 128, j * 256:(j + 1) * 256].float().mean().item()
                     if fr > 0: tiles.append((i, j, round(fr, 3)))
-            print(json.dumps({"layer": l, "param": k, "shape": [M, N], "bad_frac": round(ex.float().mean().item(), 5),
+            print(json.dumps({"nan_fused": int(torch.isnan(f).sum()), "nan_nccl": int(torch.isnan(n).sum()), "layer": l, "param": k, "shape": [M, N], "bad_frac": round(ex.float().mean().item(), 5),
                               "fused_repeatable": bool(torch.equal(f, f2)), "max_abs_diff": (f - n).abs().max().item(),
                               "upd_max": u.abs().max().item(), "bad_tiles": tiles[:12], "n_bad_tiles": len(tiles), "n_tiles": tm * tn}))
