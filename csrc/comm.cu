@@ -46,6 +46,13 @@ __device__ __forceinline__ void add8(float (&acc)[8], const uint4& v) {
     acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
     acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z); acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
 }
+// fp32 payloads (the reference's test_nccl.py uses fp32): a 16-byte vector is 4 floats
+__device__ __forceinline__ void add4(float (&acc)[8], const uint4& v) {
+    acc[0] += __uint_as_float(v.x); acc[1] += __uint_as_float(v.y); acc[2] += __uint_as_float(v.z); acc[3] += __uint_as_float(v.w);
+}
+__device__ __forceinline__ uint4 pack4f(const float (&f)[8]) {
+    return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+}
 __device__ __forceinline__ uint4 pack8f(const float (&f)[8]) {
     uint4 o;
     o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
@@ -82,7 +89,7 @@ __device__ __forceinline__ void slice_bounds(long long V, int world, int s, long
 // MODE 1: reduce-scatter (first half only; result stays in my slice of my buffer)
 // MODE 2: all-gather (second half only; my slice of my buffer is the input)
 // MODE 3: one-shot all-reduce for latency-bound sizes (every rank sums all peers; <= 1 vector per thread)
-template <int MODE>
+template <int MODE, bool F32>
 __global__ void __launch_bounds__(COLL_THREADS) coll_kernel(PeerTable buf, long long offset_bytes, long long V, PeerTable flags,
                                                             int rank, int world, uint32_t epoch, unsigned int* err) {
     const long long tstride = (long long)gridDim.x * blockDim.x;
@@ -100,11 +107,11 @@ __global__ void __launch_bounds__(COLL_THREADS) coll_kernel(PeerTable buf, long 
         if (active) {
             for (int q = 0; q < world; ++q) {
                 const uint4* src = reinterpret_cast<const uint4*>(sbuf[q] + offset_bytes);
-                add8(acc, ld_cv_u4(src + t0));
+                if (F32) add4(acc, ld_cv_u4(src + t0)); else add8(acc, ld_cv_u4(src + t0));
             }
         }
         block_barrier(flags, rank, world, 3 * epoch + 2, err); // everyone has read everything: safe to overwrite
-        if (active) st_u4(mine + t0, pack8f(acc));
+        if (active) st_u4(mine + t0, F32 ? pack4f(acc) : pack8f(acc));
         return;
     }
 
@@ -128,8 +135,8 @@ __global__ void __launch_bounds__(COLL_THREADS) coll_kernel(PeerTable buf, long 
                 float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #pragma unroll
                 for (int q = 0; q < MAX_WORLD; ++q)            // fixed order: deterministic sum
-                    if (q < world) add8(acc, v[u][q]);
-                st_u4(mine + idx, pack8f(acc));
+                    if (q < world) { if (F32) add4(acc, v[u][q]); else add8(acc, v[u][q]); }
+                st_u4(mine + idx, F32 ? pack4f(acc) : pack8f(acc));
             }
         }
     }
@@ -175,7 +182,7 @@ static int make_table(PeerTable* t, void* const* peers, int world, const char* w
     return 0;
 }
 
-static int coll_launch(int mode, void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
+static int coll_launch(int mode, bool f32, void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
                        int world, unsigned int epoch, int blocks, void* stream, const char* what) {
     PeerTable buf, flags;
     if (int rc = make_table(&buf, peers, world, what)) return rc;
@@ -190,16 +197,22 @@ static int coll_launch(int mode, void* const* peers, long long offset_bytes, lon
     if (blocks > COLL_MAX_BLOCKS) blocks = COLL_MAX_BLOCKS;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     unsigned int* err = device_error_slot();
-    if (mode == 0 && V <= (long long)blocks * COLL_THREADS && V <= 16 * COLL_THREADS) {
+#define B200_COLL(MODE_, GRID_)                                                                                              \
+    do {                                                                                                                      \
+        if (f32) coll_kernel<MODE_, true><<<GRID_, COLL_THREADS, 0, st>>>(buf, offset_bytes, V, flags, rank, world, epoch, err); \
+        else coll_kernel<MODE_, false><<<GRID_, COLL_THREADS, 0, st>>>(buf, offset_bytes, V, flags, rank, world, epoch, err);   \
+    } while (0)
+    if (mode == 0 && V <= 16 * COLL_THREADS) {                 // latency-bound: one-shot, <= 1 vector per thread
         const int b = (int)((V + COLL_THREADS - 1) / COLL_THREADS);
-        coll_kernel<3><<<b, COLL_THREADS, 0, st>>>(buf, offset_bytes, V, flags, rank, world, epoch, err);
+        B200_COLL(3, b);
     } else if (mode == 0) {
-        coll_kernel<0><<<blocks, COLL_THREADS, 0, st>>>(buf, offset_bytes, V, flags, rank, world, epoch, err);
+        B200_COLL(0, blocks);
     } else if (mode == 1) {
-        coll_kernel<1><<<blocks, COLL_THREADS, 0, st>>>(buf, offset_bytes, V, flags, rank, world, epoch, err);
+        B200_COLL(1, blocks);
     } else {
-        coll_kernel<2><<<blocks, COLL_THREADS, 0, st>>>(buf, offset_bytes, V, flags, rank, world, epoch, err);
+        B200_COLL(2, blocks);
     }
+#undef B200_COLL
     return check_cuda(cudaGetLastError(), what);
 }
 
@@ -250,15 +263,23 @@ extern "C" int b200_barrier(void* const* flag_peers, int rank, int world, unsign
 }
 extern "C" int b200_all_reduce_bf16(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
                                     int world, unsigned int epoch, int blocks, void* stream) {
-    return coll_launch(0, peers, offset_bytes, bytes, flag_peers, rank, world, epoch, blocks, stream, "all_reduce");
+    return coll_launch(0, false, peers, offset_bytes, bytes, flag_peers, rank, world, epoch, blocks, stream, "all_reduce");
 }
 extern "C" int b200_reduce_scatter_bf16(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers,
                                         int rank, int world, unsigned int epoch, int blocks, void* stream) {
-    return coll_launch(1, peers, offset_bytes, bytes, flag_peers, rank, world, epoch, blocks, stream, "reduce_scatter");
+    return coll_launch(1, false, peers, offset_bytes, bytes, flag_peers, rank, world, epoch, blocks, stream, "reduce_scatter");
+}
+extern "C" int b200_all_reduce_f32(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
+                                   int world, unsigned int epoch, int blocks, void* stream) {
+    return coll_launch(0, true, peers, offset_bytes, bytes, flag_peers, rank, world, epoch, blocks, stream, "all_reduce_f32");
+}
+extern "C" int b200_reduce_scatter_f32(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers,
+                                       int rank, int world, unsigned int epoch, int blocks, void* stream) {
+    return coll_launch(1, true, peers, offset_bytes, bytes, flag_peers, rank, world, epoch, blocks, stream, "reduce_scatter_f32");
 }
 extern "C" int b200_all_gather(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
                                int world, unsigned int epoch, int blocks, void* stream) {
-    return coll_launch(2, peers, offset_bytes, bytes, flag_peers, rank, world, epoch, blocks, stream, "all_gather");
+    return coll_launch(2, false, peers, offset_bytes, bytes, flag_peers, rank, world, epoch, blocks, stream, "all_gather");
 }
 extern "C" int b200_all_gather_into(void* dst, void* const* src_peers, long long src_offset_bytes, long long shard_bytes,
                                     void* const* flag_peers, int rank, int world, unsigned int epoch, int blocks, void* stream) {

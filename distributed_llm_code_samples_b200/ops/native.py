@@ -94,6 +94,8 @@ def _optional_declare(lib) -> None:
         "b200_barrier": ([pp, i, i, u, vp], i),
         "b200_all_reduce_bf16": ([pp, ll, ll, pp, i, i, u, i, vp], i),
         "b200_all_gather": ([pp, ll, ll, pp, i, i, u, i, vp], i),
+        "b200_all_reduce_f32": ([pp, ll, ll, pp, i, i, u, i, vp], i),
+        "b200_reduce_scatter_f32": ([pp, ll, ll, pp, i, i, u, i, vp], i),
         "b200_reduce_scatter_bf16": ([pp, ll, ll, pp, i, i, u, i, vp], i),
         "b200_all_gather_into": ([vp, pp, ll, ll, pp, i, i, u, i, vp], i),
         "b200_sumsq_static_max_elems": ([], ll),

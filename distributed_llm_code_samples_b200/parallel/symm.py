@@ -194,21 +194,23 @@ class SymmComm:
         nv.launch_count += 1
 
     def all_reduce(self, t: torch.Tensor, async_op: bool = False):
-        assert t.dtype == torch.bfloat16 and t.is_contiguous(), "native all_reduce handles contiguous bf16"
-        nbytes = (t.numel() * 2 + 15) // 16 * 16
+        assert t.dtype in (torch.bfloat16, torch.float32) and t.is_contiguous(), "native all_reduce: contiguous bf16 / fp32"
+        es = t.element_size()
+        fn = self.lib.b200_all_reduce_bf16 if es == 2 else self.lib.b200_all_reduce_f32
+        nbytes = (t.numel() * es + 15) // 16 * 16
         buf = self._find(t)
         e = self.chan.next_epoch()
-        if buf is not None and (t.numel() * 2) % 16 == 0:
+        if buf is not None and (t.numel() * es) % 16 == 0:
             off = buf.offset_of(t)
-            return self._run(lambda s: nv._check(self.lib.b200_all_reduce_bf16(buf.peers_c, off, nbytes, self.chan.flags.peers_c,
-                                                                              self.rank, self.world, e, 0, s), "b200_all_reduce_bf16"), async_op)
+            return self._run(lambda s: nv._check(fn(buf.peers_c, off, nbytes, self.chan.flags.peers_c, self.rank, self.world, e, 0, s),
+                                                 "b200_all_reduce"), async_op)
         self._stage_check(nbytes)
-        st = self.staging.tensor(0, (nbytes // 2,), torch.bfloat16)
+        st = self.staging.tensor(0, (nbytes // es,), t.dtype)
 
         def go(s):
+            st[t.numel():].zero_()                                   # the padding lanes are summed too
             st[: t.numel()].copy_(t.reshape(-1))
-            nv._check(self.lib.b200_all_reduce_bf16(self.staging.peers_c, 0, nbytes, self.chan.flags.peers_c, self.rank,
-                                                    self.world, e, 0, s), "b200_all_reduce_bf16")
+            nv._check(fn(self.staging.peers_c, 0, nbytes, self.chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_all_reduce")
             t.reshape(-1).copy_(st[: t.numel()])
         return self._run(go, async_op)
 
@@ -232,8 +234,10 @@ class SymmComm:
         return self._run(go, async_op)
 
     def reduce_scatter_into(self, out: torch.Tensor, full: torch.Tensor, async_op: bool = False):
-        assert full.dtype == torch.bfloat16 and full.is_contiguous() and out.is_contiguous()
-        nbytes = full.numel() * 2
+        assert full.dtype in (torch.bfloat16, torch.float32) and full.is_contiguous() and out.is_contiguous()
+        es = full.element_size()
+        rs = self.lib.b200_reduce_scatter_bf16 if es == 2 else self.lib.b200_reduce_scatter_f32
+        nbytes = full.numel() * es
         assert nbytes % (16 * self.world) == 0, "reduce_scatter needs bytes % (16*world) == 0"
         e = self.chan.next_epoch()
         buf = self._find(full)
@@ -243,18 +247,16 @@ class SymmComm:
             off = buf.offset_of(full)
 
             def go(s):
-                nv._check(self.lib.b200_reduce_scatter_bf16(buf.peers_c, off, nbytes, self.chan.flags.peers_c, self.rank,
-                                                            self.world, e, 0, s), "b200_reduce_scatter_bf16")
-                out.reshape(-1).copy_(full.reshape(-1)[self.rank * (sl // 2): (self.rank + 1) * (sl // 2)])
+                nv._check(rs(buf.peers_c, off, nbytes, self.chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_reduce_scatter")
+                out.reshape(-1).copy_(full.reshape(-1)[self.rank * (sl // es): (self.rank + 1) * (sl // es)])
             return self._run(go, async_op)
         self._stage_check(nbytes)
-        st = self.staging.tensor(0, (nbytes // 2,), torch.bfloat16)
+        st = self.staging.tensor(0, (nbytes // es,), full.dtype)
 
         def go2(s):
             st.copy_(full.reshape(-1))
-            nv._check(self.lib.b200_reduce_scatter_bf16(self.staging.peers_c, 0, nbytes, self.chan.flags.peers_c, self.rank,
-                                                        self.world, e, 0, s), "b200_reduce_scatter_bf16")
-            out.reshape(-1).copy_(st[self.rank * (sl // 2): (self.rank + 1) * (sl // 2)])
+            nv._check(rs(self.staging.peers_c, 0, nbytes, self.chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_reduce_scatter")
+            out.reshape(-1).copy_(st[self.rank * (sl // es): (self.rank + 1) * (sl // es)])
         return self._run(go2, async_op)
 
     def all_reduce_max(self, t: torch.Tensor) -> torch.Tensor:

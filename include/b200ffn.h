@@ -128,6 +128,10 @@ long long b200_coll_flag_bytes(void);
 int b200_barrier(void* const* flag_peers, int rank, int world, unsigned int epoch, void* stream);
 int b200_all_reduce_bf16(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
                          int world, unsigned int epoch, int blocks, void* stream);
+int b200_all_reduce_f32(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
+                        int world, unsigned int epoch, int blocks, void* stream);
+int b200_reduce_scatter_f32(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers,
+                            int rank, int world, unsigned int epoch, int blocks, void* stream);
 int b200_all_gather(void* const* peers, long long offset_bytes, long long bytes, void* const* flag_peers, int rank,
                     int world, unsigned int epoch, int blocks, void* stream);
 /* dst (local, world * shard_bytes) <- every rank's shard at src_peers[q] + src_offset_bytes (FSDP unshard, :203). */

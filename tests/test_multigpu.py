@@ -124,3 +124,17 @@ def test_fused_trainer_matches_nccl_trainer(method):
             assert (excess > 0).float().mean().item() < 5e-4 * WORLD, (excess.max().item(), (excess > 0).float().mean().item())
     assert all(torch.isfinite(u).all() for l in upd_f for u in l) and all(torch.isfinite(u).all() for l in upd_n for u in l)
     assert max(u.abs().max().item() for l in upd_f for u in l) > 0
+
+
+def test_probe_single_process_collectives_and_streams():
+    """test_nccl.py / test_torch_cuda_stream.py counterparts: one process, one stream per device."""
+    from probes import single_process
+    assert all(single_process.collectives(WORLD).values())
+    assert all(single_process.streams(WORLD).values())
+
+
+def test_probe_async_allreduce_and_ipc_barrier():
+    """test_torch_distributed.py / test_mp_barrier_gpus.py counterparts: one process per GPU."""
+    from probes import multi_process
+    assert multi_process.async_allreduce_side_stream(WORLD)
+    assert multi_process.ipc_barrier(WORLD)
