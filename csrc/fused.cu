@@ -23,6 +23,7 @@
 // that at any moment they push to different owners.
 #include "gemm_kernel.cuh"
 #include "../include/b200ffn.h"
+#include <cstdlib>
 
 namespace b200 {
 
@@ -85,10 +86,11 @@ __device__ __forceinline__ uint4 pack_row8(const uint32_t* a) {
     return v;
 }
 
-struct FusedEpi {
+template <int SIDE_WARPS>
+struct FusedEpiT {
     using Params = FusedParams;
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
-    static constexpr int EXTRA_WARPS = 2;      // the two spare warps of warpgroup 0 reduce owned tiles under the MMAs
+    static constexpr int EXTRA_WARPS = SIDE_WARPS;   // side warps reduce/broadcast owned tiles under the MMAs
     struct State {
         int k_local;               // inbox slot of the tile being pushed
         int owner;
@@ -324,5 +326,11 @@ extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_majo
     // Interleaved owners already spread consecutive tiles over ranks; row-sharded owners would make every rank push to
     // the same owner at once, so there each rank starts its walk at a different offset.
     const int rot = owner_mode == OWN_ROW_SHARDED ? rank : 0;
-    return launch_gemm<FusedEpi>(o, p, max_ctas, reinterpret_cast<cudaStream_t>(stream), rot, world);
+    static int side = -1;                       // B200_FUSED_SIDE_WARPS=2|4 (default 4): warps that reduce under the MMAs
+    if (side < 0) {
+        const char* e = getenv("B200_FUSED_SIDE_WARPS");
+        side = (e != nullptr && e[0] == '2') ? 2 : 4;
+    }
+    if (side == 2) return launch_gemm<FusedEpiT<2>>(o, p, max_ctas, reinterpret_cast<cudaStream_t>(stream), rot, world);
+    return launch_gemm<FusedEpiT<4>>(o, p, max_ctas, reinterpret_cast<cudaStream_t>(stream), rot, world);
 }
