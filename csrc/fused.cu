@@ -331,6 +331,21 @@ extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_majo
         const char* e = getenv("B200_FUSED_SIDE_WARPS");
         side = (e != nullptr && e[0] == '2') ? 2 : 4;
     }
-    if (side == 2) return launch_gemm<FusedEpiT<2>>(o, p, max_ctas, reinterpret_cast<cudaStream_t>(stream), rot, world);
-    return launch_gemm<FusedEpiT<4>>(o, p, max_ctas, reinterpret_cast<cudaStream_t>(stream), rot, world);
+    // Link-bound calls (NVLink time comparable to the MMA time, e.g. the MP all-reduce at 8 ranks) see bursts of store
+    // back-pressure in the epilogue; the kernel with two accumulator stages absorbs them under the next tile's MMAs,
+    // while compute-bound calls (the dW GEMMs) are faster on the 256x256-per-CTA pair kernel.
+    static int overlap_mode = -1;               // B200_FUSED_OVERLAP=0|1 forces; default: decide per call
+    if (overlap_mode < 0) {
+        const char* e = getenv("B200_FUSED_OVERLAP");
+        overlap_mode = e == nullptr ? 2 : (e[0] == '1' ? 1 : (e[0] == '0' ? 0 : 2));
+    }
+    bool overlap = overlap_mode == 1;
+    if (overlap_mode == 2 && world > 1) {
+        const double bytes = (broadcast ? 2.0 : 1.0) * (world - 1) / world * (double)M * N * 2.0;
+        const double link_ms = bytes / 770e9 * 1e3, mma_ms = 2.0 * M * N * (double)K / 1.4e15 * 1e3;
+        overlap = link_ms > 0.6 * mma_ms;
+    }
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (side == 2) return launch_gemm<FusedEpiT<2>>(o, p, max_ctas, st, rot, world, overlap);
+    return launch_gemm<FusedEpiT<4>>(o, p, max_ctas, st, rot, world, overlap);
 }

@@ -87,12 +87,16 @@ def case_mp(T, D, Fs, name):
 
 
 out = []
-out.append(case_dw(16384, 4096, 16384, "ddp/fsdp dW1 [F,D]"))
-out.append(case_dw(4096, 16384, 16384, "ddp/fsdp dW2 [D,F]"))
-out.append(case_mp(16384, 8192, 28672 // world, "mp y = a W2^T (70B shape)"))
+only = os.environ.get("FUSED_BENCH_ONLY", "")
+if only in ("", "dw"):
+    out.append(case_dw(16384, 4096, 16384, "ddp/fsdp dW1 [F,D]"))
+    out.append(case_dw(4096, 16384, 16384, "ddp/fsdp dW2 [D,F]"))
+if only in ("", "mp"):
+    out.append(case_mp(16384, 8192, 28672 // world, "mp y = a W2^T (70B shape)"))
 if rank == 0:
     os.makedirs("gpurun_out", exist_ok=True)
-    with open(f"gpurun_out/fused_bench_n{world}.jsonl", "w") as f:
+    tag = os.environ.get("FUSED_BENCH_TAG", "")
+    with open(f"gpurun_out/fused_bench_n{world}{tag}.jsonl", "w") as f:
         for r in out:
             r = {k: (round(v, 4) if isinstance(v, float) else v) for k, v in r.items()}
             print(json.dumps(r)); f.write(json.dumps(r) + "\n")
