@@ -52,7 +52,7 @@ struct FusedParams {
     int ready_base;                  // word offset of the ready flags inside the flag block
 };
 
-__device__ __forceinline__ int owner_of(const FusedParams& p, const GemmCore& g, int m_blk, int n_blk, int& k_local) {
+__host__ __device__ __forceinline__ int owner_of(const FusedParams& p, const GemmCore& g, int m_blk, int n_blk, int& k_local) {
     if (p.owner_mode == OWN_ROW_SHARDED) {
         k_local = (m_blk % p.mpo) * g.tiles_n + n_blk;
         return m_blk / p.mpo;
@@ -61,7 +61,7 @@ __device__ __forceinline__ int owner_of(const FusedParams& p, const GemmCore& g,
     k_local = lin / p.world;
     return lin % p.world;
 }
-__device__ __forceinline__ void owned_tile_coords(const FusedParams& p, const GemmCore& g, int k_local, int& m_blk, int& n_blk) {
+__host__ __device__ __forceinline__ void owned_tile_coords(const FusedParams& p, const GemmCore& g, int k_local, int& m_blk, int& n_blk) {
     if (p.owner_mode == OWN_ROW_SHARDED) {
         m_blk = p.rank * p.mpo + k_local / g.tiles_n;
         n_blk = k_local % g.tiles_n;
@@ -71,7 +71,7 @@ __device__ __forceinline__ void owned_tile_coords(const FusedParams& p, const Ge
         n_blk = lin % g.tiles_n;
     }
 }
-__device__ __forceinline__ size_t inbox_slot(const FusedParams& p, int k_local, int src) {
+__host__ __device__ __forceinline__ size_t inbox_slot(const FusedParams& p, int k_local, int src) {
     return ((size_t)(p.parity * p.owned_cap + k_local) * p.world + src) * TILE_ELEMS;
 }
 __device__ __forceinline__ void epi_group_sync() {       // the 8 epilogue warps only (named barrier 1)
@@ -282,6 +282,37 @@ extern "C" int b200_fused_owned_tiles(int M, int N, int world, int owner_mode) {
     const int tm = (M + BM - 1) / BM, tn = (N + BN - 1) / BN;
     if (owner_mode == OWN_ROW_SHARDED) return (tm / world) * tn;
     return (tm * tn + world - 1) / world;
+}
+
+// Host mirrors of the scheduling maps, for CPU tests (tests/test_native_maps_cpu.py): the SAME inline functions the
+// kernels use, evaluated on the host.
+// out[0] = owner rank, out[1] = inbox slot (owned-tile index) on that owner, out[2..3] = the (m_blk, n_blk) that the
+// owner maps that slot back to.
+extern "C" int b200_debug_fused_map(int M, int N, int world, int owner_mode, int m_blk, int n_blk, int* out) {
+    GemmCore g{};
+    g.M = M; g.N = N;
+    g.tiles_m = (M + BM - 1) / BM; g.tiles_n = (N + BN - 1) / BN;
+    FusedParams p{};
+    p.world = world; p.owner_mode = owner_mode;
+    p.mpo = owner_mode == OWN_ROW_SHARDED ? g.tiles_m / world : 1;
+    int k = 0;
+    const int owner = owner_of(p, g, m_blk, n_blk, k);
+    p.rank = owner;
+    int mb = -1, nb = -1;
+    owned_tile_coords(p, g, k, mb, nb);
+    out[0] = owner; out[1] = k; out[2] = mb; out[3] = nb;
+    return 0;
+}
+// order[i] = m_blk * tiles_n + n_blk of the i-th tile in the 1-CTA kernel's rasterised walk
+extern "C" int b200_debug_tile_order(int tiles_m, int tiles_n, int group_m, int* order) {
+    GemmCore g{};
+    g.tiles_m = tiles_m; g.tiles_n = tiles_n; g.group_m = group_m;
+    for (int t = 0; t < tiles_m * tiles_n; ++t) {
+        int m = 0, n = 0;
+        tile_coords(g, t, m, n);
+        order[t] = m * tiles_n + n;
+    }
+    return 0;
 }
 
 // D = A*B^T-style GEMM (same operand conventions as b200_gemm_bf16) whose output tiles are reduced across

@@ -40,11 +40,11 @@ struct GemmCore {
 };
 
 // tile index -> (m_blk, n_blk) with grouped rasterisation so the ~148 tiles in flight share A/B panels in L2
-__device__ __forceinline__ void tile_coords(const GemmCore& g, int tile, int& m_blk, int& n_blk) {
+__host__ __device__ __forceinline__ void tile_coords(const GemmCore& g, int tile, int& m_blk, int& n_blk) {
     const int per_group = g.group_m * g.tiles_n;
     const int group = tile / per_group;
     const int first_m = group * g.group_m;
-    const int gsize = min(g.tiles_m - first_m, g.group_m);
+    const int gsize = (g.tiles_m - first_m) < g.group_m ? (g.tiles_m - first_m) : g.group_m;
     const int in_group = tile - group * per_group;
     m_blk = first_m + in_group % gsize;
     n_blk = in_group / gsize;
