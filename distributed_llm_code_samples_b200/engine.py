@@ -55,9 +55,6 @@ class Engine:
             layers_params = init_params_on_device(cfg, device, seed)
         self.trainer = build_trainer(method, self.ops, self.comm, cfg, layers_params, device)
         del layers_params
-        self._metric_dev: Optional[torch.Tensor] = None
-        self._metric_host = None
-        self._metric_event = None
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 

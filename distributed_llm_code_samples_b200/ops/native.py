@@ -7,7 +7,6 @@ or broken library is an error, not a reason to run eager PyTorch.
 from __future__ import annotations
 
 import ctypes as C
-import os
 import threading
 from pathlib import Path
 from typing import Optional

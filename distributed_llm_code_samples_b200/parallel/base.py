@@ -1,7 +1,7 @@
 """Shared pieces of the per-rank trainers: optimizer state, block options, sharding rules."""
 from __future__ import annotations
 
-from typing import Dict, Iterable, List, Optional, Sequence, Tuple
+from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
 

@@ -11,7 +11,7 @@ so a checkpoint written under one strategy resumes under any other: resharding i
 from __future__ import annotations
 
 import os
-from typing import List, Optional, Sequence
+from typing import Optional, Sequence
 
 import torch
 

@@ -91,7 +91,6 @@ class PinnedPrefetcher:
             x, dy = x.pin_memory(), dy.pin_memory()
         with torch.cuda.stream(self.stream):
             self._next = (x.to(self.device, non_blocking=True), dy.to(self.device, non_blocking=True))
-            self._bytes = x.numel() * x.element_size() + dy.numel() * dy.element_size()
 
     def __iter__(self):
         return self

@@ -3,7 +3,6 @@ the reference times with ``time.time()`` around spawn + NCCL init + CPU RNG + H2
 from __future__ import annotations
 
 import time
-from typing import Optional
 
 import torch
 

@@ -12,7 +12,6 @@ from __future__ import annotations
 import torch
 import torch.distributed as dist
 
-from distributed_llm_code_samples_b200.ops import native as nv
 from distributed_llm_code_samples_b200.parallel.launcher import launch
 from distributed_llm_code_samples_b200.parallel.symm import SymmComm, SymmWorld
 

@@ -4,7 +4,6 @@ import json, os, sys
 import torch
 import torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from distributed_llm_code_samples_b200.ops import native as nv
 from distributed_llm_code_samples_b200.parallel.launcher import init_from_env
 from distributed_llm_code_samples_b200.parallel.symm import SymmComm, SymmWorld
 
