@@ -65,11 +65,13 @@ def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
     if method == "fsdp":
         ok = ok and cfg.model_size % (128 * comm.world) == 0 and cfg.ffn_dim % (128 * comm.world) == 0
     if method == "mp":
-        ok = ok and not cfg.residual and cfg.mp_mode == "ar" and (cfg.ffn_dim // comm.world) % 8 == 0
+        ok = ok and not cfg.residual and (cfg.ffn_dim // comm.world) % 8 == 0
+        if cfg.mp_mode == "sp":
+            ok = ok and cfg.tokens % (128 * comm.world) == 0
     if not ok:
         if cfg.comm == "fused":
             raise RuntimeError("comm=fused needs impl=native, bf16, SGD, no bias, world>1, dims % 8 == 0 "
-                               "(FSDP: dims % (128*world) == 0; MP: all-reduce form, no residual)")
+                               "(FSDP: dims % (128*world) == 0; MP: no residual, sp form needs tokens % (128*world) == 0)")
         return False
     try:
         from . import fused  # noqa: F401
@@ -129,6 +131,7 @@ def _run(method: str, layers_params: Sequence[Params], seeds: torch.Tensor, toke
          cfg: Optional[TrainConfig]) -> List[Params]:
     cfg = copy.deepcopy(cfg) if cfg is not None else TrainConfig(model_size=model_size)
     cfg.model_size = model_size
+    cfg.batch_size, cfg.seq_len = tokens, 1          # the drivers take the token count directly (train_ffns.py:379)
     cfg.ffn_dim = layers_params[0][0].shape[0]
     cfg.bias = len(layers_params[0]) == 4
     device = pick_device(cfg.device)

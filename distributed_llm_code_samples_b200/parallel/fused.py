@@ -237,13 +237,24 @@ class FusedFSDPTrainer:
 
 # =================================================================================================== MP
 class FusedMPTrainer:
+    """Megatron MP with the collectives inside the row-parallel GEMMs.
+
+    ``mp_mode="ar"`` (reference form): activations replicated, ``y`` and ``dx`` all-reduced in the GEMM kernel.
+    ``mp_mode="sp"`` (sequence-parallel form): activations live sharded over tokens ``[T/n, D]``; the row-parallel GEMM
+    REDUCE-SCATTERS its output to the token-shard owners inside the kernel, and the next column-parallel GEMM's input is
+    all-gathered from the peers' shards by the native pull kernel.  Same NVLink bytes (AR = RS + AG), 1/n of the saved
+    activation memory."""
+
     comm_name = "fused: row-parallel GEMM + all-reduce in one kernel (peer stores over NVLink)"
 
     def __init__(self, ops, comm, cfg: TrainConfig, shards: List[Params], device: torch.device):
         self.ops, self.comm, self.cfg, self.shards = ops, comm, cfg, shards
         self.opts = block_opts(cfg)
-        if cfg.residual or cfg.mp_mode != "ar":
-            raise RuntimeError("fused MP implements the reference all-reduce form without residual; use --comm nccl for the others")
+        if cfg.residual:
+            raise RuntimeError("fused MP has no residual path; use --comm nccl")
+        self.sp = cfg.mp_mode == "sp"
+        if self.sp:
+            self.comm_name = "fused: row-parallel GEMM + reduce-scatter in one kernel; native all-gather of the token shards"
         self.lr = cfg.lr * cfg.grad_scale
         self.sw = get_symm_world(comm, device)
         self.world, self.rank = comm.world, comm.rank
@@ -255,27 +266,47 @@ class FusedMPTrainer:
     def _ensure_buffers(self, T: int) -> None:
         if self.T == T:
             return
-        D = self.cfg.model_size
-        self.abuf: SymmBuffer = self.sw.alloc((self.L + 2) * T * D * 2 + 8192)
-        self.y, self.y_tab = [], []
-        for _ in range(self.L):
-            t, o = self.abuf.carve((T, D), torch.bfloat16)
-            self.y.append(t)
-            self.y_tab.append(self.abuf.peers_at(o))
-        self.dx, self.dx_tab = [], []
-        for _ in range(2):
-            t, o = self.abuf.carve((T, D), torch.bfloat16)
-            self.dx.append(t)
-            self.dx_tab.append(self.abuf.peers_at(o))
-        self.chan = FusedChannel(self.sw, _owned_cap([(T, D)], self.world, OWN_INTERLEAVED), _tiles(T, D))
+        D, n = self.cfg.model_size, self.world
+        if self.sp:
+            if T % (TILE_M * n):
+                raise ValueError(f"sequence-parallel fused MP needs tokens ({T}) divisible by 128 * world ({TILE_M * n})")
+            Ts = T // n
+            self.abuf: SymmBuffer = self.sw.alloc((self.L + 3) * Ts * D * 2 + 16384)
+            self.xs0, self.xs0_off = self.abuf.carve((Ts, D), torch.bfloat16)          # the input batch's token shard
+            self.ys, self.ys_off = [], []
+            for _ in range(self.L):
+                t, o = self.abuf.carve((Ts, D), torch.bfloat16)
+                self.ys.append(t)
+                self.ys_off.append(o)
+            self.dxs, self.dxs_off = [], []
+            for _ in range(2):
+                t, o = self.abuf.carve((Ts, D), torch.bfloat16)
+                self.dxs.append(t)
+                self.dxs_off.append(o)
+            self.local_tab = lambda t: (C.c_void_p * n)(*[t.data_ptr() if r == self.rank else 0 for r in range(n)])
+            self.chan = FusedChannel(self.sw, _owned_cap([(T, D)], n, OWN_ROW_SHARDED), _tiles(T, D))
+            self.coll = CollChannel(self.sw)
+        else:
+            self.abuf = self.sw.alloc((self.L + 2) * T * D * 2 + 8192)
+            self.y, self.y_tab = [], []
+            for _ in range(self.L):
+                t, o = self.abuf.carve((T, D), torch.bfloat16)
+                self.y.append(t)
+                self.y_tab.append(self.abuf.peers_at(o))
+            self.dx, self.dx_tab = [], []
+            for _ in range(2):
+                t, o = self.abuf.carve((T, D), torch.bfloat16)
+                self.dx.append(t)
+                self.dx_tab.append(self.abuf.peers_at(o))
+            self.chan = FusedChannel(self.sw, _owned_cap([(T, D)], n, OWN_INTERLEAVED), _tiles(T, D))
         self.T = T
         self.sw.host_barrier()
 
-    def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
-        ops, cfg = self.ops, self.cfg
+    # ---- reference (all-reduce) form -----------------------------------------------------------------------
+    def _step_ar(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+        ops = self.ops
         T, D = x.shape
         Fs = self.shards[0][0].shape[0]
-        self._ensure_buffers(T)
         saved = []
         y = x
         for l, (W1, W2) in enumerate(self.shards):
@@ -302,6 +333,56 @@ class FusedMPTrainer:
             saved[i] = None
             d = dn
         return y
+
+    # ---- sequence-parallel form ----------------------------------------------------------------------------
+    def _gather_tokens(self, offset_bytes: int, T: int, D: int) -> torch.Tensor:
+        """[T, D] <- every rank's [T/n, D] token shard at ``offset_bytes`` of the activation block (native pull)."""
+        full = torch.empty(T, D, dtype=torch.bfloat16, device=self.device)
+        e = self.coll.next_epoch()
+        nv._check(nv.load().b200_all_gather_into(full.data_ptr(), self.abuf.peers_c, offset_bytes, (T // self.world) * D * 2,
+                                                 self.coll.flags.peers_c, self.rank, self.world, e, 0, nv._stream()), "b200_all_gather_into")
+        nv.launch_count += 1
+        return full
+
+    def _step_sp(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+        ops, n, r = self.ops, self.world, self.rank
+        T, D = x.shape
+        Ts = T // n
+        Fs = self.shards[0][0].shape[0]
+        self.xs0.copy_(x[r * Ts:(r + 1) * Ts])
+        saved = []
+        cur_off = self.xs0_off
+        for l, (W1, W2) in enumerate(self.shards):
+            xfull = self._gather_tokens(cur_off, T, D)                    # all-gather -> column-parallel GEMM
+            a, pre = ops.linear_act(xfull, W1, self.opts.activation)
+            saved.append((cur_off, None if self.opts.recompute else a, None if self.opts.recompute else pre))
+            # row-parallel GEMM -> reduce-scatter over token shards, one kernel: I keep rows [r*Ts, (r+1)*Ts)
+            self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.local_tab(self.ys[l]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
+            cur_off = self.ys_off[l]
+        # upstream gradient: same layout, token-sharded; stage my shard in a rotating symmetric slot
+        d_slot = self.L % 2
+        self.dxs[d_slot].copy_(dloss_dx[r * Ts:(r + 1) * Ts])
+        d_off = self.dxs_off[d_slot]
+        for i in reversed(range(self.L)):
+            W1, W2 = self.shards[i]
+            x_off, a, pre = saved[i]
+            dfull = self._gather_tokens(d_off, T, D)
+            xfull = self._gather_tokens(x_off, T, D)
+            if a is None:
+                a, pre = ops.linear_act(xfull, W1, self.opts.activation)
+            dh = ops.grad_input(dfull, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
+            ops.grad_weight_sgd_(W2, dfull, a, self.lr)
+            if i > 0:
+                slot = i % 2
+                self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.local_tab(self.dxs[slot]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
+                d_off = self.dxs_off[slot]
+            ops.grad_weight_sgd_(W1, dh, xfull, self.lr)
+            saved[i] = None
+        return self._gather_tokens(self.ys_off[self.L - 1], T, D)
+
+    def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+        self._ensure_buffers(x.shape[0])
+        return self._step_sp(x, dloss_dx) if self.sp else self._step_ar(x, dloss_dx)
 
     def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor]]) -> None:
         for x, dy in batches:
