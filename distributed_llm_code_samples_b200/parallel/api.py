@@ -115,15 +115,29 @@ def _rank_main(rank: int, world: int, device: torch.device, method: str, cfg_dic
         batches = device_mock_data(my_seeds, tokens, model_size, cfg.torch_dtype, device)
     else:
         batches = mock_data(my_seeds, tokens, model_size, cfg.torch_dtype, device)
+    seeds_per_step = world if method in ("ddp", "fsdp") else 1
     with profile_if(cfg.profile, rank):
         with DeviceTimer(device) as t:
-            trainer.run(batches)
+            if cfg.save_every and cfg.save_path:
+                for k, (x, dy) in enumerate(batches):
+                    trainer.step(x, dy)
+                    if (k + 1) % cfg.save_every == 0:                # periodic checkpoint: full, unsharded layout
+                        full = trainer.full_params()                 # collective on every rank
+                        if rank == 0:
+                            from ..utils.checkpoint import save_checkpoint
+                            save_checkpoint(f"{cfg.save_path}.step{(k + 1) * seeds_per_step}", full, step=(k + 1) * seeds_per_step,
+                                            args=cfg.to_dict(), seeds=seeds)
+            else:
+                trainer.run(batches)
     ms = max_over_ranks(t.ms, comm, device)
     steps = len(my_seeds)
-    global_tokens = tokens * (world if method in ("ddp", "fsdp") else 1)
+    global_tokens = tokens * seeds_per_step
     if rank == 0:
         stats[0] = ms
         stats[1] = tokens_per_second(global_tokens, steps, ms)
+        # model FLOPs: 6 GEMMs of 2*T*D*F per block-step (the reference executes a 7th, recomputing h, train_ffns.py:63)
+        stats[2] = 12.0 * global_tokens * cfg.model_size * cfg.ffn_dim * cfg.layers * steps / (ms * 1e-3) / 1e12 if ms > 0 else 0.0
+        stats[3] = torch.cuda.max_memory_allocated(device) / 2 ** 30 if device.type == "cuda" else 0.0
     _write_back(method, trainer, comm, out_params)
 
 
@@ -141,14 +155,15 @@ def _run(method: str, layers_params: Sequence[Params], seeds: torch.Tensor, toke
         raise AssertionError(f"len(seeds)={len(seeds)} must be divisible by the world size {world}")   # :175, :263
     shared_in = [[p.detach().clone().share_memory_() for p in lp] for lp in layers_params]
     out = [[torch.empty_like(p).share_memory_() for p in lp] for lp in layers_params]
-    stats = torch.zeros(2, dtype=torch.float64).share_memory_()
+    stats = torch.zeros(4, dtype=torch.float64).share_memory_()
     args = (method, cfg.to_dict(), shared_in, seeds, tokens, model_size, out, stats)
     if world == 1:
         dev = torch.device("cuda", 0) if device == "cuda" else torch.device("cpu")
         _rank_main(0, 1, dev, *args)
     else:
         launch(world, _rank_main, args, backend=backend, device=device, port=cfg.master_port if cfg.master_port != 29500 else 0)
-    _run.last_stats = {"ms": float(stats[0]), "tokens_per_s": float(stats[1]), "world": world}
+    _run.last_stats = {"ms": float(stats[0]), "tokens_per_s": float(stats[1]), "model_tflops": float(stats[2]),
+                       "max_mem_gib": float(stats[3]), "world": world}
     return [list(lp) for lp in out]
 
 

@@ -49,3 +49,29 @@ def test_profile_flag_exports_chrome_trace(tmp_path, monkeypatch):
     monkeypatch.chdir(tmp_path)
     assert train_ffns.main(["-s", "2", "-bs", "2", "-n", "8", "-l", "1", "-d", "16", "-m", "1", "--device", "cpu", "--profile"]) == 0
     assert os.path.getsize(tmp_path / "trace_profiler_trace.json") > 0                   # :139
+
+
+@pytest.mark.timeout(600)
+def test_save_every_writes_intermediate_full_checkpoints(tmp_path):
+    ck = str(tmp_path / "ck.pt")
+    assert train_ffns.main(BASE + ["-m", "3", "--save_path", ck, "--save_every", "1"]) == 0      # FSDP: shards gathered
+    a = torch.load(ck + ".step2", weights_only=False)
+    b = torch.load(ck + ".step4", weights_only=False)
+    end = torch.load(ck, weights_only=False)
+    assert a["step"] == 2 and b["step"] == 4 and a["model"]["layers.0.ffn1.weight"].shape == (64, 16)
+    assert not torch.equal(a["model"]["layers.0.ffn1.weight"], b["model"]["layers.0.ffn1.weight"])
+    assert torch.equal(b["model"]["layers.0.ffn1.weight"], end["model"]["layers.0.ffn1.weight"])
+
+
+def test_bench_contract_without_a_gpu(capsys, monkeypatch):
+    """On a box with no CUDA device both arms print one JSON line saying so and exit 0."""
+    import json
+    import sys
+    import bench
+    for impl in ("ours", "reference"):
+        monkeypatch.setattr(sys, "argv", ["bench.py", "--impl", impl])
+        if torch.cuda.is_available():
+            pytest.skip("GPU present")
+        assert bench.main() == 0
+        line = capsys.readouterr().out.strip().splitlines()[-1]
+        assert "unavailable" in json.loads(line)

@@ -51,6 +51,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--master_port', type=int, default=29500)
     p.add_argument('--save_path', default=None)
     p.add_argument('--load_path', default=None)
+    p.add_argument('--save_every', type=int, default=0, help='also checkpoint every N optimizer steps (needs --save_path)')
     p.add_argument('--profile', action='store_true')
     p.add_argument('--data', default='cpu', choices=['cpu', 'device'])
     return p
@@ -97,7 +98,8 @@ def main(argv=None) -> int:
             fns_layers_params.append(out)
             st = api.last_stats()
             print(f'\n{fn.__name__} takes {t1 - t0} seconds')
-            print(f'{fn.__name__} device time {st.get("ms", 0.0):.3f} ms, {st.get("tokens_per_s", 0.0):.1f} tokens/s '
+            print(f'{fn.__name__} device time {st.get("ms", 0.0):.3f} ms, {st.get("tokens_per_s", 0.0):.1f} tokens/s, '
+                  f'{st.get("model_tflops", 0.0):.2f} model TFLOP/s, peak {st.get("max_mem_gib", 0.0):.2f} GiB '
                   f'on {st.get("world", 1)} rank(s) (device-timed, max over ranks)')
             print(f'final {fn.__name__} layers_params[0]', out[0][0].shape, out[0][1].shape)
             print(f'final {fn.__name__} layers_params[0]', out[0][0][:5, :5], out[0][1][:5, :5])
