@@ -38,7 +38,7 @@ def parse_args():
     ap.add_argument("--layers", type=int, default=None)
     ap.add_argument("--batch_size", type=int, default=8)
     ap.add_argument("--seq_len", type=int, default=2048)
-    ap.add_argument("--comm", default="auto", choices=["auto", "fused", "nccl"])
+    ap.add_argument("--comm", default="auto", choices=["auto", "fused", "native", "nccl"])
     ap.add_argument("--ops", default="native", choices=["native", "torch"])
     ap.add_argument("--recompute", action="store_true", help="reference-style activation recompute in backward")
     ap.add_argument("--no-e2e", action="store_true")

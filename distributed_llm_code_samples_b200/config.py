@@ -49,7 +49,7 @@ class TrainConfig:
     backend: str = "auto"                  # auto | nccl | gloo
     device: str = "auto"                   # auto | cuda | cpu
     impl: str = "auto"                     # auto | native (sm_100a kernels) | torch (cuBLAS/ATen fallback + oracle)
-    comm: str = "auto"                     # auto | fused (peer-memory kernels) | nccl (torch.distributed)
+    comm: str = "auto"                     # auto | fused (collective inside the GEMM) | native (peer-memory collectives) | nccl
     recompute: bool = False                # reference recomputes h in backward (:63); we keep it by default
     mp_mode: str = "ar"                    # ar = reference all-reduce form (:303,:309); sp = AG/RS sequence-parallel
     master_port: int = 29500               # train_ffns.py:124

@@ -35,6 +35,13 @@ def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Seque
     """Place/shard the full CPU parameters for this rank and return its trainer."""
     dtype = cfg.torch_dtype
     r, n = comm.rank, comm.world
+    if cfg.comm == "native" and n > 1:
+        # unfused trainers (so Adam / bias / residual / SP all work) on the framework's own peer-memory collectives
+        if device.type != "cuda" or dtype != torch.bfloat16:
+            raise RuntimeError("comm=native needs CUDA and bf16 parameters (the native collectives sum bf16 / fp32)")
+        from .symm import SymmComm, get_symm_world
+        full_bytes = 2 * max(cfg.model_size * cfg.ffn_dim, cfg.tokens * max(cfg.model_size, cfg.ffn_dim // n))
+        comm = SymmComm(get_symm_world(comm, device), staging_bytes=max(64 << 20, full_bytes + 4096), group=getattr(comm, "group", None))
     if method == "single" or n == 1:        # a world of one: every strategy degenerates to the single-device loop
         return SingleTrainer(ops, cfg, place(layers_params, device, dtype))
     if method == "ddp":

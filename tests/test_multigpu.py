@@ -137,6 +137,23 @@ def test_fused_trainer_matches_nccl_trainer(method):
     assert max(u.abs().max().item() for l in uf for u in l) > 0
 
 
+@pytest.mark.parametrize("method,extra", [("ddp", {"optimizer": "adam"}), ("fsdp", {"bias": True}), ("mp", {"residual": True})])
+def test_unfused_trainers_on_native_collectives_match_nccl(method, extra):
+    """--comm native: the plain trainers (so Adam / bias / residual work) with every collective on the peer-memory
+    kernels instead of NCCL; same weights and data must give the NCCL trainers' result to bf16 accuracy."""
+    from distributed_llm_code_samples_b200.models import ffn
+    from distributed_llm_code_samples_b200.parallel import api
+    g = torch.Generator().manual_seed(33)
+    lp = [[p.to(torch.bfloat16).float() for p in l] for l in ffn.init_stack(3, DM, 4 * DM, g, bias=extra.get("bias", False))]
+    seeds = torch.arange(1 if method == "mp" else WORLD)
+    fn = {"ddp": api.train_ddp, "fsdp": api.train_fsdp, "mp": api.train_tp}[method]
+    native = fn(lp, seeds, 512, DM, _cfg(comm="native", lr=1e-3, **extra))
+    nccl = fn(lp, seeds, 512, DM, _cfg(comm="nccl", lr=1e-3, **extra))
+    upd = lambda res: [[p.float() - q for p, q in zip(a, b)] for a, b in zip(res, lp)]
+    assert all(torch.isfinite(p).all() for l in native for p in l)
+    assert _rel(upd(native), upd(nccl)) < 0.25
+
+
 def test_probe_single_process_collectives_and_streams():
     """test_nccl.py / test_torch_cuda_stream.py counterparts: one process, one stream per device."""
     from probes import single_process
