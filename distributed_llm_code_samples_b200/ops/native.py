@@ -100,6 +100,19 @@ def _optional_declare(lib) -> None:
         "b200_sumsq_static_max_elems": ([], ll),
         "b200_sumsq_bf16_static": ([vp, vp, ll, vp], i),
         "b200_all_gather_into_dma": ([vp, pp, ll, ll, pp, i, i, u, vp], i),
+        "b200_fd_listen": ([C.c_char_p], i),
+        "b200_fd_send": ([C.c_char_p, i, i], i),
+        "b200_fd_recv": ([i, C.POINTER(i)], i),
+        "b200_fd_close": ([i], i),
+        "b200_vmm_query": ([C.POINTER(i)], i),
+        "b200_vmm_granularity": ([i, i], ll),
+        "b200_vmm_alloc": ([ll, pp, C.POINTER(C.c_ulonglong), C.POINTER(i)], i),
+        "b200_vmm_import": ([i, ll, pp, C.POINTER(C.c_ulonglong)], i),
+        "b200_vmm_free": ([vp, ll, C.c_ulonglong], i),
+        "b200_mc_create": ([i, ll, C.POINTER(C.c_ulonglong), C.POINTER(i)], i),
+        "b200_mc_import": ([i, C.POINTER(C.c_ulonglong)], i),
+        "b200_mc_attach": ([C.c_ulonglong, i, C.c_ulonglong, ll, pp], i),
+        "b200_all_reduce_nvls_bf16": ([vp, ll, pp, i, i, u, i, vp], i),
         "b200_fused_inbox_bytes": ([i, i], ll),
         "b200_fused_flag_bytes": ([i, i], ll),
         "b200_fused_owned_tiles": ([i, i, i, i], i),

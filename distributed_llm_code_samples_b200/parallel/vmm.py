@@ -1,0 +1,105 @@
+"""EXPERIMENTAL: symmetric blocks on cuMem VMM allocations with an NVLS multicast mapping (``csrc/vmm.cu``).
+
+Same peer-table contract as ``symm.SymmBuffer`` (CUDA IPC), plus ``mc_ptr``: a multicast address on which
+``multimem.ld_reduce`` / ``multimem.st`` reduce and broadcast inside the NVSwitch.  File descriptors travel between the
+ranks of the node over unix datagram sockets (``SCM_RIGHTS``).  Round 1 status: host side unit-tested on CPU
+(``tests/test_vmm_cpu.py``); device side compiled, GPU test queued (``tests/test_multigpu.py::test_vmm_multicast_all_reduce``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import tempfile
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import native as nv
+
+
+def supported() -> tuple[bool, bool]:
+    """(posix-fd export, multicast) support of the current device."""
+    out = (C.c_int * 2)()
+    if nv.load().b200_vmm_query(out) != 0:
+        return False, False
+    return bool(out[0]), bool(out[1])
+
+
+def _sock_path(tag: str, rank: int) -> str:
+    return os.path.join(tempfile.gettempdir(), f"b200ffn_{tag}_{rank}.sock")
+
+
+class VmmBuffer:
+    """One shareable block per rank, every peer's block mapped locally, optional multicast mapping of all of them."""
+
+    def __init__(self, rank: int, world: int, device: torch.device, nbytes: int, multicast: bool = True,
+                 group: Optional[dist.ProcessGroup] = None, tag: str = "blk"):
+        lib = nv.load()
+        torch.cuda.set_device(device)
+        self.rank, self.world, self.device = rank, world, device
+        gran = int(lib.b200_vmm_granularity(world, int(multicast)))
+        if gran <= 0:
+            raise nv.NativeError("VMM allocation granularity query failed: " + lib.b200_last_error().decode())
+        self.nbytes = (nbytes + gran - 1) // gran * gran
+        tag = f"{tag}{os.getpid() if world == 1 else ''}"
+        ptr, handle, fd = C.c_void_p(), C.c_ulonglong(), C.c_int()
+        nv._check(lib.b200_vmm_alloc(self.nbytes, C.byref(ptr), C.byref(handle), C.byref(fd)), "b200_vmm_alloc")
+        self.ptr, self.handle = ptr.value, handle.value
+        self.peer_ptrs: List[int] = [0] * world
+        self.peer_handles: List[int] = [0] * world
+        self.peer_ptrs[rank] = self.ptr
+        # every rank listens, then sends its fd to every peer (tag = sender rank), then receives world-1 fds
+        sock = lib.b200_fd_listen(_sock_path(tag, rank).encode())
+        if sock < 0:
+            raise nv.NativeError(lib.b200_last_error().decode())
+        if world > 1:
+            dist.barrier(group=group)
+        for q in range(world):
+            if q != rank:
+                nv._check(lib.b200_fd_send(_sock_path(tag, q).encode(), fd.value, rank), "b200_fd_send")
+        for _ in range(world - 1):
+            src = C.c_int()
+            rfd = lib.b200_fd_recv(sock, C.byref(src))
+            if rfd < 0:
+                raise nv.NativeError(lib.b200_last_error().decode())
+            p, h = C.c_void_p(), C.c_ulonglong()
+            nv._check(lib.b200_vmm_import(rfd, self.nbytes, C.byref(p), C.byref(h)), "b200_vmm_import")
+            lib.b200_fd_close(rfd)
+            self.peer_ptrs[src.value], self.peer_handles[src.value] = p.value, h.value
+        lib.b200_fd_close(fd.value)
+        self.peers_c = (C.c_void_p * world)(*self.peer_ptrs)
+        self.mc_ptr: Optional[int] = None
+        if multicast and world > 1:
+            mc = C.c_ulonglong()
+            if rank == 0:
+                mfd = C.c_int()
+                nv._check(lib.b200_mc_create(world, self.nbytes, C.byref(mc), C.byref(mfd)), "b200_mc_create")
+                for q in range(1, world):
+                    nv._check(lib.b200_fd_send(_sock_path(tag, q).encode(), mfd.value, -1), "b200_fd_send(mc)")
+                lib.b200_fd_close(mfd.value)
+            else:
+                src = C.c_int()
+                rfd = lib.b200_fd_recv(sock, C.byref(src))
+                nv._check(lib.b200_mc_import(rfd, C.byref(mc)), "b200_mc_import")
+                lib.b200_fd_close(rfd)
+            nv._check(lib.b200_mc_attach(mc.value, 1, 0, 0, None), "b200_mc_attach(add device)")
+            dist.barrier(group=group)                      # every device must be added before anyone binds
+            mp = C.c_void_p()
+            nv._check(lib.b200_mc_attach(mc.value, 2, self.handle, self.nbytes, C.byref(mp)), "b200_mc_attach(bind)")
+            dist.barrier(group=group)
+            self.mc_ptr, self.mc_handle = mp.value, mc.value
+        lib.b200_fd_close(sock)
+        try:
+            os.unlink(_sock_path(tag, rank))
+        except OSError:
+            pass
+
+    def tensor(self, offset_bytes: int, shape, dtype: torch.dtype) -> torch.Tensor:
+        from .symm import _CudaArray
+        base = torch.as_tensor(_CudaArray(self.ptr, self.nbytes), device=self.device)
+        n = 1
+        for s in shape:
+            n *= s
+        nb = n * torch.empty((), dtype=dtype).element_size()
+        return base[offset_bytes: offset_bytes + nb].view(dtype).view(*shape)

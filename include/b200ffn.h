@@ -168,6 +168,30 @@ int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const vo
                              int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
                              float alpha, int max_ctas, void* stream);
 
+/* ---- EXPERIMENTAL: cuMem VMM blocks + NVLS multicast (csrc/vmm.cu) -----------------------------------------------
+ * The runtime the in-switch reductions need; not used by the default training paths.  Host-side fd
+ * passing is unit-tested on CPU; the device side has GPU tests queued (tests/test_multigpu.py::test_vmm_*).
+ * Descriptor passing between the ranks of one node (SCM_RIGHTS over a unix datagram socket): */
+int b200_fd_listen(const char* path);              /* returns the listening socket fd */
+int b200_fd_send(const char* path, int fd, int tag);
+int b200_fd_recv(int sock, int* tag_out);          /* returns the received fd */
+int b200_fd_close(int fd);
+/* Shareable blocks: out[0] = POSIX-fd export supported, out[1] = multicast supported (current device). */
+int b200_vmm_query(int* out);
+long long b200_vmm_granularity(int world, int with_multicast);
+int b200_vmm_alloc(long long bytes, void** ptr_out, unsigned long long* handle_out, int* fd_out);
+int b200_vmm_import(int fd, long long bytes, void** ptr_out, unsigned long long* handle_out);
+int b200_vmm_free(void* ptr, long long bytes, unsigned long long handle);
+/* Multicast object: rank 0 creates + exports, the others import; then every rank attaches in two collective steps
+ * (1: add device; host barrier; 2: bind its block, map the multicast VA -> *ptr_out). */
+int b200_mc_create(int world, long long bytes, unsigned long long* mc_out, int* fd_out);
+int b200_mc_import(int fd, unsigned long long* mc_out);
+int b200_mc_attach(unsigned long long mc, int step, unsigned long long mem_handle, long long bytes, void** ptr_out);
+/* In-place bf16 all-reduce through the switch: multimem.ld_reduce (fp32 accumulate) of my slice, multimem.st of the
+ * result to every replica.  Counterpart of train_ffns.py:165/:303 on NVLS. */
+int b200_all_reduce_nvls_bf16(void* mc_ptr, long long bytes, void* const* flag_peers, int rank, int world,
+                              unsigned int epoch, int blocks, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -166,3 +166,50 @@ def test_probe_async_allreduce_and_ipc_barrier():
     from probes import multi_process
     assert multi_process.async_allreduce_side_stream(WORLD)
     assert multi_process.ipc_barrier(WORLD)
+
+
+def _vmm_worker(rank, world, dev, out):
+    import ctypes as C
+    from distributed_llm_code_samples_b200.ops import native as nv
+    from distributed_llm_code_samples_b200.parallel import vmm
+    from distributed_llm_code_samples_b200.parallel.symm import CollChannel, SymmWorld
+    fd_ok, mc_ok = vmm.supported()
+    if not fd_ok:
+        out[rank] = -1.0                                   # unsupported on this box: reported as a skip
+        return
+    n = 1 << 20
+    buf = vmm.VmmBuffer(rank, world, dev, n * 2, multicast=mc_ok, tag="t1")
+    x = buf.tensor(0, (n,), torch.bfloat16)
+    g = torch.Generator().manual_seed(5)
+    allx = [torch.randn(n, generator=g).to(torch.bfloat16) for _ in range(world)]
+    x.copy_(allx[rank].to(dev))
+    torch.cuda.synchronize()
+    # (a) the imported peer blocks are usable as an ordinary peer table: native (P2P) all-reduce on them
+    sw = SymmWorld(rank, world, dev)
+    chan = CollChannel(sw)
+    lib = nv.load()
+    nv._check(lib.b200_all_reduce_bf16(buf.peers_c, 0, n * 2, chan.flags.peers_c, rank, world, chan.next_epoch(), 0, nv._stream()), "all_reduce on VMM blocks")
+    torch.cuda.synchronize()
+    total = sum(t.float() for t in allx)
+    ok = bool((x.float().cpu() - total).abs().max() <= 0.05 * world)
+    # (b) the same sum through the switch
+    if mc_ok and buf.mc_ptr:
+        x.copy_(allx[rank].to(dev))
+        torch.cuda.synchronize()
+        nv._check(lib.b200_all_reduce_nvls_bf16(C.c_void_p(buf.mc_ptr), n * 2, chan.flags.peers_c, rank, world, chan.next_epoch(), 0, nv._stream()),
+                  "b200_all_reduce_nvls_bf16")
+        torch.cuda.synchronize()
+        ok &= bool((x.float().cpu() - total).abs().max() <= 0.05 * world)
+    ok &= nv.device_error()[0] == 0
+    out[rank] = (2.0 if mc_ok else 1.0) if ok else 0.0
+
+
+def test_vmm_multicast_all_reduce():
+    """EXPERIMENTAL runtime (csrc/vmm.cu): cuMem blocks shared by fd, used as a peer table, and - where the box has
+    NVLS - an in-switch all-reduce (multimem.ld_reduce / multimem.st) on the multicast mapping."""
+    from distributed_llm_code_samples_b200.parallel.launcher import launch
+    out = torch.zeros(WORLD).share_memory_()
+    launch(WORLD, _vmm_worker, (out,), backend="nccl", device="cuda")
+    if (out == -1.0).all():
+        pytest.skip("POSIX-fd shareable allocations not supported here")
+    assert (out >= 1.0).all(), out.tolist()
