@@ -213,3 +213,40 @@ def test_vmm_multicast_all_reduce():
     if (out == -1.0).all():
         pytest.skip("POSIX-fd shareable allocations not supported here")
     assert (out >= 1.0).all(), out.tolist()
+
+
+def _stress_worker(rank, world, dev, out):
+    """Flag-protocol stress: hundreds of back-to-back barriers and small all-reduces on alternating
+    sizes with rank-dependent delays in between; any lost or stale flag shows up as a wrong sum or a device timeout."""
+    from distributed_llm_code_samples_b200.ops import native as nv
+    from distributed_llm_code_samples_b200.parallel.symm import SymmComm, SymmWorld
+    sw = SymmWorld(rank, world, dev)
+    comm = SymmComm(sw, staging_bytes=4 << 20)
+    big = sw.alloc(1 << 20).tensor(0, (1 << 19,), torch.bfloat16)
+    ok = True
+    junk = torch.empty(1 << 22, device=dev)
+    for it in range(300):
+        if (it + rank) % 3 == 0:
+            junk.normal_()                                  # skew the ranks
+        n = (8 * world) << (it % 5)
+        t = torch.full((n,), float(rank + 1 + it % 4), dtype=torch.float32, device=dev)
+        comm.all_reduce(t)
+        if it % 7 == 0:
+            comm.barrier()
+        big.fill_(1.0)
+        comm.all_reduce(big)                                # two-shot path, in-place in symmetric memory
+        if it % 50 == 49:
+            torch.cuda.synchronize()
+            expect = sum(r + 1 + it % 4 for r in range(world))
+            ok &= bool((t == expect).all()) and bool((big.float() == world).all())
+    torch.cuda.synchronize()
+    ok &= nv.device_error()[0] == 0
+    out[rank] = 1.0 if ok else 0.0
+    sw.close()
+
+
+def test_barrier_and_flag_protocol_stress():
+    from distributed_llm_code_samples_b200.parallel.launcher import launch
+    out = torch.zeros(WORLD).share_memory_()
+    launch(WORLD, _stress_worker, (out,), backend="nccl", device="cuda")
+    assert out.tolist() == [1.0] * WORLD
