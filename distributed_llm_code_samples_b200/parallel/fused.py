@@ -4,10 +4,10 @@ collectives (``csrc/comm.cu``) - no NCCL on the data path.
 * ``FusedDDPTrainer``  dW GEMM -> (push partial tiles to their owners) -> fp32 sum -> ``W -= lr * sum`` -> new weight
   tile stored into every replica.  Replaces dW GEMM + all_reduce + SGD (``train_ffns.py:66/68, :165, :172``).
 * ``FusedFSDPTrainer`` dW GEMM -> reduce-scatter to the row-shard owner -> sharded SGD in the same kernel
-  (``:253-259``); parameters are unsharded one layer ahead by a pull all-gather on a side stream straight into
-  the contiguous buffer the GEMM reads (``:203-209``, ``:236-249``).
+  (``:253-259``); parameters are unsharded one layer ahead on a side stream by the copy engines (P2P DMA between two
+  one-warp barrier kernels) straight into the contiguous buffer the GEMM reads (``:203-209``, ``:236-249``).
 * ``FusedMPTrainer``   row-parallel GEMM -> all-reduce of the partial activations inside the kernel
-  (``:302-303``, ``:308-309``).
+  (``:302-303``, ``:308-309``), or (``mp_mode="sp"``) -> reduce-scatter over token shards + native all-gather.
 """
 from __future__ import annotations
 
