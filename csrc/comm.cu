@@ -11,32 +11,13 @@
 // Values never reset, so there is no reset race; each kernel consumes three values per call (`3*epoch+k`).
 // Index->block assignment is identical in every phase and on every rank, so a per-block barrier is enough to
 // order "peer q finished phase 1 of the elements I am about to read".
-#include "common.cuh"
+#include "peer_sync.cuh"
 #include "../include/b200ffn.h"
 
 namespace b200 {
 
 constexpr int COLL_THREADS = 256;   // small footprint: must be able to co-reside with a 320-thread GEMM CTA on every SM
 constexpr int COLL_MAX_BLOCKS = 64;
-constexpr int MAX_WORLD = 8;
-
-struct PeerTable {
-    void* p[MAX_WORLD];
-};
-
-// ---- cross-rank barrier among the blocks with the same index ------------------------------------------------
-__device__ __forceinline__ void block_barrier(const PeerTable& flags, int rank, int world, uint32_t value,
-                                              unsigned int* err) {
-    __syncthreads();                                    // every thread's prior writes are issued
-    if (threadIdx.x < world) {
-        fence_acq_rel_sys();                         // ... and ordered before the signal
-        uint32_t* dst = reinterpret_cast<uint32_t*>(flags.p[threadIdx.x]) + blockIdx.x * MAX_WORLD + rank;
-        st_release_sys(dst, value);
-        const uint32_t* mine = reinterpret_cast<const uint32_t*>(flags.p[rank]) + blockIdx.x * MAX_WORLD + threadIdx.x;
-        wait_flag_ge(mine, value, err, 0x500 + threadIdx.x);
-    }
-    __syncthreads();
-}
 
 __global__ void __launch_bounds__(32) barrier_kernel(PeerTable flags, int rank, int world, uint32_t value, unsigned int* err) {
     block_barrier(flags, rank, world, value, err);

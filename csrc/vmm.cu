@@ -10,7 +10,7 @@
 //     the switch-side sum of all replicas.
 // SURVEY.md 5.8 lists this as the target runtime; DESIGN.md section 8 lists it as the next step for the link-bound
 // MP all-reduce.  Nothing in the default training paths depends on this file.
-#include "common.cuh"
+#include "peer_sync.cuh"
 #include "../include/b200ffn.h"
 #include <cudaTypedefs.h>
 #include <cerrno>
@@ -336,24 +336,12 @@ namespace b200 {
 constexpr int NVLS_THREADS = 256;
 constexpr int NVLS_MAX_BLOCKS = 64;
 
-struct NvlsPeers { void* p[8]; };
-
-__device__ __forceinline__ void nvls_barrier(const NvlsPeers& flags, int rank, int world, uint32_t value, unsigned int* err) {
-    __syncthreads();
-    if (threadIdx.x < world) {
-        fence_acq_rel_sys();
-        st_release_sys(reinterpret_cast<uint32_t*>(flags.p[threadIdx.x]) + blockIdx.x * 8 + rank, value);
-        wait_flag_ge(reinterpret_cast<const uint32_t*>(flags.p[rank]) + blockIdx.x * 8 + threadIdx.x, value, err, 0x800 + threadIdx.x);
-    }
-    __syncthreads();
-}
-
-__global__ void __launch_bounds__(NVLS_THREADS) nvls_all_reduce_bf16_kernel(uint4* mc, long long V, NvlsPeers flags, int rank, int world,
+__global__ void __launch_bounds__(NVLS_THREADS) nvls_all_reduce_bf16_kernel(uint4* mc, long long V, PeerTable flags, int rank, int world,
                                                                             uint32_t epoch, unsigned int* err) {
     const long long tstride = (long long)gridDim.x * blockDim.x;
     const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long lo = V * rank / world, hi = V * (rank + 1) / world;
-    nvls_barrier(flags, rank, world, 3 * epoch + 1, err);          // every replica holds its input
+    block_barrier(flags, rank, world, 3 * epoch + 1, err, 0x800);          // every replica holds its input
     for (long long i = lo + t0; i < hi; i += tstride) {
         uint32_t a, b, c, d;
         asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
@@ -363,7 +351,7 @@ __global__ void __launch_bounds__(NVLS_THREADS) nvls_all_reduce_bf16_kernel(uint
         asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc + i), "r"(a), "r"(b), "r"(c), "r"(d)
                      : "memory");
     }
-    nvls_barrier(flags, rank, world, 3 * epoch + 3, err);          // every slice has been written to every replica
+    block_barrier(flags, rank, world, 3 * epoch + 3, err, 0x800);          // every slice has been written to every replica
 }
 
 }  // namespace b200
@@ -376,7 +364,7 @@ extern "C" int b200_all_reduce_nvls_bf16(void* mc_ptr, long long bytes, void* co
         set_last_error("all_reduce_nvls: bad arguments");
         return B200_ERR_ARG;
     }
-    NvlsPeers flags{};
+    PeerTable flags{};
     for (int i = 0; i < world; ++i) {
         if (flag_peers[i] == nullptr) { set_last_error("all_reduce_nvls: null flag pointer for rank %d", i); return B200_ERR_ARG; }
         flags.p[i] = flag_peers[i];
