@@ -1,16 +1,17 @@
 // Fused GEMM + collective: ONE persistent tcgen05 kernel that computes its output tiles and, tile by tile,
 // reduces them across ranks over NVLink peer memory.
 //
-//   push    each finished accumulator tile is converted to bf16, transposed through shared memory so that every
-//           warp store covers whole 128-byte lines, and STORED INTO THE OWNER RANK'S INBOX (a peer pointer); a
-//           release flag per (tile, source) tells the owner it has landed.  The next tile's MMAs are already
-//           running (TMEM double buffer), so the transfer overlaps the math.
-//   reduce  between tiles the epilogue warps poll (non-blocking) the owned tiles assigned to this CTA; a tile whose
-//           `world` partials have all arrived is summed in fp32 in a fixed order, the optional optimizer step is
-//           applied (W -= alpha * sum) and the result is written to the local output and, in broadcast mode, to
-//           every peer's output.  What is still outstanding when the CTA runs out of GEMM tiles is finished in a
-//           blocking tail.
-//   done    in broadcast mode the kernel returns only when every tile of the local output has been delivered.
+//   push    (epilogue warps) each finished accumulator tile is converted to bf16, transposed through shared memory so
+//           that every warp store covers whole 128-byte lines, and STORED INTO THE OWNER RANK'S INBOX (a peer pointer);
+//           a release flag per (tile, source) tells the owner it has landed.
+//   reduce  (side warps, concurrently with the TMA / MMA / epilogue warps) poll the owned tiles assigned to this CTA,
+//           in any order; a tile whose `world` partials have all arrived is summed in fp32 in a fixed source order, the
+//           optional optimizer step is applied (W -= alpha * sum) and the result is written to the local output and,
+//           in broadcast mode, to every peer's output, followed by a per-tile ready flag.
+//   done    the kernel returns when its owned tiles are reduced and, in broadcast mode, every tile of the local output
+//           has been delivered.
+// Compute-bound calls run on the 256x256-per-CTA pair mainloop; link-bound ones on the double-buffered 128x256
+// mainloop whose second accumulator stage absorbs NVLink back-pressure in the epilogue (chosen per call, see below).
 //
 // One kernel therefore covers the reference's
 //   DDP   dW GEMM + all_reduce(SUM) + SGD      (train_ffns.py:66/68 + :165 + :172)   interleaved owners, broadcast, SGD
@@ -19,8 +20,8 @@
 //   MP-SP row-parallel GEMM + reduce_scatter   (sequence-parallel extension)         row-sharded owners, local, SUM
 //
 // Inbox slots are double-buffered by call parity so a fast rank may start the next call while a slow one is still
-// reducing; flags carry a per-channel sequence number (monotonic, never reset).  Ranks rotate their tile order so
-// that at any moment they push to different owners.
+// reducing; flags carry a per-channel sequence number (monotonic, never reset).  With row-sharded owners ranks rotate
+// their tile order so that at any moment they push to different owners (interleaved owners spread by construction).
 #include "gemm_kernel.cuh"
 #include "../include/b200ffn.h"
 #include <cstdlib>
