@@ -1,5 +1,9 @@
-// Persistent, warp-specialised bf16 GEMM for sm_100a: TMA -> 4-stage smem ring -> tcgen05.mma (128x256x16,
-// fp32 accumulators in TMEM, double-buffered) -> tcgen05.ld epilogue.  One CTA per SM.
+// Persistent, warp-specialised bf16 GEMMs for sm_100a: TMA -> 4-stage smem ring -> tcgen05.mma with fp32 accumulators
+// in TMEM -> tcgen05.ld epilogue.  One CTA per SM.  Two kernels share the epilogue policies:
+//   gemm_tcgen05_pair_kernel  (default) clusters of 2 CTAs, cta_group::2, 512x256 tile per pair = 256x256 per CTA: two
+//                             128x256 accumulators (all 512 TMEM columns) share every B stage
+//   gemm_tcgen05_kernel       1 CTA, 128x256 tile, TWO accumulator stages: the epilogue of tile i runs under the MMAs of
+//                             tile i+1 (used when the epilogue is long: link-bound fused collectives)
 //
 //   D[M,N] = sum_k A(m,k) * B(n,k)
 //
