@@ -24,7 +24,19 @@ fn = {
     "cublas_G1": lambda: torch.matmul(x, w1.T, out=h),
     "cublas_G2": lambda: torch.matmul(a, w2.T, out=y),
     "cublas_G4": lambda: torch.matmul(dy.T, a, out=dw),
+    "fused_dw": None,
 }[case]
+if case == "fused_dw":
+    # the fused GEMM + collective kernel in a world of ONE: pushes to its own inbox, side warps reduce + apply SGD
+    import ctypes as C
+    from distributed_llm_code_samples_b200.parallel.symm import SymmWorld
+    from distributed_llm_code_samples_b200.parallel.fused import FusedChannel, _owned_cap, _tiles
+    sw = SymmWorld(0, 1, dev)
+    chan = FusedChannel(sw, _owned_cap([(D, F)], 1, 0), _tiles(D, F))
+    wbuf = sw.alloc(D * F * 2 + 4096)
+    W, off = wbuf.carve((D, F), torch.bfloat16)
+    tab = wbuf.peers_at(off)
+    fn = lambda: chan.gemm(dy, 1, a, 1, D, F, T, tab, F, 0, 0, 1, True, 1e-6)
 for _ in range(iters):
     fn()
 torch.cuda.synchronize()
