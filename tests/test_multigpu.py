@@ -5,7 +5,11 @@ import torch
 
 pytestmark = [pytest.mark.gpu, pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")]
 
+import os
+
 WORLD = min(torch.cuda.device_count(), 8) if torch.cuda.is_available() else 0
+# Tests written after round 1's GPU budget was spent have never run on hardware: they are opt-in until validated.
+queued = pytest.mark.skipif(os.environ.get("B200_QUEUED_TESTS") != "1", reason="queued for the next GPU round (set B200_QUEUED_TESTS=1)")
 DM = max(256, 128 * max(WORLD, 1))
 
 
@@ -137,6 +141,7 @@ def test_fused_trainer_matches_nccl_trainer(method):
     assert max(u.abs().max().item() for l in uf for u in l) > 0
 
 
+@queued
 @pytest.mark.parametrize("method,extra", [("ddp", {"optimizer": "adam"}), ("fsdp", {"bias": True}), ("mp", {"residual": True})])
 def test_unfused_trainers_on_native_collectives_match_nccl(method, extra):
     """--comm native: the plain trainers (so Adam / bias / residual work) with every collective on the peer-memory
@@ -204,6 +209,7 @@ def _vmm_worker(rank, world, dev, out):
     out[rank] = (2.0 if mc_ok else 1.0) if ok else 0.0
 
 
+@queued
 def test_vmm_multicast_all_reduce():
     """EXPERIMENTAL runtime (csrc/vmm.cu): cuMem blocks shared by fd, used as a peer table, and - where the box has
     NVLS - an in-switch all-reduce (multimem.ld_reduce / multimem.st) on the multicast mapping."""
@@ -245,6 +251,7 @@ def _stress_worker(rank, world, dev, out):
     sw.close()
 
 
+@queued
 def test_barrier_and_flag_protocol_stress():
     from distributed_llm_code_samples_b200.parallel.launcher import launch
     out = torch.zeros(WORLD).share_memory_()
