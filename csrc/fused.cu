@@ -92,11 +92,13 @@ struct FusedEpiT {
     using Params = FusedParams;
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
     static constexpr int EXTRA_WARPS = SIDE_WARPS;   // side warps reduce/broadcast owned tiles under the MMAs
+    static constexpr int LAUNCH_BOUND_PAD = 32;      // a one-warp barrier kernel of another stream (FSDP prefetch) must fit beside it
     struct State {
         int k_local;               // inbox slot of the tile being pushed
         int owner;
     };
 
+    static __device__ __forceinline__ void before_loads(const Params&, const GemmCore&, int, int) {}
     static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx&, State& st) {
         st.k_local = 0;
         st.owner = 0;

@@ -1,0 +1,229 @@
+// All-gather -> GEMM in ONE kernel (sequence-parallel MP: the column-parallel GEMM whose A operand is the token-sharded
+// activation, SURVEY.md 2.6 C4/C5 "SP form"; no counterpart in the reference, which all-reduces instead,
+// train_ffns.py:303,:309).
+//
+//   A is [M, K] bf16, K-major, contiguous, and lives at the SAME offset of a symmetric block on every rank.  Rank q
+//   holds the final values of rows [q*M/world, (q+1)*M/world) only (its token shard).  The kernel computes
+//   C = epilogue(A_full * B^T) and, as a side effect, completes the local copy of A_full.
+//
+//   side warps   (2 per CTA, concurrently with the TMA / MMA / epilogue warps) pull the other ranks' shards over NVLink
+//                into the local buffer, 16/32 KiB chunks in the order the GEMM will need them (ring order starting at
+//                the next rank), and count finished chunks per 128-row block (red.release.gpu).
+//   TMA producer before loading a tile's A rows it waits until those 128-row blocks are complete (ld.acquire.gpu +
+//                a generic->async proxy fence); tiles are walked starting at the rank's own shard, so the first wave
+//                needs no remote data at all and the pull runs ahead of the MMAs from then on.
+//   cross-rank   one flag per (reader, owner): "owner's kernel for call `seq` has started", i.e. everything that was
+//                stream-ordered before it - the kernel that produced its shard - has completed.  Nothing else is
+//                exchanged; the kernel never waits for a peer to finish READING (see the reuse rules in
+//                docs/KERNELS.md section 2.5 - callers keep a barrier-ed collective between reuse of a shard buffer).
+//
+// STATUS: written after round 1's GPU budget was spent - compiles for sm_100a, host-side maps are tested on the CPU,
+// never run on hardware.  Opt-in (TrainConfig.mp_mode = "spf").
+#include "gemm_kernel.cuh"
+#include "peer_sync.cuh"
+#include "../include/b200ffn.h"
+
+namespace b200 {
+
+constexpr int GATHER_SIDE_WARPS = 2;        // 320 + 64 = 384 threads: one more warp would cap registers at 128/thread
+constexpr int GATHER_BATCH = 16;            // 16-byte loads in flight per lane (peer reads: ~2-3 us round trip)
+
+struct GatherParams {
+    LocalEpiParams base;
+    const uint4* src[MAX_WORLD];            // every rank's A buffer
+    uint4* dst;                             // the local A buffer (= src[rank])
+    uint32_t* started[MAX_WORLD];           // symmetric flag arrays: started[q][r] = last call rank r has entered
+    uint32_t* ready;                        // local: finished chunks per 128-row block, zeroed before the launch
+    long long shard_vecs;                   // 16-byte vectors per token shard
+    int chunk_vecs;                         // vectors per pull chunk
+    int chunks_per_block;                   // chunks per 128-row block
+    int blocks_per_shard;                   // 128-row blocks per token shard
+    int rank, world;
+    uint32_t seq;
+};
+
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+__device__ __forceinline__ void red_release_gpu_add(uint32_t* p, uint32_t v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Pull order.  Chunk u of the (world-1) * chunks_per_shard remote chunks: ring distance d = 1 + u / chunks_per_shard
+// (the rank after mine first: its rows follow mine in the rotated tile walk), chunk j = u % chunks_per_shard of it.
+struct ChunkRef {
+    int peer;
+    long long first_vec;                    // vector index in the full A buffer
+    int block;                              // 128-row block the chunk belongs to
+};
+__host__ __device__ __forceinline__ ChunkRef chunk_ref(long long u, int rank, int world, long long shard_vecs, int chunk_vecs,
+                                                       int chunks_per_block, int blocks_per_shard) {
+    const long long cps = shard_vecs / chunk_vecs;
+    const int d = 1 + (int)(u / cps);
+    const long long j = u % cps;
+    ChunkRef r;
+    r.peer = (rank + d) % world;
+    r.first_vec = (long long)r.peer * shard_vecs + j * chunk_vecs;
+    r.block = r.peer * blocks_per_shard + (int)(j / chunks_per_block);
+    return r;
+}
+
+template <int KIND>
+struct GatherEpi {
+    using Local = LocalEpi<KIND>;
+    using Params = GatherParams;
+    using State = typename Local::State;
+    static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
+    static constexpr int EXTRA_WARPS = GATHER_SIDE_WARPS;
+    static constexpr int LAUNCH_BOUND_PAD = 0;       // 384 threads: the epilogue warps keep 168 registers
+
+    static __device__ __forceinline__ void init(const Params& p, const GemmCore& g, const EpiCtx& c, State& s) { Local::init(p.base, g, c, s); }
+    static __device__ __forceinline__ void process_tile(const Params& p, const GemmCore& g, const EpiCtx& c, uint32_t taddr, State& s) {
+        Local::process_tile(p.base, g, c, taddr, s);
+    }
+    static __device__ __forceinline__ void after_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {}
+    static __device__ __forceinline__ void after_skipped_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {}
+    static __device__ __forceinline__ void tail(const Params&, const GemmCore&, const EpiCtx&, State&) {}
+
+    // TMA producer thread: the A rows of blocks [m_blk, m_blk + n) must be complete in the local buffer
+    static __device__ __forceinline__ void before_loads(const Params& p, const GemmCore& g, int m_blk, int n) {
+        if (p.world == 1) return;
+        for (int i = 0; i < n; ++i) {
+            const int b = m_blk + i;
+            if (b >= g.tiles_m || b / p.blocks_per_shard == p.rank) continue;      // ragged tail / my own shard
+            long long t0 = clock64();
+            uint32_t spins = 0;
+            while (ld_acquire_gpu(p.ready + b) < (uint32_t)p.chunks_per_block) {
+                __nanosleep(64);
+                if (((++spins) & 0xff) == 0 && (clock64() - t0) > B200_FLAG_TIMEOUT_CYCLES) device_fail(g.err, ERR_FLAG_TIMEOUT, 0xA00 + (b & 0xff));
+            }
+        }
+        fence_proxy_async_global();          // the rows were written with generic stores; TMA reads them via the async proxy
+    }
+
+    static __device__ __forceinline__ void side_loop(const Params& p, const GemmCore& g, int swarp, int lane, uint32_t*) {
+        if (p.world == 1) return;
+        if (blockIdx.x == 0 && swarp == 0 && lane < p.world && lane != p.rank) {
+            fence_acq_rel_sys();
+            st_release_sys(p.started[lane] + p.rank, p.seq);     // "my shard is final" (this kernel is stream-ordered after its producer)
+        }
+        const long long total = (p.shard_vecs / p.chunk_vecs) * (p.world - 1);
+        const long long W = (long long)gridDim.x * EXTRA_WARPS;
+        uint32_t seen = 0;
+        for (long long u = (long long)swarp * gridDim.x + blockIdx.x; u < total; u += W) {
+            const ChunkRef c = chunk_ref(u, p.rank, p.world, p.shard_vecs, p.chunk_vecs, p.chunks_per_block, p.blocks_per_shard);
+            if (!((seen >> c.peer) & 1u)) {
+                if (lane == 0) wait_flag_ge(p.started[p.rank] + c.peer, p.seq, g.err, 0x900 + c.peer);
+                __syncwarp();
+                seen |= 1u << c.peer;
+            }
+            const uint4* s = p.src[c.peer] + c.first_vec;
+            uint4* d = p.dst + c.first_vec;
+#pragma unroll 1
+            for (int i = lane; i < p.chunk_vecs; i += 32 * GATHER_BATCH) {
+                uint4 v[GATHER_BATCH];
+#pragma unroll
+                for (int b = 0; b < GATHER_BATCH; ++b)
+                    if (i + b * 32 < p.chunk_vecs) v[b] = ld_cv_u4(s + i + b * 32);
+#pragma unroll
+                for (int b = 0; b < GATHER_BATCH; ++b)
+                    if (i + b * 32 < p.chunk_vecs) st_u4(d + i + b * 32, v[b]);
+            }
+            fence_proxy_async_global();
+            __syncwarp();                                        // every lane's stores are issued ...
+            if (lane == 0) {
+                fence_acq_rel_gpu();                             // ... and ordered before the count
+                red_release_gpu_add(p.ready + c.block, 1u);
+            }
+        }
+    }
+};
+
+template <int KIND>
+static int launch_kind(const GemmOperands& o, const GatherParams& p, int max_ctas, cudaStream_t st) {
+    // walk the tiles starting at my own shard; rasterisation groups no larger than a shard keep the walk shard by shard
+    const int group_m = p.blocks_per_shard < 16 ? p.blocks_per_shard : 16;
+    return launch_gemm<GatherEpi<KIND>>(o, p, max_ctas, st, p.rank, p.world, false, group_m);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// Pull-chunk size for a K-wide bf16 A operand: 32 KiB when a 128-row block is a whole number of them, else 16 KiB
+// (K % 64 == 0 makes a block a multiple of 16 KiB).
+static int gather_chunk_bytes(int K) { return (256ll * K) % 32768 == 0 ? 32768 : 16384; }
+
+extern "C" long long b200_gather_gemm_ready_bytes(int M) { return (long long)((M + BM - 1) / BM) * 4; }
+
+// Host mirror of the pull order for CPU tests: out = {peer, first_vec, block, chunk_vecs, chunks_per_block, total_chunks}
+extern "C" int b200_debug_gather_chunk(int M, int K, int rank, int world, long long u, long long* out) {
+    if (world < 1 || world > MAX_WORLD || M % (BM * world) || K % BK) return B200_ERR_ARG;
+    const int cb = gather_chunk_bytes(K);
+    const long long shard_vecs = (long long)(M / world) * K * 2 / 16;
+    const int chunk_vecs = cb / 16, cpb = (int)(256ll * K / cb), bps = M / world / BM;
+    out[3] = chunk_vecs; out[4] = cpb; out[5] = (shard_vecs / chunk_vecs) * (world - 1);
+    if (u < 0 || u >= out[5]) return 0;
+    const ChunkRef c = chunk_ref(u, rank, world, shard_vecs, chunk_vecs, cpb, bps);
+    out[0] = c.peer; out[1] = c.first_vec; out[2] = c.block;
+    return 0;
+}
+
+extern "C" int b200_gather_gemm_bf16(void* const* a_peers, const void* B, long long ldb, int b_major, void* Cout, long long ldc,
+                                     int M, int N, int K, int epilogue, const void* aux, long long ldaux, void* out2, long long ldc2,
+                                     const float* bias, float alpha, void* const* started_peers, void* ready, int rank, int world,
+                                     unsigned int seq, int max_ctas, void* stream) {
+    if (world < 1 || world > MAX_WORLD || rank < 0 || rank >= world) { set_last_error("gather_gemm: bad rank/world"); return B200_ERR_ARG; }
+    if (a_peers == nullptr || started_peers == nullptr || ready == nullptr || Cout == nullptr) { set_last_error("gather_gemm: null argument"); return B200_ERR_ARG; }
+    if (seq == 0) { set_last_error("gather_gemm: seq must start at 1"); return B200_ERR_ARG; }
+    if (M % (BM * world)) { set_last_error("gather_gemm: M (%d) must be a multiple of 128 * world (%d)", M, BM * world); return B200_ERR_ARG; }
+    if (K % BK) { set_last_error("gather_gemm: K (%d) must be a multiple of 64", K); return B200_ERR_ARG; }
+    GatherParams p{};
+    for (int i = 0; i < world; ++i) {
+        if (a_peers[i] == nullptr || started_peers[i] == nullptr || (reinterpret_cast<uintptr_t>(a_peers[i]) & 127)) {
+            set_last_error("gather_gemm: peer %d pointer null or not 128-byte aligned", i); return B200_ERR_ARG;
+        }
+        p.src[i] = reinterpret_cast<const uint4*>(a_peers[i]);
+        p.started[i] = reinterpret_cast<uint32_t*>(started_peers[i]);
+    }
+    p.dst = reinterpret_cast<uint4*>(a_peers[rank]);
+    p.ready = reinterpret_cast<uint32_t*>(ready);
+    const int cb = gather_chunk_bytes(K);
+    p.shard_vecs = (long long)(M / world) * K * 2 / 16;
+    p.chunk_vecs = cb / 16;
+    p.chunks_per_block = (int)(256ll * K / cb);
+    p.blocks_per_shard = M / world / BM;
+    p.rank = rank; p.world = world; p.seq = seq;
+    p.base.C = Cout; p.base.ldc = ldc; p.base.aux = reinterpret_cast<const __nv_bfloat16*>(aux); p.base.ldaux = ldaux;
+    p.base.C2 = reinterpret_cast<__nv_bfloat16*>(out2); p.base.ldc2 = ldc2; p.base.bias = bias; p.base.alpha = alpha;
+    const bool needs_aux = epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD || epilogue == EPI_RELU_BWD_MASK;
+    const bool needs_out2 = epilogue == EPI_GELU || epilogue == EPI_RELU_MASK;
+    if (needs_aux && (aux == nullptr || (reinterpret_cast<uintptr_t>(aux) & 15))) { set_last_error("gather_gemm: epilogue %d needs a 16-byte aligned aux", epilogue); return B200_ERR_ARG; }
+    if (needs_out2 && (out2 == nullptr || (reinterpret_cast<uintptr_t>(out2) & 15))) { set_last_error("gather_gemm: epilogue %d needs a 16-byte aligned out2", epilogue); return B200_ERR_ARG; }
+    const long long mask_pitch = ((N + 127) / 128) * 16;             // bytes per row of a packed ReLU sign mask
+    if ((epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD) && (ldaux % 8 || ldaux < N)) { set_last_error("gather_gemm: ldaux must be >= N and a multiple of 8"); return B200_ERR_ARG; }
+    if (epilogue == EPI_GELU && (ldc2 % 8 || ldc2 < N)) { set_last_error("gather_gemm: ldc2 must be >= N and a multiple of 8"); return B200_ERR_ARG; }
+    if (epilogue == EPI_RELU_MASK && (ldc2 % 16 || ldc2 < mask_pitch)) { set_last_error("gather_gemm: RELU_MASK needs out2 = uint8 mask with pitch %% 16 == 0 and >= %lld bytes", mask_pitch); return B200_ERR_ARG; }
+    if (epilogue == EPI_RELU_BWD_MASK && (ldaux % 16 || ldaux < mask_pitch)) { set_last_error("gather_gemm: RELU_BWD_MASK needs aux = uint8 mask with pitch %% 16 == 0 and >= %lld bytes", mask_pitch); return B200_ERR_ARG; }
+    if (reinterpret_cast<uintptr_t>(Cout) & 15) { set_last_error("gather_gemm: C must be 16-byte aligned"); return B200_ERR_ARG; }
+    if (ldc % 8 || ldc < N) { set_last_error("gather_gemm: ldc must be >= N and a multiple of 8"); return B200_ERR_ARG; }
+    GemmOperands o{a_peers[rank], (long long)K, MAJOR_K, B, ldb, b_major, M, N, K};
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (world > 1) {
+        if (int rc = check_cuda(cudaMemsetAsync(ready, 0, (size_t)b200_gather_gemm_ready_bytes(M), st), "gather_gemm: clear ready counters")) return rc;
+    }
+    switch (epilogue) {
+        case EPI_STORE: return launch_kind<EPI_STORE>(o, p, max_ctas, st);
+        case EPI_RELU: return launch_kind<EPI_RELU>(o, p, max_ctas, st);
+        case EPI_GELU: return launch_kind<EPI_GELU>(o, p, max_ctas, st);
+        case EPI_RELU_BWD: return launch_kind<EPI_RELU_BWD>(o, p, max_ctas, st);
+        case EPI_GELU_BWD: return launch_kind<EPI_GELU_BWD>(o, p, max_ctas, st);
+        case EPI_RELU_MASK: return launch_kind<EPI_RELU_MASK>(o, p, max_ctas, st);
+        case EPI_RELU_BWD_MASK: return launch_kind<EPI_RELU_BWD_MASK>(o, p, max_ctas, st);
+        default: set_last_error("gather_gemm: unsupported epilogue %d", epilogue); return B200_ERR_ARG;
+    }
+}

@@ -94,10 +94,14 @@ __device__ __forceinline__ SmemView carve_smem(uint8_t* raw) {
 //   static __device__ void after_tile(const Params&, const GemmCore&, const EpiCtx&, State&)
 //        runs after the accumulator stage has been handed back to the MMA warp (signals, opportunistic work)
 //   static __device__ void tail(const Params&, const GemmCore&, const EpiCtx&, State&)   (after the last tile)
-//   (with EXTRA_WARPS > 0 the launch bound is one warp larger than the launch, which caps registers at 152/thread and
-//    leaves room on every SM for a one-warp barrier kernel of a concurrent stream)
+//   static constexpr int LAUNCH_BOUND_PAD;   threads added to the launch bound beyond the launch itself: 32 keeps room on
+//        every SM (registers) for a one-warp barrier kernel of a concurrent stream (fused.cu); 0 otherwise.  ptxas
+//        budgets registers for the bound rounded up to 128 threads: 320 -> 168/thread, 384 -> 168, above 384 -> 128.
 //   static constexpr int EXTRA_WARPS;  static __device__ void side_loop(Params, GemmCore, side_warp, lane, scratch)
 //        extra warps (between the MMA warp and the epilogue warps) that run side_loop concurrently with the GEMM
+//   static __device__ void before_loads(const Params&, const GemmCore&, int m_blk, int n_blks)
+//        called by the TMA producer thread before it loads A rows of 128-row blocks [m_blk, m_blk + n_blks) for a
+//        tile: a policy whose A operand is still being assembled (gather_gemm.cu) waits here; empty otherwise
 // ---------------------------------------------------------------------------------------------
 struct EpiCtx {
     int tile;        // linear tile index in the scheduler's order
@@ -112,7 +116,7 @@ struct EpiCtx {
 };
 
 template <class Epi>
-__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + (Epi::EXTRA_WARPS ? 32 : 0), 1)
+__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + Epi::LAUNCH_BOUND_PAD, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmCore g, const typename Epi::Params ep) {
     extern __shared__ uint8_t smem_raw[];
@@ -155,6 +159,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             int m_blk, n_blk;
             tile_coords(g, tile, m_blk, n_blk);
             const int m0 = m_blk * BM, n0 = n_blk * BN;
+            Epi::before_loads(ep, g, m_blk, 1);
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&sm.empty[s], phase ^ 1, g.err, 0x100 + s);
                 mbar_arrive_expect_tx(&sm.full[s], STAGE_BYTES);
@@ -274,7 +279,7 @@ constexpr int P_STAGE_BYTES = P_A_STAGE_BYTES + P_B_STAGE_BYTES;
 static_assert(P_STAGES * P_STAGE_BYTES == STAGES * STAGE_BYTES, "both variants use the same smem carve-up");
 
 template <class Epi>
-__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + (Epi::EXTRA_WARPS ? 32 : 0), 1)
+__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + Epi::LAUNCH_BOUND_PAD, 1)
 gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const GemmCore g, const typename Epi::Params ep) {
     extern __shared__ uint8_t smem_raw[];
@@ -342,6 +347,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             pair_coords(tile, pm, n_blk);
             const int m0 = (pm * 4 + (int)rank * 2) * BM;        // my 256 rows of A
             const int n0 = n_blk * BN + (int)rank * 128;         // my 128 rows of B
+            Epi::before_loads(ep, g, pm * 4 + (int)rank * 2, 2);
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&empty[s], phase ^ 1, g.err, 0x100 + s);
                 // The peer's bytes may land before this arrival: the transaction count just goes negative for a
@@ -543,7 +549,9 @@ struct LocalEpi {
     using Params = LocalEpiParams;
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
     static constexpr int EXTRA_WARPS = 0;
+    static constexpr int LAUNCH_BOUND_PAD = 0;
     static __device__ __forceinline__ void side_loop(const Params&, const GemmCore&, int, int, uint32_t*) {}
+    static __device__ __forceinline__ void before_loads(const Params&, const GemmCore&, int, int) {}
     // a second bf16 [M,N] operand is read by these epilogues: aux, or (SGD) the weight tile itself
     static constexpr bool READS = (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD || KIND == EPI_SGD);
     struct State {};
@@ -683,7 +691,7 @@ bool use_pair_kernel();   // runtime switch (B200_GEMM_PAIR=0 selects the 1-CTA 
 
 template <class Epi>
 int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_ctas, cudaStream_t stream,
-                int tile_offset_num = 0, int tile_offset_den = 1, bool overlap_epilogue = false) {
+                int tile_offset_num = 0, int tile_offset_den = 1, bool overlap_epilogue = false, int group_m = 0) {
     GemmCore core;
     alignas(64) CUtensorMap tmA, tmB;
     // overlap_epilogue: the epilogue is long (peer-memory pushes, cross-rank reduction), so use the kernel whose two
@@ -692,6 +700,7 @@ int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_c
     const bool pair = use_pair_kernel() && !overlap_epilogue;
     int rc = make_core_and_maps(o, &core, &tmA, &tmB, pair);
     if (rc != 0) return rc;
+    if (group_m > 0) core.group_m = group_m;   // rasterisation group (128-row blocks); callers align it with a row shard
     static unsigned long long attr_mask = 0;   // per template instantiation, one bit per device
     int dev = 0;
     cudaGetDevice(&dev);

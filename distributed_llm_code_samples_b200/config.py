@@ -51,7 +51,7 @@ class TrainConfig:
     impl: str = "auto"                     # auto | native (sm_100a kernels) | torch (cuBLAS/ATen fallback + oracle)
     comm: str = "auto"                     # auto | fused (collective inside the GEMM) | native (peer-memory collectives) | nccl
     recompute: bool = False                # reference recomputes h in backward (:63); we keep it by default
-    mp_mode: str = "ar"                    # ar = reference all-reduce form (:303,:309); sp = AG/RS sequence-parallel
+    mp_mode: str = "ar"                    # ar = reference all-reduce form (:303,:309); sp = AG/RS sequence-parallel; spf = sp with the AG inside the GEMM
     master_port: int = 29500               # train_ffns.py:124
     save_path: Optional[str] = None
     load_path: Optional[str] = None
@@ -67,8 +67,8 @@ class TrainConfig:
             raise ValueError("activation must be relu or gelu")
         if self.optimizer not in ("sgd", "adam"):
             raise ValueError("optimizer must be sgd or adam")
-        if self.mp_mode not in ("ar", "sp"):
-            raise ValueError("mp_mode must be ar or sp")
+        if self.mp_mode not in ("ar", "sp", "spf"):
+            raise ValueError("mp_mode must be ar, sp or spf")
         parse_dtype(self.dtype)
 
     @property

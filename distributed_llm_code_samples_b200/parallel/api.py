@@ -73,8 +73,10 @@ def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
         ok = ok and cfg.model_size % (128 * comm.world) == 0 and cfg.ffn_dim % (128 * comm.world) == 0
     if method == "mp":
         ok = ok and not cfg.residual and (cfg.ffn_dim // comm.world) % 8 == 0
-        if cfg.mp_mode == "sp":
+        if cfg.mp_mode in ("sp", "spf"):
             ok = ok and cfg.tokens % (128 * comm.world) == 0
+        if cfg.mp_mode == "spf":
+            ok = ok and cfg.model_size % 64 == 0
     if not ok:
         if cfg.comm == "fused":
             raise RuntimeError("comm=fused needs impl=native, bf16, SGD, no bias, world>1, dims % 8 == 0 "

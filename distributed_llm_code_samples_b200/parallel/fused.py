@@ -7,7 +7,8 @@ collectives (``csrc/comm.cu``) - no NCCL on the data path.
   (``:253-259``); parameters are unsharded one layer ahead on a side stream by the copy engines (P2P DMA between two
   one-warp barrier kernels) straight into the contiguous buffer the GEMM reads (``:203-209``, ``:236-249``).
 * ``FusedMPTrainer``   row-parallel GEMM -> all-reduce of the partial activations inside the kernel
-  (``:302-303``, ``:308-309``), or (``mp_mode="sp"``) -> reduce-scatter over token shards + native all-gather.
+  (``:302-303``, ``:308-309``), or (``mp_mode="sp"``) -> reduce-scatter over token shards + native all-gather, or
+  (``mp_mode="spf"``, not yet run on hardware) the all-gather fused into the column-parallel GEMM as well.
 """
 from __future__ import annotations
 
@@ -65,6 +66,34 @@ class FusedChannel:
 def _owned_cap(shapes, world: int, owner_mode: int) -> int:
     lib = nv.load()
     return max(int(lib.b200_fused_owned_tiles(M, N, world, owner_mode)) for M, N in shapes)
+
+
+class GatherChannel:
+    """Flags + call counter for one stream of all-gather -> GEMM calls (``csrc/gather_gemm.cu``).
+
+    NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent)."""
+
+    def __init__(self, sw: SymmWorld, max_rows: int):
+        lib = nv.load()
+        self.sw = sw
+        self.started = sw.alloc(256)                                       # symmetric, zero-initialised
+        self.ready = torch.zeros(int(lib.b200_gather_gemm_ready_bytes(max_rows)) // 4, dtype=torch.int32, device=sw.device)
+        self.max_rows = max_rows
+        self.seq = 0
+
+    def gemm(self, a_peers, B: torch.Tensor, b_major: int, out: torch.Tensor, M: int, N: int, K: int, epilogue: int,
+             aux: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None, max_ctas: int = 0) -> torch.Tensor:
+        """``out = epilogue(A_full @ B^T)``; ``a_peers[q]`` = rank q's ``[M, K]`` buffer holding its token shard."""
+        assert M <= self.max_rows and B.dtype == torch.bfloat16 and B.stride(-1) == 1 and out.stride(-1) == 1
+        self.seq += 1
+        sw = self.sw
+        rc = nv.load().b200_gather_gemm_bf16(
+            a_peers, B.data_ptr(), B.stride(0), b_major, out.data_ptr(), out.stride(0), M, N, K, epilogue,
+            nv._ptr(aux), aux.stride(0) if aux is not None else 0, nv._ptr(out2), out2.stride(0) if out2 is not None else 0,
+            None, 1.0, self.started.peers_c, self.ready.data_ptr(), sw.rank, sw.world, self.seq, int(max_ctas), nv._stream())
+        nv._check(rc, "b200_gather_gemm_bf16")
+        nv.launch_count += 1
+        return out
 
 
 # =================================================================================================== DDP
@@ -253,8 +282,11 @@ class FusedMPTrainer:
         if cfg.residual:
             raise RuntimeError("fused MP has no residual path; use --comm nccl")
         self.sp = cfg.mp_mode == "sp"
+        self.spf = cfg.mp_mode == "spf"
         if self.sp:
             self.comm_name = "fused: row-parallel GEMM + reduce-scatter in one kernel; native all-gather of the token shards"
+        if self.spf:
+            self.comm_name = "fused: all-gather + column-parallel GEMM in one kernel; row-parallel GEMM + reduce-scatter in one kernel"
         self.lr = cfg.lr * cfg.grad_scale
         self.sw = get_symm_world(comm, device)
         self.world, self.rank = comm.world, comm.rank
@@ -267,7 +299,27 @@ class FusedMPTrainer:
         if self.T == T:
             return
         D, n = self.cfg.model_size, self.world
-        if self.sp:
+        if self.spf:
+            if T % (TILE_M * n) or D % 64:
+                raise ValueError(f"mp_mode=spf needs tokens ({T}) divisible by 128 * world ({TILE_M * n}) and model_size ({D}) by 64")
+            # Activations live in FULL-size symmetric buffers; a rank's own token rows are written by the reduce-scatter
+            # kernel, the other rows by the next all-gather+GEMM kernel, in place.
+            self.abuf = self.sw.alloc((self.L + 3) * T * D * 2 + 16384)
+            self.X, self.X_off = [], []
+            for _ in range(self.L + 1):
+                t, o = self.abuf.carve((T, D), torch.bfloat16)
+                self.X.append(t)
+                self.X_off.append(o)
+            self.DX, self.DX_off = [], []
+            for _ in range(2):
+                t, o = self.abuf.carve((T, D), torch.bfloat16)
+                self.DX.append(t)
+                self.DX_off.append(o)
+            self.local_tab = lambda t: (C.c_void_p * n)(*[t.data_ptr() if r == self.rank else 0 for r in range(n)])
+            self.chan = FusedChannel(self.sw, _owned_cap([(T, D)], n, OWN_ROW_SHARDED), _tiles(T, D))
+            self.gchan = GatherChannel(self.sw, T)
+            self.coll = CollChannel(self.sw)
+        elif self.sp:
             if T % (TILE_M * n):
                 raise ValueError(f"sequence-parallel fused MP needs tokens ({T}) divisible by 128 * world ({TILE_M * n})")
             Ts = T // n
@@ -380,8 +432,64 @@ class FusedMPTrainer:
             saved[i] = None
         return self._gather_tokens(self.ys_off[self.L - 1], T, D)
 
+    # ---- sequence-parallel form, gathers fused into the column-parallel GEMMs ------------------------------------
+    def _step_spf(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+        """Per layer: [all-gather x -> x W1^T -> act] one kernel, [a W2^T -> reduce-scatter] one kernel; backward
+        [all-gather dy -> dy W2 -> act'] one kernel, dW2/dW1 GEMM+SGD local, [dh W1 -> reduce-scatter] one kernel.
+        Buffer-reuse argument: docs/KERNELS.md 2.5.  NOT YET RUN ON HARDWARE."""
+        ops, n, r = self.ops, self.world, self.rank
+        T, D = x.shape
+        Ts = T // n
+        Fs = self.shards[0][0].shape[0]
+        own = slice(r * Ts, (r + 1) * Ts)
+        act = self.opts.activation
+        use_mask = act == "relu" and Fs % 128 == 0
+        self.X[0][own].copy_(x[own])
+        saved = []
+        for l, (W1, W2) in enumerate(self.shards):
+            a = torch.empty(T, Fs, dtype=torch.bfloat16, device=self.device)
+            if use_mask:
+                aux = torch.empty(T, Fs // 8, dtype=torch.uint8, device=self.device)
+                self.gchan.gemm(self.abuf.peers_at(self.X_off[l]), W1, nv.MAJOR_K, a, T, Fs, D, nv.EPI_RELU_MASK, out2=aux)
+            elif act == "relu":
+                self.gchan.gemm(self.abuf.peers_at(self.X_off[l]), W1, nv.MAJOR_K, a, T, Fs, D, nv.EPI_RELU)
+                aux = a
+            else:
+                aux = torch.empty_like(a)
+                self.gchan.gemm(self.abuf.peers_at(self.X_off[l]), W1, nv.MAJOR_K, a, T, Fs, D, nv.EPI_GELU, out2=aux)
+            # row-parallel GEMM -> reduce-scatter: my token rows of the next layer's input, in place
+            self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.local_tab(self.X[l + 1][own]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
+            saved.append(None if self.opts.recompute else (a, aux))
+        cur = 0
+        self.DX[cur][own].copy_(dloss_dx[own])
+        for i in reversed(range(self.L)):
+            W1, W2 = self.shards[i]
+            if saved[i] is None:                                          # X[i] is complete since the forward pass
+                a, pre = ops.linear_act(self.X[i], W1, act)
+                aux = (pre if pre is not None else a) if act == "relu" else pre
+            else:
+                a, aux = saved[i]
+            dh = torch.empty(T, Fs, dtype=torch.bfloat16, device=self.device)
+            epi = (nv.EPI_RELU_BWD_MASK if aux.dtype == torch.uint8 else nv.EPI_RELU_BWD) if act == "relu" else nv.EPI_GELU_BWD
+            self.gchan.gemm(self.abuf.peers_at(self.DX_off[cur]), W2, nv.MAJOR_MN, dh, T, Fs, D, epi, aux=aux)
+            ops.grad_weight_sgd_(W2, self.DX[cur], a, self.lr)            # DX[cur] is the full upstream gradient now
+            if i > 0:
+                self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.local_tab(self.DX[1 - cur][own]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
+            ops.grad_weight_sgd_(W1, dh, self.X[i], self.lr)
+            saved[i] = None
+            cur = 1 - cur
+        # the stack output, gathered in place by the barrier-ed native all-gather: its opening barrier is also what
+        # lets the next step overwrite X[0] / DX[0] (every rank has finished every kernel that read them)
+        e = self.coll.next_epoch()
+        nv._check(nv.load().b200_all_gather(self.abuf.peers_c, self.X_off[self.L], T * D * 2, self.coll.flags.peers_c, r, n, e, 0, nv._stream()),
+                  "b200_all_gather")
+        nv.launch_count += 1
+        return self.X[self.L].clone()                                     # the buffer is rewritten by the next step
+
     def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         self._ensure_buffers(x.shape[0])
+        if self.spf:
+            return self._step_spf(x, dloss_dx)
         return self._step_sp(x, dloss_dx) if self.sp else self._step_ar(x, dloss_dx)
 
     def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor]]) -> None:

@@ -168,6 +168,28 @@ int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const vo
                              int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
                              float alpha, int max_ctas, void* stream);
 
+/* ---- all-gather -> GEMM in one kernel (csrc/gather_gemm.cu) -------------------------------------------------------
+ * C[M,N] = epilogue(A_full[M,K] * B^T) where A is token-sharded: a_peers[q] is rank q's [M,K] bf16 buffer (K-major,
+ * contiguous, 128-byte aligned, same symmetric offset everywhere) in which only rows [q*M/world, (q+1)*M/world) are
+ * final when q's call starts.  The kernel pulls the other shards into a_peers[rank] (complete when it returns) while
+ * the MMAs start on the local rows.  M % (128*world) == 0, K % 64 == 0.  B / epilogue / aux / out2 / bias / alpha as
+ * b200_gemm_bf16 (epilogues STORE, RELU, GELU, RELU_BWD, GELU_BWD, RELU_MASK, RELU_BWD_MASK).
+ * `started_peers[q]`: symmetric array of >= `world` uint32 reserved for this stream of calls, zero-initialised;
+ * `seq` starts at 1 and increases by one per call (same on every rank).  `ready`: LOCAL scratch of
+ * b200_gather_gemm_ready_bytes(M) bytes, cleared by the call itself (stream-ordered).
+ * The kernel never waits for peers to finish reading a shard: the caller must not overwrite its shard before a later
+ * collective that every rank enters after this call (docs/KERNELS.md 2.5).
+ * No counterpart in the reference (it all-reduces, train_ffns.py:303,:309); this is the sequence-parallel form
+ * SURVEY.md 2.6 plans for C4/C5.  NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent). */
+long long b200_gather_gemm_ready_bytes(int M);
+int b200_gather_gemm_bf16(void* const* a_peers, const void* B, long long ldb, int b_major, void* C, long long ldc,
+                          int M, int N, int K, int epilogue, const void* aux, long long ldaux, void* out2, long long ldc2,
+                          const float* bias, float alpha, void* const* started_peers, void* ready, int rank, int world,
+                          unsigned int seq, int max_ctas, void* stream);
+/* host mirror of the pull order (CPU tests): out = {peer, first 16-byte vector, 128-row block, vectors per chunk,
+ * chunks per block, total chunks} for pull chunk `u` */
+int b200_debug_gather_chunk(int M, int K, int rank, int world, long long u, long long* out);
+
 /* ---- EXPERIMENTAL: cuMem VMM blocks + NVLS multicast (csrc/vmm.cu) -----------------------------------------------
  * The runtime the in-switch reductions need; not used by the default training paths.  Host-side fd
  * passing is unit-tested on CPU; the device side has GPU tests queued (tests/test_multigpu.py::test_vmm_*).

@@ -59,3 +59,57 @@ def test_argument_validation_without_a_gpu(lib):
                             None, C.c_longlong(0), None, C.c_float(1.0), 0, None)
     assert rc == -1 and b"null" in lib.b200_last_error()
     assert lib.b200_sumsq_bf16_static(None, None, C.c_longlong(0), None) == -1
+
+
+@pytest.mark.parametrize("M,K", [(1024, 64), (2048, 512), (16384, 8192), (4096, 192)])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_gather_gemm_pull_order_covers_every_remote_vector_once(lib, M, K, world):
+    """csrc/gather_gemm.cu: the side warps' chunk list covers each remote 16-byte vector exactly once, in ring order
+    starting at the next rank, and every 128-row block receives exactly `chunks_per_block` chunks (the count the TMA
+    producer waits for)."""
+    lib.b200_debug_gather_chunk.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_longlong, C.POINTER(C.c_longlong)]
+    out = (C.c_longlong * 6)()
+    for rank in range(world):
+        assert lib.b200_debug_gather_chunk(M, K, rank, world, -1, out) == 0
+        chunk_vecs, cpb, total = out[3], out[4], out[5]
+        shard_vecs = (M // world) * K * 2 // 16
+        assert chunk_vecs * 16 in (16384, 32768) and cpb * chunk_vecs * 16 == 128 * K * 2
+        assert total == (shard_vecs // chunk_vecs) * (world - 1)
+        per_block = {}
+        covered = []
+        last_dist = 1
+        for u in range(total):
+            lib.b200_debug_gather_chunk(M, K, rank, world, u, out)
+            peer, first, block = out[0], out[1], out[2]
+            assert peer != rank
+            dist = (peer - rank) % world
+            assert dist >= last_dist, "ring order: nearer successors first"
+            last_dist = dist
+            assert peer * shard_vecs <= first and first + chunk_vecs <= (peer + 1) * shard_vecs
+            assert block == first * 16 // (128 * K * 2), "the chunk lies inside the block it is counted for"
+            assert (first + chunk_vecs - 1) * 16 // (128 * K * 2) == block
+            per_block[block] = per_block.get(block, 0) + 1
+            covered.append(first)
+        assert len(set(covered)) == total
+        blocks = M // 128
+        own = set(range(rank * blocks // world, (rank + 1) * blocks // world))
+        assert set(per_block) == set(range(blocks)) - own
+        assert all(v == cpb for v in per_block.values())
+
+
+def test_gather_gemm_argument_validation_without_a_gpu(lib):
+    lib.b200_last_error.restype = C.c_char_p
+    pp = C.POINTER(C.c_void_p)
+    vp, ll, i, f, u = C.c_void_p, C.c_longlong, C.c_int, C.c_float, C.c_uint
+    lib.b200_gather_gemm_bf16.argtypes = [pp, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp]
+    two = (C.c_void_p * 2)(0x1000, 0x2000)
+    args = dict(M=1024, N=256, K=64, seq=1, world=2, rank=0)
+
+    def call(**kw):
+        a = dict(args, **kw)
+        return lib.b200_gather_gemm_bf16(two, 0x3000, 64, 0, 0x4000, a["N"], a["M"], a["N"], a["K"], 0, None, 0, None, 0, None, 1.0,
+                                         two, 0x5000, a["rank"], a["world"], a["seq"], 0, None)
+    assert call(M=1000) == -1 and b"128 * world" in lib.b200_last_error()
+    assert call(K=72) == -1 and b"multiple of 64" in lib.b200_last_error()
+    assert call(seq=0) == -1 and b"seq" in lib.b200_last_error()
+    assert call(rank=2) == -1

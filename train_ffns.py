@@ -47,7 +47,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--impl', default='auto', choices=['auto', 'native', 'torch'])
     p.add_argument('--comm', default='auto', choices=['auto', 'fused', 'native', 'nccl'])
     p.add_argument('--recompute', action='store_true')
-    p.add_argument('--mp_mode', default='ar', choices=['ar', 'sp'])
+    p.add_argument('--mp_mode', default='ar', choices=['ar', 'sp', 'spf'])
     p.add_argument('--master_port', type=int, default=29500)
     p.add_argument('--save_path', default=None)
     p.add_argument('--load_path', default=None)
