@@ -87,7 +87,10 @@ __device__ __forceinline__ uint4 pack_row8(const uint32_t* a) {
     return v;
 }
 
-template <int SIDE_WARPS>
+// POLL = 0: side warps re-scan their owned tiles every 200 ns while nothing is ready (the validated default).
+// POLL = 1: exponential back-off 256 ns -> 4 us while nothing is ready, reset on progress (B200_FUSED_POLL=1; written
+//           after round 1's GPU budget was spent to cut the polling instructions ncu shows - not yet run on hardware).
+template <int SIDE_WARPS, int POLL = 0>
 struct FusedEpiT {
     using Params = FusedParams;
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
@@ -173,6 +176,7 @@ struct FusedEpiT {
         unsigned long long done = 0ull;
         int remaining = n_mine;
         long long t0 = clock64();
+        [[maybe_unused]] unsigned int backoff = 256;
         while (remaining > 0) {
             bool progressed = false;
             for (int j = 0; j < n_mine; ++j) {
@@ -198,10 +202,16 @@ struct FusedEpiT {
                 }
             }
             if (!progressed) {
-                __nanosleep(200);
+                if constexpr (POLL == 0) {
+                    __nanosleep(200);
+                } else {
+                    __nanosleep(backoff);
+                    backoff = backoff < 4096 ? backoff * 2 : 4096;
+                }
                 if ((clock64() - t0) > B200_FLAG_TIMEOUT_CYCLES) device_fail(g.err, ERR_FLAG_TIMEOUT, 0x680);
             } else {
                 t0 = clock64();
+                if constexpr (POLL != 0) backoff = 256;
             }
         }
     }
@@ -380,6 +390,12 @@ extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_majo
         overlap = link_ms > 0.6 * mma_ms;
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    static int poll = -1;                       // B200_FUSED_POLL=1: exponential back-off in the side warps (unvalidated)
+    if (poll < 0) {
+        const char* e = getenv("B200_FUSED_POLL");
+        poll = (e != nullptr && e[0] == '1') ? 1 : 0;
+    }
+    if (poll == 1 && side == 4) return launch_gemm<FusedEpiT<4, 1>>(o, p, max_ctas, st, rot, world, overlap);
     if (side == 2) return launch_gemm<FusedEpiT<2>>(o, p, max_ctas, st, rot, world, overlap);
     return launch_gemm<FusedEpiT<4>>(o, p, max_ctas, st, rot, world, overlap);
 }
