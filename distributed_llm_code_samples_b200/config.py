@@ -58,6 +58,7 @@ class TrainConfig:
     save_every: int = 0
     profile: bool = False
     data: str = "cpu"                      # cpu = reference mock_data semantics; device = on-device Philox
+    cuda_graph: bool = False               # replay the whole step from a CUDA graph (1 GPU, SGD; utils/graph.py)
     extra: dict = field(default_factory=dict)
 
     def __post_init__(self) -> None:

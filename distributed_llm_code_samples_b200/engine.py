@@ -57,9 +57,16 @@ class Engine:
         del layers_params
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self._graphs: dict = {}
 
     # ---- device-side step ---------------------------------------------------------------------------------
     def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+        if self.cfg.cuda_graph and x.is_cuda:
+            g = self._graphs.get((tuple(x.shape), x.dtype))
+            if g is None:                      # first step of this shape: warm up, capture (weights are put back)
+                from .utils.graph import GraphedStep
+                g = self._graphs[(tuple(x.shape), x.dtype)] = GraphedStep(self.trainer, x, dloss_dx)
+            return g.step(x, dloss_dx)
         return self.trainer.step(x, dloss_dx)
 
     @property

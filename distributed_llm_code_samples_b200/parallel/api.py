@@ -125,17 +125,30 @@ def _rank_main(rank: int, world: int, device: torch.device, method: str, cfg_dic
     else:
         batches = mock_data(my_seeds, tokens, model_size, cfg.torch_dtype, device)
     seeds_per_step = world if method in ("ddp", "fsdp") else 1
+    step = trainer.step
+    if cfg.cuda_graph and world == 1 and device.type == "cuda":
+        from ..utils.graph import GraphedStep
+        graphs: dict = {}
+
+        def step(x, dy):                                             # noqa: F811 - graph replay of the same step
+            g = graphs.get(tuple(x.shape))
+            if g is None:
+                g = graphs[tuple(x.shape)] = GraphedStep(trainer, x, dy)
+            return g.step(x, dy)
     with profile_if(cfg.profile, rank):
         with DeviceTimer(device) as t:
             if cfg.save_every and cfg.save_path:
                 for k, (x, dy) in enumerate(batches):
-                    trainer.step(x, dy)
+                    step(x, dy)
                     if (k + 1) % cfg.save_every == 0:                # periodic checkpoint: full, unsharded layout
                         full = trainer.full_params()                 # collective on every rank
                         if rank == 0:
                             from ..utils.checkpoint import save_checkpoint
                             save_checkpoint(f"{cfg.save_path}.step{(k + 1) * seeds_per_step}", full, step=(k + 1) * seeds_per_step,
                                             args=cfg.to_dict(), seeds=seeds)
+            elif step is not trainer.step:
+                for x, dy in batches:
+                    step(x, dy)
             else:
                 trainer.run(batches)
     ms = max_over_ranks(t.ms, comm, device)

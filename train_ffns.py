@@ -7,7 +7,7 @@ Same command line as the reference (``train_ffns.py:343-351``):
 
 ``M``: 0 = all methods, 1 = one GPU, 2 = DDP, 3 = FSDP, 4 = MP/TP (``:5-6``).  Extra flags select what the
 reference hard-codes: ``--ffn_dim --dtype --activation --residual --bias --optimizer --lr --world_size --backend
---device --impl --comm --recompute --mp_mode --save_path --load_path --profile --data``.
+--device --impl --comm --recompute --mp_mode --save_path --load_path --profile --cuda_graph --data``.
 """
 from __future__ import annotations
 
@@ -53,6 +53,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--load_path', default=None)
     p.add_argument('--save_every', type=int, default=0, help='also checkpoint every N optimizer steps (needs --save_path)')
     p.add_argument('--profile', action='store_true')
+    p.add_argument('--cuda_graph', action='store_true', help='replay each step from a CUDA graph (1 GPU, SGD)')
     p.add_argument('--data', default='cpu', choices=['cpu', 'device'])
     return p
 
