@@ -18,6 +18,7 @@ import torch
 from torch import nn
 
 from ..config import INIT_SCALE
+from ..utils.profiler import block_range
 
 Params = List[torch.Tensor]            # [W1, W2] or [W1, W2, b1, b2]
 LayerGrads = Tuple[torch.Tensor, ...]
@@ -123,8 +124,9 @@ def _bias(p: Params, j: int) -> Optional[torch.Tensor]:
 
 def tlayer_ffn_fwd(ops, p: Params, x: torch.Tensor, opts: BlockOpts = BlockOpts()) -> Tuple[torch.Tensor, Saved]:
     """``y = act(x W1^T + b1) W2^T + b2 (+ x)`` (``train_ffns.py:54-58``)."""
-    a, pre = ops.linear_act(x, p[0], opts.activation, _bias(p, 0))
-    y = ops.linear(a, p[1], _bias(p, 1), residual=x if opts.residual else None)
+    with block_range("ffn_fwd"):
+        a, pre = ops.linear_act(x, p[0], opts.activation, _bias(p, 0))
+        y = ops.linear(a, p[1], _bias(p, 1), residual=x if opts.residual else None)
     return y, (Saved(x) if opts.recompute else Saved(x, a, pre))
 
 
@@ -138,6 +140,11 @@ def tlayer_ffn_bkwd(ops, dy: torch.Tensor, p: Params, saved: Saved, opts: BlockO
     one kernel, no gradient tensor) - the returned grads are then ``None``.  ``need_dx=False`` skips the
     layer-0 input gradient the reference computes and discards (``:88``).
     """
+    with block_range("ffn_bwd"):
+        return _tlayer_ffn_bkwd(ops, dy, p, saved, opts, need_dx, update_lr)
+
+
+def _tlayer_ffn_bkwd(ops, dy, p, saved, opts, need_dx, update_lr):
     x = saved.x
     a, pre = saved.a, saved.pre
     if a is None:                                   # recompute policy (:63, :66)

@@ -18,7 +18,7 @@ from ..config import TrainConfig
 from ..models.ffn import Params
 from ..ops import get_ops
 from ..utils.data import device_mock_data, mock_data, split_seeds
-from ..utils.profiler import profile_if
+from ..utils.profiler import enable_ranges, profile_if
 from ..utils.timing import DeviceTimer, max_over_ranks, tokens_per_second
 from .base import fsdp_shard, place, tp_shard, tp_shard_dim
 from .comm import LocalComm, make_comm
@@ -135,6 +135,8 @@ def _rank_main(rank: int, world: int, device: torch.device, method: str, cfg_dic
             if g is None:
                 g = graphs[tuple(x.shape)] = GraphedStep(trainer, x, dy)
             return g.step(x, dy)
+    if cfg.profile:
+        enable_ranges(True)                                          # per-block NVTX ranges in the model loops
     with profile_if(cfg.profile, rank):
         with DeviceTimer(device) as t:
             if cfg.save_every and cfg.save_path:

@@ -5,6 +5,7 @@ from __future__ import annotations
 
 import contextlib
 import functools
+import os
 
 import torch
 
@@ -50,3 +51,19 @@ def nvtx(name: str):
             torch.cuda.nvtx.range_pop()
     else:
         yield
+
+
+# Per-block ranges inside the model loops (``ffn_fwd`` / ``ffn_bwd``): off by default - one shared null context, no
+# per-call allocation - and switched on by ``--profile`` or ``B200_NVTX=1`` so timeline captures show the block
+# structure above the kernel names.
+_NULL = contextlib.nullcontext()
+_ranges_on = os.environ.get("B200_NVTX") == "1"
+
+
+def enable_ranges(on: bool = True) -> None:
+    global _ranges_on
+    _ranges_on = bool(on)
+
+
+def block_range(name: str):
+    return nvtx(name) if _ranges_on else _NULL
