@@ -2,7 +2,6 @@
 The module imports fine with 0 GPUs (its ``nGPUs == 1`` guard does not trip, train_ffns.py:25-27)."""
 import importlib.util
 import os
-import sys
 
 CANDIDATES = ["/root/reference/train_ffns.py",
               os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref", "train_ffns.py")]
