@@ -433,63 +433,53 @@ class FusedMPTrainer:
         return self._gather_tokens(self.ys_off[self.L - 1], T, D)
 
     # ---- sequence-parallel form, gathers fused into the column-parallel GEMMs ------------------------------------
-    def _step_spf(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
-        """Per layer: [all-gather x -> x W1^T -> act] one kernel, [a W2^T -> reduce-scatter] one kernel; backward
-        [all-gather dy -> dy W2 -> act'] one kernel, dW2/dW1 GEMM+SGD local, [dh W1 -> reduce-scatter] one kernel.
-        Buffer-reuse argument: docs/KERNELS.md 2.5.  NOT YET RUN ON HARDWARE."""
-        ops, n, r = self.ops, self.world, self.rank
-        T, D = x.shape
-        Ts = T // n
-        Fs = self.shards[0][0].shape[0]
-        own = slice(r * Ts, (r + 1) * Ts)
-        act = self.opts.activation
-        use_mask = act == "relu" and Fs % 128 == 0
-        self.X[0][own].copy_(x[own])
-        saved = []
-        for l, (W1, W2) in enumerate(self.shards):
-            a = torch.empty(T, Fs, dtype=torch.bfloat16, device=self.device)
-            if use_mask:
-                aux = torch.empty(T, Fs // 8, dtype=torch.uint8, device=self.device)
-                self.gchan.gemm(self.abuf.peers_at(self.X_off[l]), W1, nv.MAJOR_K, a, T, Fs, D, nv.EPI_RELU_MASK, out2=aux)
-            elif act == "relu":
-                self.gchan.gemm(self.abuf.peers_at(self.X_off[l]), W1, nv.MAJOR_K, a, T, Fs, D, nv.EPI_RELU)
-                aux = a
-            else:
-                aux = torch.empty_like(a)
-                self.gchan.gemm(self.abuf.peers_at(self.X_off[l]), W1, nv.MAJOR_K, a, T, Fs, D, nv.EPI_GELU, out2=aux)
-            # row-parallel GEMM -> reduce-scatter: my token rows of the next layer's input, in place
-            self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.local_tab(self.X[l + 1][own]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
-            saved.append(None if self.opts.recompute else (a, aux))
-        cur = 0
-        self.DX[cur][own].copy_(dloss_dx[own])
-        for i in reversed(range(self.L)):
-            W1, W2 = self.shards[i]
-            if saved[i] is None:                                          # X[i] is complete since the forward pass
-                a, pre = ops.linear_act(self.X[i], W1, act)
-                aux = (pre if pre is not None else a) if act == "relu" else pre
-            else:
-                a, aux = saved[i]
-            dh = torch.empty(T, Fs, dtype=torch.bfloat16, device=self.device)
-            epi = (nv.EPI_RELU_BWD_MASK if aux.dtype == torch.uint8 else nv.EPI_RELU_BWD) if act == "relu" else nv.EPI_GELU_BWD
-            self.gchan.gemm(self.abuf.peers_at(self.DX_off[cur]), W2, nv.MAJOR_MN, dh, T, Fs, D, epi, aux=aux)
-            ops.grad_weight_sgd_(W2, self.DX[cur], a, self.lr)            # DX[cur] is the full upstream gradient now
-            if i > 0:
-                self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.local_tab(self.DX[1 - cur][own]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
-            ops.grad_weight_sgd_(W1, dh, self.X[i], self.lr)
-            saved[i] = None
-            cur = 1 - cur
-        # the stack output, gathered in place by the barrier-ed native all-gather: its opening barrier is also what
-        # lets the next step overwrite X[0] / DX[0] (every rank has finished every kernel that read them)
+    # The schedule itself is `spf_step` (below the class); these are its three primitives on the native kernels.
+    def ag_gemm(self, buf: torch.Tensor, W: torch.Tensor, b_major: int, kind: str, aux: Optional[torch.Tensor] = None):
+        """``out = epilogue(all_gather(buf) @ W^T)`` in one kernel; ``buf`` (a full-size symmetric ``[T, D]`` buffer whose
+        own token rows are final) is complete on return.  Returns ``(out, saved_for_backward)``."""
+        T, D = buf.shape
+        N = W.shape[0] if b_major == nv.MAJOR_K else W.shape[1]
+        out = torch.empty(T, N, dtype=torch.bfloat16, device=self.device)
+        peers = self.abuf.peers_at(self.abuf.offset_of(buf))
+        if kind == "relu" and N % 128 == 0:
+            mask = torch.empty(T, N // 8, dtype=torch.uint8, device=self.device)
+            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_RELU_MASK, out2=mask)
+            return out, mask
+        if kind == "relu":
+            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_RELU)
+            return out, out
+        if kind == "gelu":
+            pre = torch.empty_like(out)
+            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_GELU, out2=pre)
+            return out, pre
+        if kind == "relu_bwd":
+            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_RELU_BWD_MASK if aux.dtype == torch.uint8 else nv.EPI_RELU_BWD, aux=aux)
+            return out, None
+        if kind == "gelu_bwd":
+            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_GELU_BWD, aux=aux)
+            return out, None
+        raise ValueError(kind)
+
+    def rs_gemm(self, A: torch.Tensor, W: torch.Tensor, b_major: int, dst: torch.Tensor) -> None:
+        """``dst[own token rows] = sum over ranks of A @ W^T`` - row-parallel GEMM + reduce-scatter in one kernel."""
+        T, D = dst.shape
+        Ts = T // self.world
+        own = dst[self.rank * Ts:(self.rank + 1) * Ts]
+        self.chan.gemm(A, nv.MAJOR_K, W, b_major, T, D, A.shape[1], self.local_tab(own), D, self.rank * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
+
+    def gather_out(self, buf: torch.Tensor) -> torch.Tensor:
+        """In-place all-gather of the token shards by the barrier-ed native kernel.  Its opening barrier is also what lets
+        the next step overwrite X[0] / DX[0]: every rank has finished every kernel that read them."""
         e = self.coll.next_epoch()
-        nv._check(nv.load().b200_all_gather(self.abuf.peers_c, self.X_off[self.L], T * D * 2, self.coll.flags.peers_c, r, n, e, 0, nv._stream()),
-                  "b200_all_gather")
+        nv._check(nv.load().b200_all_gather(self.abuf.peers_c, self.abuf.offset_of(buf), buf.numel() * 2, self.coll.flags.peers_c,
+                                            self.rank, self.world, e, 0, nv._stream()), "b200_all_gather")
         nv.launch_count += 1
-        return self.X[self.L].clone()                                     # the buffer is rewritten by the next step
+        return buf.clone()                                                # the buffer is rewritten by the next step
 
     def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         self._ensure_buffers(x.shape[0])
         if self.spf:
-            return self._step_spf(x, dloss_dx)
+            return spf_step(self, x, dloss_dx)
         return self._step_sp(x, dloss_dx) if self.sp else self._step_ar(x, dloss_dx)
 
     def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor]]) -> None:
@@ -499,3 +489,46 @@ class FusedMPTrainer:
     def full_params(self) -> List[Params]:
         from .mp import MPTrainer
         return MPTrainer.full_params(self)      # same reassembly rule (W1 dim 0, W2 dim 1)
+
+
+def spf_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+    """One ``mp_mode="spf"`` optimizer step, written against three primitives so that the schedule (which buffer, whose
+    rows, which operand layout) is testable on CPU with gloo stand-ins (``tests/test_spf_schedule_cpu.py``):
+
+    * ``t.ag_gemm(buf, W, b_major, kind, aux)``  all-gather ``buf``'s token shards, then ``epilogue(buf @ W^T)``
+    * ``t.rs_gemm(A, W, b_major, dst)``          ``dst[own rows] = sum_ranks A @ W^T``
+    * ``t.gather_out(buf)``                      all-gather the final output
+
+    ``t`` also provides ``shards, L, rank, world, ops, opts, lr`` and the full-size activation buffers ``X[0..L]``,
+    ``DX[0..1]``.  Per layer, forward: [all-gather x -> x W1^T -> act] one kernel, [a W2^T -> reduce-scatter] one
+    kernel; backward: [all-gather dy -> dy W2 -> act'] one kernel, dW2 / dW1 GEMM+SGD local, [dh W1 -> reduce-scatter]
+    one kernel.  Same math as the reference's TP loop (``train_ffns.py:296-312``) with AR split into RS + AG.
+    Buffer-reuse argument: docs/KERNELS.md 2.5."""
+    n, r = t.world, t.rank
+    T = x.shape[0]
+    Ts = T // n
+    own = slice(r * Ts, (r + 1) * Ts)
+    act = t.opts.activation
+    t.X[0][own].copy_(x[own])
+    saved = []
+    for l, (W1, W2) in enumerate(t.shards):
+        a, aux = t.ag_gemm(t.X[l], W1, nv.MAJOR_K, act)                   # completes X[l] as a side effect
+        t.rs_gemm(a, W2, nv.MAJOR_K, t.X[l + 1])                          # my token rows of the next layer's input
+        saved.append(None if t.opts.recompute else (a, aux))
+    cur = 0
+    t.DX[cur][own].copy_(dloss_dx[own])
+    for i in reversed(range(t.L)):
+        W1, W2 = t.shards[i]
+        if saved[i] is None:                                              # X[i] is complete since the forward pass
+            a, pre = t.ops.linear_act(t.X[i], W1, act)
+            aux = (pre if pre is not None else a) if act == "relu" else pre
+        else:
+            a, aux = saved[i]
+        dh, _ = t.ag_gemm(t.DX[cur], W2, nv.MAJOR_MN, act + "_bwd", aux)  # completes DX[cur] = the full upstream gradient
+        t.ops.grad_weight_sgd_(W2, t.DX[cur], a, t.lr)
+        if i > 0:
+            t.rs_gemm(dh, W1, nv.MAJOR_MN, t.DX[1 - cur])
+        t.ops.grad_weight_sgd_(W1, dh, t.X[i], t.lr)
+        saved[i] = None
+        cur = 1 - cur
+    return t.gather_out(t.X[t.L])

@@ -59,7 +59,7 @@ def test_ddp_equals_fsdp_equals_oracle():
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("mp_mode", ["ar", "sp"])
+@pytest.mark.parametrize("mp_mode", ["ar", "sp", "spf"])
 def test_mp_equals_single(mp_mode):
     lp, seeds = _init()
     single = api.train_1gpu(lp, seeds, T, D, _cfg())
