@@ -41,6 +41,8 @@ def parse_args():
     ap.add_argument("--comm", default="auto", choices=["auto", "fused", "native", "nccl"])
     ap.add_argument("--ops", default="native", choices=["native", "torch"])
     ap.add_argument("--recompute", action="store_true", help="reference-style activation recompute in backward")
+    ap.add_argument("--mp_mode", default="ar", choices=["ar", "sp", "spf"],
+                    help="MP form: ar = the reference's all-reduce form (default, the benchmarked one); sp / spf = sequence-parallel variants")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--pool", type=int, default=3, help="distinct synthetic batches cycled through")
     return ap.parse_args()
@@ -114,7 +116,7 @@ def run_ours(args):
     method = args.method if world > 1 or args.method == "single" else args.method
     cfg = TrainConfig(num_steps=args.steps, batch_size=args.batch_size, seq_len=args.seq_len, layers=l, model_size=d,
                       ffn_dim=f, dtype="bf16", device="cuda", backend="nccl", impl=args.ops, comm=args.comm,
-                      recompute=args.recompute)
+                      recompute=args.recompute, mp_mode=args.mp_mode)
     from distributed_llm_code_samples_b200.engine import init_params_on_device
     _, _, local0 = rank_world()
     torch.cuda.set_device(local0)

@@ -1,0 +1,42 @@
+#!/bin/bash
+# First GPU call of the next round: run everything that was written while no GPU was available, cheapest and safest first.
+#   gpurun --gpus 2 --timeout 1500 -- 'bash tools/run_queued_validation.sh 2'
+# Every step has its own timeout (a hang must not take the box down) and logs under gpurun_out/queued/.
+N=${1:-2}
+O=gpurun_out/queued
+mkdir -p $O
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
+export B200_QUEUED_TESTS=1
+step() { echo "== $1"; shift; timeout "$@"; echo "rc=$?"; }
+
+# 1. single GPU: CUDA-graph replay (bitwise vs eager), then the whole 1-GPU suite with the queued tests on
+step "graph replay test" 300 python -m pytest tests/test_train_gpu.py -q -m gpu -k cuda_graph > $O/graph.log 2>&1; tail -3 $O/graph.log
+step "1-GPU suite (queued on)" 900 python -m pytest tests -q -m gpu --deselect tests/test_multigpu.py > $O/suite_1gpu.log 2>&1; tail -3 $O/suite_1gpu.log
+
+# 2. multi GPU, one queued test per process so that a hang / trap is attributed
+for k in barrier_and_flag_protocol_stress unfused_trainers_on_native_collectives vmm_multicast_all_reduce "fused_trainer_matches_nccl_trainer and mp_spf"; do
+  tag=$(echo "$k" | tr ' ' '_')
+  step "multigpu: $k" 400 python -m pytest tests/test_multigpu.py -q -m gpu -k "$k" > $O/mgpu_$tag.log 2>&1; tail -4 $O/mgpu_$tag.log
+done
+
+# 3. MP forms, same config: ar (validated) vs sp (validated) vs spf (new); then the poll back-off on DDP
+for mode in ar sp spf; do
+  step "bench mp $mode" 500 $TR --master-port 29521 bench.py --method mp --mp_mode $mode --gpus $N --steps 4 --warmup 3 --no-e2e 2> $O/bench_mp_$mode.err | grep "^{" > $O/bench_mp_$mode.json
+  python -c "
+import json
+try:
+    d=json.load(open('$O/bench_mp_$mode.json')); print('mp $mode', round(d['value']), 'tok/s', round(d['ms_per_step'],2), 'ms/step', d['clocks']['sm_mhz'], 'MHz')
+except Exception as e:
+    print('mp $mode FAILED', e); print(open('$O/bench_mp_$mode.err').read()[-1200:])
+"
+done
+for poll in 0 1; do
+  B200_FUSED_POLL=$poll step "bench ddp poll=$poll" 500 $TR --master-port 29522 bench.py --method ddp --gpus $N --steps 4 --warmup 3 --no-e2e 2> $O/bench_ddp_poll$poll.err | grep "^{" > $O/bench_ddp_poll$poll.json
+  python -c "
+import json
+try:
+    d=json.load(open('$O/bench_ddp_poll$poll.json')); print('ddp poll=$poll', round(d['value']), 'tok/s', round(d['ms_per_step'],2), 'ms/step', d['clocks']['sm_mhz'], 'MHz')
+except Exception as e:
+    print('ddp poll=$poll FAILED', e); print(open('$O/bench_ddp_poll$poll.err').read()[-1200:])
+"
+done
