@@ -7,7 +7,8 @@ O=gpurun_out/queued
 mkdir -p $O
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 export B200_QUEUED_TESTS=1
-step() { echo "== $1"; shift; timeout "$@"; echo "rc=$?"; }
+exec 3>&1                                  # step() reports on the real stdout even when the command's output is redirected
+step() { echo "== $1" >&3; shift; timeout "$@"; echo "rc=$?" >&3; }
 
 # 1. single GPU: CUDA-graph replay (bitwise vs eager), then the whole 1-GPU suite with the queued tests on
 step "graph replay test" 300 python -m pytest tests/test_train_gpu.py -q -m gpu -k cuda_graph > $O/graph.log 2>&1; tail -3 $O/graph.log
