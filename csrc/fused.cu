@@ -25,6 +25,7 @@
 #include "gemm_kernel.cuh"
 #include "../include/b200ffn.h"
 #include <cstdlib>
+#include <type_traits>
 
 namespace b200 {
 
@@ -51,6 +52,15 @@ struct FusedParams {
     int owned_cap;
     int owned_count;                 // tiles this rank owns in this call
     int ready_base;                  // word offset of the ready flags inside the flag block
+};
+
+// Adam variant (OPT = 1): the owner of a tile also owns its optimizer state - fp32 moments in a compact per-owned-tile
+// layout [owned slot][128][256], i.e. 1/world of the state per rank (ZeRO-1 for DDP, the natural layout for FSDP).
+// Formula as b200_adam_bf16 (elementwise.cu).  Written after round 1's GPU budget was spent: not yet run on hardware.
+struct FusedAdamParams : FusedParams {
+    float* adam_m;
+    float* adam_v;
+    float lr, beta1, beta2, eps, bc1, bc2, gscale;
 };
 
 __host__ __device__ __forceinline__ int owner_of(const FusedParams& p, const GemmCore& g, int m_blk, int n_blk, int& k_local) {
@@ -90,9 +100,9 @@ __device__ __forceinline__ uint4 pack_row8(const uint32_t* a) {
 // POLL = 0: side warps re-scan their owned tiles every 200 ns while nothing is ready (the validated default).
 // POLL = 1: exponential back-off 256 ns -> 4 us while nothing is ready, reset on progress (B200_FUSED_POLL=1; written
 //           after round 1's GPU budget was spent to cut the polling instructions ncu shows - not yet run on hardware).
-template <int SIDE_WARPS, int POLL = 0>
+template <int SIDE_WARPS, int POLL = 0, int OPT = 0>
 struct FusedEpiT {
-    using Params = FusedParams;
+    using Params = std::conditional_t<OPT == 1, FusedAdamParams, FusedParams>;
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
     static constexpr int EXTRA_WARPS = SIDE_WARPS;   // side warps reduce/broadcast owned tiles under the MMAs
     static constexpr int LAUNCH_BOUND_PAD = 32;      // a one-warp barrier kernel of another stream (FSDP prefetch) must fit beside it
@@ -226,7 +236,7 @@ struct FusedEpiT {
         const __nv_bfloat16* inb = reinterpret_cast<const __nv_bfloat16*>(p.inbox[p.rank]);
         const int col = n_blk * BN + lane * 8;                       // 32 lanes x 8 columns = one 256-wide row
         if (col >= g.N) return;
-        constexpr int RB = 2;
+        constexpr int RB = OPT == 1 ? 1 : 2;                         // Adam keeps 16 more floats live per row
 #pragma unroll 1
         for (int r0 = 0; r0 < ROWS; r0 += RB) {
             uint4 v[RB][MAX_WORLD_F];
@@ -241,7 +251,7 @@ struct FusedEpiT {
 #pragma unroll
             for (int rr = 0; rr < RB; ++rr) {
                 const int grow = m_blk * BM + swarp * ROWS + r0 + rr;
-                if (p.op == FOP_SGD && grow < g.M)
+                if ((OPT == 1 || p.op == FOP_SGD) && grow < g.M)
                     w[rr] = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.out[p.rank]) + (size_t)(grow - p.out_row_offset) * p.ldo + col);
             }
 #pragma unroll
@@ -258,7 +268,26 @@ struct FusedEpiT {
                     }
                 }
                 const size_t off = (size_t)(grow - p.out_row_offset) * p.ldo + col;
-                if (p.op == FOP_SGD) {
+                if constexpr (OPT == 1) {
+                    const size_t so = ((size_t)k_local * BM + (size_t)(swarp * ROWS + r0 + rr)) * BN + lane * 8;
+                    float4* mp = reinterpret_cast<float4*>(p.adam_m + so);
+                    float4* vp = reinterpret_cast<float4*>(p.adam_v + so);
+                    const float4 m0 = mp[0], m1 = mp[1], v0 = vp[0], v1 = vp[1];
+                    float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+                    float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+                    const uint4 ww = w[rr];
+                    const float wf[8] = {bf16_lo(ww.x), bf16_hi(ww.x), bf16_lo(ww.y), bf16_hi(ww.y),
+                                         bf16_lo(ww.z), bf16_hi(ww.z), bf16_lo(ww.w), bf16_hi(ww.w)};
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float gr = p.gscale * acc[j];
+                        mm[j] = p.beta1 * mm[j] + (1.0f - p.beta1) * gr;
+                        vv[j] = p.beta2 * vv[j] + (1.0f - p.beta2) * gr * gr;
+                        acc[j] = wf[j] - p.lr * ((mm[j] / p.bc1) / (sqrtf(vv[j] / p.bc2) + p.eps));
+                    }
+                    mp[0] = make_float4(mm[0], mm[1], mm[2], mm[3]); mp[1] = make_float4(mm[4], mm[5], mm[6], mm[7]);
+                    vp[0] = make_float4(vv[0], vv[1], vv[2], vv[3]); vp[1] = make_float4(vv[4], vv[5], vv[6], vv[7]);
+                } else if (p.op == FOP_SGD) {
                     const uint4 ww = w[rr];
                     acc[0] = bf16_lo(ww.x) - p.alpha * acc[0]; acc[1] = bf16_hi(ww.x) - p.alpha * acc[1];
                     acc[2] = bf16_lo(ww.y) - p.alpha * acc[2]; acc[3] = bf16_hi(ww.y) - p.alpha * acc[3];
@@ -330,11 +359,18 @@ extern "C" int b200_debug_tile_order(int tiles_m, int tiles_n, int group_m, int*
 
 // D = A*B^T-style GEMM (same operand conventions as b200_gemm_bf16) whose output tiles are reduced across
 // `world` ranks inside the kernel.  See include/b200ffn.h.
-extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
-                                        int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
-                                        void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
-                                        int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
-                                        float alpha, int max_ctas, void* stream) {
+struct AdamArgs {
+    float* m;
+    float* v;
+    float lr, beta1, beta2, eps, gscale;
+    int step;
+};
+
+static int fused_entry(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
+                       int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
+                       void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
+                       int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
+                       float alpha, int max_ctas, void* stream, const AdamArgs* adam) {
     if (world < 1 || world > MAX_WORLD_F || rank < 0 || rank >= world) { set_last_error("gemm_allreduce: bad rank/world"); return B200_ERR_ARG; }
     if (out_peers == nullptr || inbox_peers == nullptr || flag_peers == nullptr) { set_last_error("gemm_allreduce: null peer table"); return B200_ERR_ARG; }
     if (seq == 0) { set_last_error("gemm_allreduce: seq must start at 1"); return B200_ERR_ARG; }
@@ -390,6 +426,19 @@ extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_majo
         overlap = link_ms > 0.6 * mma_ms;
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (adam != nullptr) {
+        if (adam->m == nullptr || adam->v == nullptr || adam->step < 1 || (reinterpret_cast<uintptr_t>(adam->m) & 15) || (reinterpret_cast<uintptr_t>(adam->v) & 15)) {
+            set_last_error("gemm_allreduce_adam: moments must be 16-byte aligned device pointers and step >= 1"); return B200_ERR_ARG;
+        }
+        FusedAdamParams ap{};
+        static_cast<FusedParams&>(ap) = p;
+        ap.op = FOP_SGD;                      // (unused by the Adam instantiation; keeps the weight-tile load path identical)
+        ap.adam_m = adam->m; ap.adam_v = adam->v;
+        ap.lr = adam->lr; ap.beta1 = adam->beta1; ap.beta2 = adam->beta2; ap.eps = adam->eps; ap.gscale = adam->gscale;
+        ap.bc1 = 1.0f - powf(adam->beta1, (float)adam->step);
+        ap.bc2 = 1.0f - powf(adam->beta2, (float)adam->step);
+        return launch_gemm<FusedEpiT<4, 0, 1>>(o, ap, max_ctas, st, rot, world, overlap);
+    }
     static int poll = -1;                       // B200_FUSED_POLL=1: exponential back-off in the side warps (unvalidated)
     if (poll < 0) {
         const char* e = getenv("B200_FUSED_POLL");
@@ -398,4 +447,28 @@ extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_majo
     if (poll == 1 && side == 4) return launch_gemm<FusedEpiT<4, 1>>(o, p, max_ctas, st, rot, world, overlap);
     if (side == 2) return launch_gemm<FusedEpiT<2>>(o, p, max_ctas, st, rot, world, overlap);
     return launch_gemm<FusedEpiT<4>>(o, p, max_ctas, st, rot, world, overlap);
+}
+
+extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
+                                        int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
+                                        void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
+                                        int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
+                                        float alpha, int max_ctas, void* stream) {
+    return fused_entry(A, lda, a_major, B, ldb, b_major, M, N, K, out_peers, ldo, out_row_offset, inbox_peers, flag_peers, owned_cap,
+                       ready_cap, rank, world, seq, owner_mode, op, broadcast, alpha, max_ctas, stream, nullptr);
+}
+
+// Same kernel with the Adam update in the owner's reduction: out = W - lr * mhat / (sqrt(vhat) + eps) with the gradient
+// gscale * sum_ranks(A B^T).  `adam_m` / `adam_v`: LOCAL fp32 moments of this rank's owned tiles, compact layout
+// [owned slot][128][256] = b200_fused_adam_state_bytes(owned_cap) bytes each, zero-initialised by the caller; `step` >= 1.
+extern "C" long long b200_fused_adam_state_bytes(int owned_cap) { return (long long)owned_cap * TILE_ELEMS * 4; }
+extern "C" int b200_gemm_allreduce_adam_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
+                                             int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
+                                             void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
+                                             int rank, int world, unsigned int seq, int owner_mode, int broadcast,
+                                             float* adam_m, float* adam_v, float lr, float beta1, float beta2, float eps, int step,
+                                             float grad_scale, int max_ctas, void* stream) {
+    AdamArgs a{adam_m, adam_v, lr, beta1, beta2, eps, grad_scale, step};
+    return fused_entry(A, lda, a_major, B, ldb, b_major, M, N, K, out_peers, ldo, out_row_offset, inbox_peers, flag_peers, owned_cap,
+                       ready_cap, rank, world, seq, owner_mode, FOP_SGD, broadcast, 1.0f, max_ctas, stream, &a);
 }

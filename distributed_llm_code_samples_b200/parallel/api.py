@@ -10,6 +10,7 @@ per-rank trainer and writes the result back into CPU shared-memory tensors owned
 from __future__ import annotations
 
 import copy
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -67,8 +68,10 @@ def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Seque
 def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
     """The peer-memory fused kernels need the native ops, bf16, >1 rank, SGD, no bias and TMA-legal shapes
     (FSDP additionally needs every row shard to be a whole number of 128-row tiles)."""
+    # Adam inside the fused kernels (DDP / FSDP) is written but has not run on hardware yet: opt-in via B200_FUSED_ADAM=1
+    opt_ok = cfg.optimizer == "sgd" or (cfg.optimizer == "adam" and method in ("ddp", "fsdp") and os.environ.get("B200_FUSED_ADAM") == "1")
     ok = (getattr(ops, "name", "") == "native" and comm.world > 1 and cfg.dtype in ("bf16", "bfloat16")
-          and cfg.optimizer == "sgd" and not cfg.bias and cfg.model_size % 8 == 0 and cfg.ffn_dim % 8 == 0)
+          and opt_ok and not cfg.bias and cfg.model_size % 8 == 0 and cfg.ffn_dim % 8 == 0)
     if method == "fsdp":
         ok = ok and cfg.model_size % (128 * comm.world) == 0 and cfg.ffn_dim % (128 * comm.world) == 0
     if method == "mp":
@@ -79,7 +82,7 @@ def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
             ok = ok and cfg.model_size % 64 == 0
     if not ok:
         if cfg.comm == "fused":
-            raise RuntimeError("comm=fused needs impl=native, bf16, SGD, no bias, world>1, dims % 8 == 0 "
+            raise RuntimeError("comm=fused needs impl=native, bf16, SGD (Adam for DDP/FSDP with B200_FUSED_ADAM=1), no bias, world>1, dims % 8 == 0 "
                                "(FSDP: dims % (128*world) == 0; MP: no residual, sp form needs tokens % (128*world) == 0)")
         return False
     try:

@@ -62,6 +62,28 @@ class FusedChannel:
         nv._check(rc, "b200_gemm_allreduce_bf16")
         nv.launch_count += 1
 
+    def adam_state(self, M: int, N: int, owner_mode: int) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Zeroed fp32 moments for the tiles this rank owns of an ``[M, N]`` weight (compact per-tile layout)."""
+        lib = nv.load()
+        cap = int(lib.b200_fused_owned_tiles(M, N, self.sw.world, owner_mode))
+        n = int(lib.b200_fused_adam_state_bytes(cap)) // 4
+        return (torch.zeros(n, dtype=torch.float32, device=self.sw.device), torch.zeros(n, dtype=torch.float32, device=self.sw.device))
+
+    def gemm_adam(self, A: torch.Tensor, a_major: int, B: torch.Tensor, b_major: int, M: int, N: int, K: int,
+                  out_peers, ldo: int, out_row_offset: int, owner_mode: int, broadcast: bool, state, lr: float, step: int,
+                  beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, grad_scale: float = 1.0, max_ctas: int = 0) -> None:
+        """As ``gemm`` with FOP_SGD, but the owner applies Adam (NOT YET RUN ON HARDWARE)."""
+        self.seq += 1
+        sw = self.sw
+        m, v = state
+        rc = nv.load().b200_gemm_allreduce_adam_bf16(
+            A.data_ptr(), A.stride(0), a_major, B.data_ptr(), B.stride(0), b_major, M, N, K, out_peers, ldo,
+            out_row_offset, self.inbox.peers_c, self.flags.peers_c, self.owned_cap, self.ready_cap, sw.rank, sw.world,
+            self.seq, owner_mode, int(broadcast), m.data_ptr(), v.data_ptr(), float(lr), float(beta1), float(beta2), float(eps),
+            int(step), float(grad_scale), int(max_ctas), nv._stream())
+        nv._check(rc, "b200_gemm_allreduce_adam_bf16")
+        nv.launch_count += 1
+
 
 def _owned_cap(shapes, world: int, owner_mode: int) -> int:
     lib = nv.load()
@@ -119,12 +141,26 @@ class FusedDDPTrainer:
         self.peer_tabs = [(self.wbuf.peers_at(o1), self.wbuf.peers_at(o2)) for o1, o2 in self.offsets]
         shapes = [(F, D), (D, F)]
         self.chan = FusedChannel(self.sw, _owned_cap(shapes, comm.world, OWN_INTERLEAVED), max(_tiles(*s) for s in shapes))
+        self.adam = cfg.optimizer == "adam"
+        if self.adam:                          # 1/world of the moments per rank: the owner of a tile owns its state
+            self.comm_name = "fused: dW GEMM + all-reduce + Adam (state sharded by tile owner) in one kernel"
+            self.state = [[self.chan.adam_state(*shapes[k], OWN_INTERLEAVED) for k in range(2)] for _ in layers_params]
+        self.t = 0
         self.sw.host_barrier()
+
+    def _update(self, i: int, k: int, dy: torch.Tensor, xin: torch.Tensor, M: int, N: int, T: int) -> None:
+        """``W[i][k] -= update(sum over ranks of dy^T xin)`` and the new weight stored to every replica - one kernel."""
+        if self.adam:
+            self.chan.gemm_adam(dy, nv.MAJOR_MN, xin, nv.MAJOR_MN, M, N, T, self.peer_tabs[i][k], N, 0, OWN_INTERLEAVED, True,
+                                self.state[i][k], self.lr, self.t)
+        else:
+            self.chan.gemm(dy, nv.MAJOR_MN, xin, nv.MAJOR_MN, M, N, T, self.peer_tabs[i][k], N, 0, OWN_INTERLEAVED, FOP_SGD, True, self.lr)
 
     def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         from ..models.ffn import tlayers_ffn_fwd
         cfg, ops = self.cfg, self.ops
         D, F = cfg.model_size, cfg.ffn_dim
+        self.t += 1
         y, acts = tlayers_ffn_fwd(ops, self.params, x, self.opts)
         d = dloss_dx
         T = x.shape[0]
@@ -136,9 +172,9 @@ class FusedDDPTrainer:
                 a, pre = ops.linear_act(s.x, W1, self.opts.activation)
             dh = ops.grad_input(d, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
             # dW2 = d^T a  summed over ranks, W2 -= lr * dW2, new W2 stored to every replica - one kernel
-            self.chan.gemm(d, nv.MAJOR_MN, a, nv.MAJOR_MN, D, F, T, self.peer_tabs[i][1], F, 0, OWN_INTERLEAVED, FOP_SGD, True, self.lr)
+            self._update(i, 1, d, a, D, F, T)
             dn = ops.grad_input(dh, W1, add=d if self.opts.residual else None) if i > 0 else None
-            self.chan.gemm(dh, nv.MAJOR_MN, s.x, nv.MAJOR_MN, F, D, T, self.peer_tabs[i][0], D, 0, OWN_INTERLEAVED, FOP_SGD, True, self.lr)
+            self._update(i, 0, dh, s.x, F, D, T)
             acts[i] = None
             d = dn
         return y
@@ -182,7 +218,20 @@ class FusedFSDPTrainer:
         self.coll = CollChannel(self.sw)
         self.side = torch.cuda.Stream(device=device)
         self._pending = {}
+        self.adam = cfg.optimizer == "adam"
+        if self.adam:
+            self.comm_name = "fused: dW GEMM + reduce-scatter + sharded Adam in one kernel; P2P-DMA all-gather prefetch"
+            self.state = [[self.chan.adam_state(*shapes[k], OWN_ROW_SHARDED) for k in range(2)] for _ in self.shards]
+        self.t = 0
         self.sw.host_barrier()
+
+    def _update(self, i: int, k: int, dy: torch.Tensor, xin: torch.Tensor, M: int, N: int, T: int) -> None:
+        """Rows ``[r*M/n, (r+1)*M/n)`` of ``dy^T xin`` summed over ranks and applied to MY shard - one kernel, no broadcast."""
+        out, row0 = self.local_out[2 * i + k], self.rank * (M // self.world)
+        if self.adam:
+            self.chan.gemm_adam(dy, nv.MAJOR_MN, xin, nv.MAJOR_MN, M, N, T, out, N, row0, OWN_ROW_SHARDED, False, self.state[i][k], self.lr, self.t)
+        else:
+            self.chan.gemm(dy, nv.MAJOR_MN, xin, nv.MAJOR_MN, M, N, T, out, N, row0, OWN_ROW_SHARDED, FOP_SGD, False, self.lr)
 
     def _start_gather(self, layer: int) -> None:
         if not (0 <= layer < self.L) or layer in self._pending:
@@ -213,8 +262,8 @@ class FusedFSDPTrainer:
         from ..models.ffn import tlayer_ffn_fwd
         cfg, ops, L = self.cfg, self.ops, self.L
         D, F = cfg.model_size, cfg.ffn_dim
-        n, r = self.world, self.rank
         T = x.shape[0]
+        self.t += 1
         acts = []
         y = x
         self._start_gather(0)
@@ -236,10 +285,9 @@ class FusedFSDPTrainer:
             if a is None:
                 a, pre = ops.linear_act(s.x, W1, self.opts.activation)
             dh = ops.grad_input(d, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
-            # dW2 rows [r*D/n, (r+1)*D/n) summed over ranks and applied to MY shard of W2 - one kernel, no broadcast
-            self.chan.gemm(d, nv.MAJOR_MN, a, nv.MAJOR_MN, D, F, T, self.local_out[2 * i + 1], F, r * (D // n), OWN_ROW_SHARDED, FOP_SGD, False, self.lr)
+            self._update(i, 1, d, a, D, F, T)
             dn = ops.grad_input(dh, W1, add=d if self.opts.residual else None) if i > 0 else None
-            self.chan.gemm(dh, nv.MAJOR_MN, s.x, nv.MAJOR_MN, F, D, T, self.local_out[2 * i], D, r * (F // n), OWN_ROW_SHARDED, FOP_SGD, False, self.lr)
+            self._update(i, 0, dh, s.x, F, D, T)
             acts[i] = None
             d = dn
         return y

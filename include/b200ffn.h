@@ -168,6 +168,20 @@ int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const vo
                              int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
                              float alpha, int max_ctas, void* stream);
 
+/* Same kernel with an ADAM update in the owner's reduction instead of SGD (the north star's "sharded SGD/Adam update"):
+ * out = W - lr * mhat / (sqrt(vhat) + eps), gradient = grad_scale * sum over ranks of A B^T, formula as b200_adam_bf16.
+ * `adam_m` / `adam_v`: LOCAL fp32 moments of the tiles this rank owns, compact layout [owned slot][128][256]
+ * (b200_fused_adam_state_bytes(owned_cap) bytes each, zeroed by the caller before the first step): every rank holds
+ * 1/world of the optimizer state, for DDP as well as FSDP.  `step` >= 1 (bias correction).  No counterpart in the
+ * reference (SGD only, train_ffns.py:172).  NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent). */
+long long b200_fused_adam_state_bytes(int owned_cap);
+int b200_gemm_allreduce_adam_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
+                                  int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
+                                  void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
+                                  int rank, int world, unsigned int seq, int owner_mode, int broadcast,
+                                  float* adam_m, float* adam_v, float lr, float beta1, float beta2, float eps, int step,
+                                  float grad_scale, int max_ctas, void* stream);
+
 /* ---- all-gather -> GEMM in one kernel (csrc/gather_gemm.cu) -------------------------------------------------------
  * C[M,N] = epilogue(A_full[M,K] * B^T) where A is token-sharded: a_peers[q] is rank q's [M,K] bf16 buffer (K-major,
  * contiguous, 128-byte aligned, same symmetric offset everywhere) in which only rows [q*M/world, (q+1)*M/world) are

@@ -144,6 +144,25 @@ def test_fused_trainer_matches_nccl_trainer(method):
 
 
 @queued
+@pytest.mark.parametrize("method", ["ddp", "fsdp"])
+def test_fused_adam_matches_unfused_adam(method, monkeypatch):
+    """Adam inside the fused kernel's owner reduction (moments sharded by tile owner) vs the unfused trainer (bf16
+    all-reduce / reduce-scatter, then b200_adam_bf16).  Adam's first step moves every weight by ~lr regardless of the
+    gradient scale, so the two must agree closely; two steps exercise the stored moments."""
+    from distributed_llm_code_samples_b200.parallel import api
+    monkeypatch.setenv("B200_FUSED_ADAM", "1")
+    lp, _ = _init()
+    seeds = torch.arange(2 * WORLD)
+    fn = {"ddp": api.train_ddp, "fsdp": api.train_fsdp}[method]
+    fused = fn(lp, seeds, 512, DM, _cfg(comm="fused", optimizer="adam", lr=1e-3))
+    unfused = fn(lp, seeds, 512, DM, _cfg(comm="nccl", optimizer="adam", lr=1e-3))
+    upd = lambda res: [[p.float() - q for p, q in zip(a, b)] for a, b in zip(res, lp)]
+    assert all(torch.isfinite(p).all() for l in fused for p in l)
+    assert max(u.abs().max().item() for l in upd(fused) for u in l) > 0
+    assert _rel(upd(fused), upd(unfused)) < 0.25
+
+
+@queued
 @pytest.mark.parametrize("method,extra", [("ddp", {"optimizer": "adam"}), ("fsdp", {"bias": True}), ("mp", {"residual": True})])
 def test_unfused_trainers_on_native_collectives_match_nccl(method, extra):
     """--comm native: the plain trainers (so Adam / bias / residual work) with every collective on the peer-memory

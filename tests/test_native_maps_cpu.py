@@ -113,3 +113,21 @@ def test_gather_gemm_argument_validation_without_a_gpu(lib):
     assert call(K=72) == -1 and b"multiple of 64" in lib.b200_last_error()
     assert call(seq=0) == -1 and b"seq" in lib.b200_last_error()
     assert call(rank=2) == -1
+
+
+def test_fused_adam_entry_validation_without_a_gpu(lib):
+    lib.b200_last_error.restype = C.c_char_p
+    lib.b200_fused_adam_state_bytes.restype = C.c_longlong
+    assert lib.b200_fused_adam_state_bytes(3) == 3 * 128 * 256 * 4
+    pp = C.POINTER(C.c_void_p)
+    vp, ll, i, f, u = C.c_void_p, C.c_longlong, C.c_int, C.c_float, C.c_uint
+    lib.b200_gemm_allreduce_adam_bf16.argtypes = [vp, ll, i, vp, ll, i, i, i, i, pp, ll, i, pp, pp, i, i, i, i, u, i, i,
+                                                  vp, vp, f, f, f, f, i, f, i, vp]
+    two = (C.c_void_p * 2)(0x1000, 0x2000)
+    # world=3 > table of 2 is never dereferenced: the rank/world and seq checks come first
+    assert lib.b200_gemm_allreduce_adam_bf16(0x100, 8, 1, 0x200, 8, 1, 256, 256, 64, two, 256, 0, two, two, 4, 4, 5, 2, 1, 0, 1,
+                                             0x300, 0x400, 1e-3, 0.9, 0.999, 1e-8, 1, 1.0, 0, None) == -1
+    assert b"rank/world" in lib.b200_last_error()
+    assert lib.b200_gemm_allreduce_adam_bf16(0x100, 8, 1, 0x200, 8, 1, 256, 256, 64, two, 256, 0, two, two, 4, 4, 0, 2, 0, 0, 1,
+                                             0x300, 0x400, 1e-3, 0.9, 0.999, 1e-8, 1, 1.0, 0, None) == -1
+    assert b"seq" in lib.b200_last_error()
