@@ -75,7 +75,8 @@ def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
     if method == "fsdp":
         ok = ok and cfg.model_size % (128 * comm.world) == 0 and cfg.ffn_dim % (128 * comm.world) == 0
     if method == "mp":
-        ok = ok and not cfg.residual and (cfg.ffn_dim // comm.world) % 8 == 0
+        # the residual form of the fused MP trainer reuses the kernels' in-place update mode; not yet run on hardware
+        ok = ok and (not cfg.residual or os.environ.get("B200_FUSED_MP_RESIDUAL") == "1") and (cfg.ffn_dim // comm.world) % 8 == 0
         if cfg.mp_mode in ("sp", "spf"):
             ok = ok and cfg.tokens % (128 * comm.world) == 0
         if cfg.mp_mode == "spf":
@@ -83,7 +84,7 @@ def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
     if not ok:
         if cfg.comm == "fused":
             raise RuntimeError("comm=fused needs impl=native, bf16, SGD (Adam for DDP/FSDP with B200_FUSED_ADAM=1), no bias, world>1, dims % 8 == 0 "
-                               "(FSDP: dims % (128*world) == 0; MP: no residual, sp form needs tokens % (128*world) == 0)")
+                               "(FSDP: dims % (128*world) == 0; MP: residual needs B200_FUSED_MP_RESIDUAL=1, sp forms need tokens % (128*world) == 0)")
         return False
     try:
         from . import fused  # noqa: F401

@@ -327,8 +327,9 @@ class FusedMPTrainer:
     def __init__(self, ops, comm, cfg: TrainConfig, shards: List[Params], device: torch.device):
         self.ops, self.comm, self.cfg, self.shards = ops, comm, cfg, shards
         self.opts = block_opts(cfg)
-        if cfg.residual:
-            raise RuntimeError("fused MP has no residual path; use --comm nccl")
+        # Residual: the output buffer is pre-filled with the residual and the kernel runs its in-place update mode with
+        # alpha = -1 (out = out + sum over ranks), i.e. the DDP / FSDP code path of the same kernel.
+        self.residual = cfg.residual
         self.sp = cfg.mp_mode == "sp"
         self.spf = cfg.mp_mode == "spf"
         if self.sp:
@@ -413,7 +414,11 @@ class FusedMPTrainer:
             a, pre = ops.linear_act(y, W1, self.opts.activation)
             saved.append((y, None if self.opts.recompute else a, None if self.opts.recompute else pre))
             # y_l = sum over ranks of a_r @ W2_r^T, delivered to every rank - one kernel (:302-303)
-            self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
+            if self.residual:
+                self.y[l].copy_(y)
+                self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SGD, True, -1.0)
+            else:
+                self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
             y = self.y[l]
         d = dloss_dx
         for i in reversed(range(self.L)):
@@ -427,7 +432,11 @@ class FusedMPTrainer:
             if i > 0:
                 slot = i % 2
                 # dx = sum over ranks of dh_r @ W1_r, delivered to every rank - one kernel (:308-309)
-                self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
+                if self.residual:
+                    self.dx[slot].copy_(d)
+                    self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SGD, True, -1.0)
+                else:
+                    self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
                 dn = self.dx[slot]
             ops.grad_weight_sgd_(W1, dh, xin, self.lr)
             saved[i] = None
@@ -452,17 +461,22 @@ class FusedMPTrainer:
         self.xs0.copy_(x[r * Ts:(r + 1) * Ts])
         saved = []
         cur_off = self.xs0_off
+        cur_shard = self.xs0
         for l, (W1, W2) in enumerate(self.shards):
             xfull = self._gather_tokens(cur_off, T, D)                    # all-gather -> column-parallel GEMM
             a, pre = ops.linear_act(xfull, W1, self.opts.activation)
             saved.append((cur_off, None if self.opts.recompute else a, None if self.opts.recompute else pre))
             # row-parallel GEMM -> reduce-scatter over token shards, one kernel: I keep rows [r*Ts, (r+1)*Ts)
-            self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.local_tab(self.ys[l]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
-            cur_off = self.ys_off[l]
+            if self.residual:
+                self.ys[l].copy_(cur_shard)
+                self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.local_tab(self.ys[l]), D, r * Ts, OWN_ROW_SHARDED, FOP_SGD, False, -1.0)
+            else:
+                self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.local_tab(self.ys[l]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
+            cur_off, cur_shard = self.ys_off[l], self.ys[l]
         # upstream gradient: same layout, token-sharded; stage my shard in a rotating symmetric slot
         d_slot = self.L % 2
         self.dxs[d_slot].copy_(dloss_dx[r * Ts:(r + 1) * Ts])
-        d_off = self.dxs_off[d_slot]
+        d_off, d_shard = self.dxs_off[d_slot], self.dxs[d_slot]
         for i in reversed(range(self.L)):
             W1, W2 = self.shards[i]
             x_off, a, pre = saved[i]
@@ -474,8 +488,12 @@ class FusedMPTrainer:
             ops.grad_weight_sgd_(W2, dfull, a, self.lr)
             if i > 0:
                 slot = i % 2
-                self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.local_tab(self.dxs[slot]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
-                d_off = self.dxs_off[slot]
+                if self.residual:
+                    self.dxs[slot].copy_(d_shard)
+                    self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.local_tab(self.dxs[slot]), D, r * Ts, OWN_ROW_SHARDED, FOP_SGD, False, -1.0)
+                else:
+                    self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.local_tab(self.dxs[slot]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
+                d_off, d_shard = self.dxs_off[slot], self.dxs[slot]
             ops.grad_weight_sgd_(W1, dh, xfull, self.lr)
             saved[i] = None
         return self._gather_tokens(self.ys_off[self.L - 1], T, D)
@@ -508,12 +526,18 @@ class FusedMPTrainer:
             return out, None
         raise ValueError(kind)
 
-    def rs_gemm(self, A: torch.Tensor, W: torch.Tensor, b_major: int, dst: torch.Tensor) -> None:
-        """``dst[own token rows] = sum over ranks of A @ W^T`` - row-parallel GEMM + reduce-scatter in one kernel."""
+    def rs_gemm(self, A: torch.Tensor, W: torch.Tensor, b_major: int, dst: torch.Tensor, residual: Optional[torch.Tensor] = None) -> None:
+        """``dst[own token rows] = sum over ranks of A @ W^T (+ residual[own token rows])`` - row-parallel GEMM +
+        reduce-scatter in one kernel."""
         T, D = dst.shape
         Ts = T // self.world
-        own = dst[self.rank * Ts:(self.rank + 1) * Ts]
-        self.chan.gemm(A, nv.MAJOR_K, W, b_major, T, D, A.shape[1], self.local_tab(own), D, self.rank * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
+        rows = slice(self.rank * Ts, (self.rank + 1) * Ts)
+        own = dst[rows]
+        if residual is not None:
+            own.copy_(residual[rows])
+            self.chan.gemm(A, nv.MAJOR_K, W, b_major, T, D, A.shape[1], self.local_tab(own), D, self.rank * Ts, OWN_ROW_SHARDED, FOP_SGD, False, -1.0)
+        else:
+            self.chan.gemm(A, nv.MAJOR_K, W, b_major, T, D, A.shape[1], self.local_tab(own), D, self.rank * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
 
     def gather_out(self, buf: torch.Tensor) -> torch.Tensor:
         """In-place all-gather of the token shards by the barrier-ed native kernel.  Its opening barrier is also what lets
@@ -544,7 +568,7 @@ def spf_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
     rows, which operand layout) is testable on CPU with gloo stand-ins (``tests/test_spf_schedule_cpu.py``):
 
     * ``t.ag_gemm(buf, W, b_major, kind, aux)``  all-gather ``buf``'s token shards, then ``epilogue(buf @ W^T)``
-    * ``t.rs_gemm(A, W, b_major, dst)``          ``dst[own rows] = sum_ranks A @ W^T``
+    * ``t.rs_gemm(A, W, b_major, dst, res)``     ``dst[own rows] = sum_ranks A @ W^T (+ res[own rows])``
     * ``t.gather_out(buf)``                      all-gather the final output
 
     ``t`` also provides ``shards, L, rank, world, ops, opts, lr`` and the full-size activation buffers ``X[0..L]``,
@@ -561,7 +585,7 @@ def spf_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
     saved = []
     for l, (W1, W2) in enumerate(t.shards):
         a, aux = t.ag_gemm(t.X[l], W1, nv.MAJOR_K, act)                   # completes X[l] as a side effect
-        t.rs_gemm(a, W2, nv.MAJOR_K, t.X[l + 1])                          # my token rows of the next layer's input
+        t.rs_gemm(a, W2, nv.MAJOR_K, t.X[l + 1], t.X[l] if t.opts.residual else None)   # my token rows of the next layer's input
         saved.append(None if t.opts.recompute else (a, aux))
     cur = 0
     t.DX[cur][own].copy_(dloss_dx[own])
@@ -575,7 +599,7 @@ def spf_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         dh, _ = t.ag_gemm(t.DX[cur], W2, nv.MAJOR_MN, act + "_bwd", aux)  # completes DX[cur] = the full upstream gradient
         t.ops.grad_weight_sgd_(W2, t.DX[cur], a, t.lr)
         if i > 0:
-            t.rs_gemm(dh, W1, nv.MAJOR_MN, t.DX[1 - cur])
+            t.rs_gemm(dh, W1, nv.MAJOR_MN, t.DX[1 - cur], t.DX[cur] if t.opts.residual else None)
         t.ops.grad_weight_sgd_(W1, dh, t.X[i], t.lr)
         saved[i] = None
         cur = 1 - cur

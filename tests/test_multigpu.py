@@ -144,6 +144,25 @@ def test_fused_trainer_matches_nccl_trainer(method):
 
 
 @queued
+@pytest.mark.parametrize("mp_mode", ["ar", "sp", "spf"])
+def test_fused_mp_with_gelu_and_residual_matches_nccl(mp_mode, monkeypatch):
+    """The north-star block (Linear -> GELU -> Linear, residual) under fused MP: the residual rides on the kernels'
+    in-place update mode (output pre-filled with the residual, alpha = -1)."""
+    from distributed_llm_code_samples_b200.parallel import api
+    monkeypatch.setenv("B200_FUSED_MP_RESIDUAL", "1")
+    lp, _ = _init()
+    seeds = torch.arange(1)
+    T = max(512, 256 * WORLD)
+    kw = dict(activation="gelu", residual=True, mp_mode=mp_mode, lr=1e-3)
+    fused = api.train_tp(lp, seeds, T, DM, _cfg(comm="fused", **kw))
+    nccl = api.train_tp(lp, seeds, T, DM, _cfg(comm="nccl", **kw))
+    upd = lambda res: [[p.float() - q for p, q in zip(a, b)] for a, b in zip(res, lp)]
+    assert all(torch.isfinite(p).all() for l in fused for p in l)
+    assert max(u.abs().max().item() for l in upd(fused) for u in l) > 0
+    assert _rel(upd(fused), upd(nccl)) < 0.25
+
+
+@queued
 @pytest.mark.parametrize("method", ["ddp", "fsdp"])
 def test_fused_adam_matches_unfused_adam(method, monkeypatch):
     """Adam inside the fused kernel's owner reduction (moments sharded by tile owner) vs the unfused trainer (bf16

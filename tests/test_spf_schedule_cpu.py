@@ -53,11 +53,13 @@ class _GlooSpf:
             return h * g, None
         raise ValueError(kind)
 
-    def rs_gemm(self, A, W, b_major, dst):
+    def rs_gemm(self, A, W, b_major, dst, residual=None):
         full = A @ (W.t() if b_major == nv.MAJOR_K else W)
         dist.all_reduce(full)
         Ts = dst.shape[0] // self.world
-        dst[self.rank * Ts:(self.rank + 1) * Ts] = full[self.rank * Ts:(self.rank + 1) * Ts]
+        rows = slice(self.rank * Ts, (self.rank + 1) * Ts)
+        res = residual[rows].clone() if residual is not None else 0.0     # (residual may alias dst's buffer family)
+        dst[rows] = full[rows] + res
         # the rows of dst that belong to other ranks keep whatever they had: poison them so a read would be caught
         for q in range(self.world):
             if q != self.rank:
@@ -81,13 +83,14 @@ def _worker(rank, world, dev, lp, seeds, cfg_dict, out):
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("act,recompute", [("relu", False), ("gelu", False), ("relu", True)])
-def test_spf_schedule_equals_single_device(act, recompute):
+@pytest.mark.parametrize("act,recompute,residual", [("relu", False, False), ("gelu", False, False), ("relu", True, False),
+                                                    ("gelu", False, True), ("relu", True, True)])
+def test_spf_schedule_equals_single_device(act, recompute, residual):
     g = torch.Generator().manual_seed(17)
     lp = ffn.init_stack(L, D, FF, g)
     seeds = torch.tensor([5, 9, 13])
     cfg = TrainConfig(model_size=D, ffn_dim=FF, layers=L, device="cpu", backend="gloo", world_size=2, impl="torch", lr=0.05,
-                      activation=act, recompute=recompute, mp_mode="spf")
+                      activation=act, recompute=recompute, residual=residual, mp_mode="spf")
     shared = [[p.clone().share_memory_() for p in l] for l in lp]
     out = [[torch.empty_like(p).share_memory_() for p in l] for l in lp]
     launch(2, _worker, (shared, seeds, cfg.to_dict(), out), backend="gloo", device="cpu")

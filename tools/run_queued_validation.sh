@@ -15,7 +15,7 @@ step "graph replay test" 300 python -m pytest tests/test_train_gpu.py -q -m gpu 
 step "1-GPU suite (queued on)" 900 python -m pytest tests -q -m gpu --deselect tests/test_multigpu.py > $O/suite_1gpu.log 2>&1; tail -3 $O/suite_1gpu.log
 
 # 2. multi GPU, one queued test per process so that a hang / trap is attributed
-for k in barrier_and_flag_protocol_stress unfused_trainers_on_native_collectives fused_adam_matches_unfused_adam vmm_multicast_all_reduce "fused_trainer_matches_nccl_trainer and mp_spf"; do
+for k in barrier_and_flag_protocol_stress unfused_trainers_on_native_collectives fused_adam_matches_unfused_adam fused_mp_with_gelu_and_residual vmm_multicast_all_reduce "fused_trainer_matches_nccl_trainer and mp_spf"; do
   tag=$(echo "$k" | tr ' ' '_')
   step "multigpu: $k" 400 python -m pytest tests/test_multigpu.py -q -m gpu -k "$k" > $O/mgpu_$tag.log 2>&1; tail -4 $O/mgpu_$tag.log
 done
