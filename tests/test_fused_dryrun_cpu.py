@@ -1,0 +1,145 @@
+"""Dry run of the fused (GPU-only) trainers on CPU.
+
+The peer-memory trainers in parallel/fused.py never execute in the CPU suite, so a Python slip or a mis-ordered C-ABI
+argument would first show up on the GPU box.  Here they run against
+  * a fake symmetric world (CPU memory, every "peer" pointer = the local block),
+  * the REAL native library: each call goes through ctypes marshalling and the entry point's host-side validation
+    (shapes, strides, alignment, inbox / flag capacities, owner maps) and only then fails at its first CUDA call,
+    which this harness tolerates.  Any B200_ERR_ARG (-1) is a test failure.
+The numbers the steps produce are meaningless (no kernel runs); what is checked is that every call is well-formed."""
+import ctypes as C
+
+import pytest
+import torch
+
+from distributed_llm_code_samples_b200.config import TrainConfig
+from distributed_llm_code_samples_b200.models import ffn
+from distributed_llm_code_samples_b200.ops import get_ops, native as nv
+from distributed_llm_code_samples_b200.parallel import fused, symm
+from distributed_llm_code_samples_b200.parallel.base import fsdp_shard, tp_shard
+
+D, FF, L, T, WORLD = 256, 1024, 2, 512, 2
+
+
+class _FakeBuffer(symm.SymmBuffer):
+    def __init__(self, world, nbytes):          # noqa: super().__init__ would cudaMalloc
+        self.world, self.nbytes = world, nbytes
+        self._store = torch.zeros(nbytes + 512, dtype=torch.uint8)
+        pad = (-self._store.data_ptr()) % 256
+        self._base = self._store[pad: pad + nbytes]
+        self.ptr = self._base.data_ptr()
+        self.peer_ptrs = [self.ptr] * world.world
+        self.peers_c = (C.c_void_p * world.world)(*self.peer_ptrs)
+        self._opened, self._cursor = [], 0
+
+
+class _FakeWorld:
+    def __init__(self, rank, world):
+        self.rank, self.world, self.device, self.group, self.buffers = rank, world, torch.device("cpu"), None, []
+
+    def alloc(self, nbytes):
+        b = _FakeBuffer(self, (nbytes + 255) // 256 * 256)
+        self.buffers.append(b)
+        return b
+
+    def host_barrier(self):
+        pass
+
+
+class _Comm:
+    def __init__(self, rank, world):
+        self.rank, self.world = rank, world
+
+
+class _Stream:
+    cuda_stream = 0
+
+    def __init__(self, *a, **k):
+        pass
+
+    def wait_stream(self, *_):
+        pass
+
+    def wait_event(self, *_):
+        pass
+
+
+class _Event:
+    def record(self, *_):
+        pass
+
+
+@pytest.fixture
+def dry(monkeypatch):
+    calls = []
+
+    def check(rc, what):
+        calls.append((what, rc))
+        if rc == -1:
+            raise AssertionError(f"{what}: argument rejected: {nv.load().b200_last_error().decode()}")
+
+    monkeypatch.setattr(nv, "_check", check)
+    monkeypatch.setattr(nv, "_stream", lambda: 0)
+    monkeypatch.setattr(torch.cuda, "Stream", _Stream)
+    monkeypatch.setattr(torch.cuda, "Event", _Event)
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda *a, **k: _Stream())
+    monkeypatch.setattr(fused, "get_symm_world", lambda comm, device: _FakeWorld(comm.rank, comm.world))
+    return calls
+
+
+def _cfg(**kw):
+    return TrainConfig(model_size=D, ffn_dim=FF, layers=L, dtype="bf16", lr=1e-3, world_size=WORLD, **kw)
+
+
+def _batch():
+    g = torch.Generator().manual_seed(0)
+    return torch.randn(T, D, generator=g).to(torch.bfloat16), (0.1 * torch.randn(T, D, generator=g)).to(torch.bfloat16)
+
+
+def _params():
+    return [[p.to(torch.bfloat16) for p in l] for l in ffn.init_stack(L, D, FF, torch.Generator().manual_seed(1))]
+
+
+def _names(calls):
+    return [w for w, _ in calls]
+
+
+@pytest.mark.parametrize("rank", [0, 1])
+@pytest.mark.parametrize("optimizer", ["sgd", "adam"])
+def test_fused_ddp_calls_are_well_formed(dry, rank, optimizer):
+    tr = fused.FusedDDPTrainer(get_ops("torch", "cpu"), _Comm(rank, WORLD), _cfg(optimizer=optimizer), _params(), torch.device("cpu"))
+    tr.step(*_batch())
+    tr.step(*_batch())
+    want = "b200_gemm_allreduce_adam_bf16" if optimizer == "adam" else "b200_gemm_allreduce_bf16"
+    assert _names(dry).count(want) == 2 * 2 * L and all(rc != 0 for _, rc in dry), "no GPU: every call stops at its first CUDA call"
+    assert tr.chan.seq == 2 * 2 * L and tr.t == 2
+
+
+@pytest.mark.parametrize("rank", [0, 1])
+@pytest.mark.parametrize("optimizer", ["sgd", "adam"])
+def test_fused_fsdp_calls_are_well_formed(dry, rank, optimizer):
+    shards = [[fsdp_shard(p, rank, WORLD) for p in l] for l in _params()]
+    tr = fused.FusedFSDPTrainer(get_ops("torch", "cpu"), _Comm(rank, WORLD), _cfg(optimizer=optimizer), shards, torch.device("cpu"))
+    tr.step(*_batch())
+    names = _names(dry)
+    want = "b200_gemm_allreduce_adam_bf16" if optimizer == "adam" else "b200_gemm_allreduce_bf16"
+    assert names.count(want) == 2 * L
+    assert names.count("b200_all_gather_into_dma") == 2 * (2 * L - 1), "prefetch: L forward + L-1 backward layers, two weights each (:244-249)"
+    tr.full_params()
+
+
+@pytest.mark.parametrize("rank", [0, 1])
+@pytest.mark.parametrize("mp_mode", ["ar", "sp", "spf"])
+@pytest.mark.parametrize("residual,act", [(False, "relu"), (True, "gelu")])
+def test_fused_mp_calls_are_well_formed(dry, rank, mp_mode, residual, act):
+    shards = [[tp_shard(p, j, rank, WORLD).contiguous() for j, p in enumerate(l)] for l in _params()]
+    cfg = _cfg(mp_mode=mp_mode, residual=residual, activation=act)
+    tr = fused.FusedMPTrainer(get_ops("torch", "cpu"), _Comm(rank, WORLD), cfg, shards, torch.device("cpu"))
+    y = tr.step(*_batch())
+    assert y.shape == (T, D)
+    names = _names(dry)
+    assert names.count("b200_gemm_allreduce_bf16") == 2 * L - 1, "one fused row-parallel GEMM per layer forward, L-1 backward (:303, :309)"
+    if mp_mode == "spf":
+        assert names.count("b200_gather_gemm_bf16") == 2 * L and names.count("b200_all_gather") == 1
+    if mp_mode == "sp":
+        assert names.count("b200_all_gather_into") == L + 2 * L + 1
