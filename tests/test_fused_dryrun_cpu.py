@@ -143,3 +143,23 @@ def test_fused_mp_calls_are_well_formed(dry, rank, mp_mode, residual, act):
         assert names.count("b200_gather_gemm_bf16") == 2 * L and names.count("b200_all_gather") == 1
     if mp_mode == "sp":
         assert names.count("b200_all_gather_into") == L + 2 * L + 1
+
+
+def test_native_collective_wrappers_are_well_formed(dry):
+    """SymmComm (--comm native): in-place (symmetric operand) and staged (ordinary tensor) forms of every collective."""
+    sw = _FakeWorld(1, WORLD)
+    comm = symm.SymmComm(sw, staging_bytes=1 << 20)
+    inplace = sw.alloc(1 << 16).tensor(0, (4096,), torch.bfloat16)
+    comm.barrier()
+    for t in (inplace, torch.zeros(1000, dtype=torch.bfloat16), torch.zeros(1000, dtype=torch.float32)):
+        comm.all_reduce(t)
+    comm.all_gather_into(torch.zeros(2 * 4096, dtype=torch.bfloat16), inplace)
+    comm.all_gather_into(torch.zeros(2 * 512, dtype=torch.bfloat16), torch.zeros(512, dtype=torch.bfloat16))
+    comm.reduce_scatter_into(torch.zeros(2048, dtype=torch.bfloat16), inplace)
+    comm.reduce_scatter_into(torch.zeros(256, dtype=torch.float32), torch.zeros(512, dtype=torch.float32))
+    h = comm.all_reduce(inplace, async_op=True)
+    h.wait()
+    names = _names(dry)
+    assert names.count("b200_all_reduce") == 4 and names.count("b200_all_gather_into") == 2 and names.count("b200_reduce_scatter") == 2
+    assert names.count("b200_barrier") == 1 and all(rc != 0 for _, rc in dry)
+    assert comm.chan.epoch == 9, "every collective consumed exactly one epoch"
