@@ -82,12 +82,17 @@ class Engine:
                 y = self.step(x.to(self.cfg.torch_dtype), dy.to(self.cfg.torch_dtype))
                 yield float((y.float() ** 2).sum())
             return
-        pf = PinnedPrefetcher(host_batches, self.device)
+        rows = None
+        if self.method == "mp" and self.world > 1 and self.cfg.mp_mode in ("sp", "spf"):
+            # sequence-parallel MP reads only its own token shard of the batch: stage 1/world of the bytes
+            ts = self.cfg.tokens // self.world
+            rows = slice(self.rank * ts, (self.rank + 1) * ts)
+        pf = PinnedPrefetcher(host_batches, self.device, rows=rows)
         pending = None
         host = torch.empty(2, dtype=torch.float32).pin_memory()
         slot = 0
         for x, dy in pf:
-            self.h2d_bytes += x.numel() * x.element_size() + dy.numel() * dy.element_size()
+            self.h2d_bytes += pf.last_bytes
             y = self.step(x, dy)
             m = self.ops.sumsq(y)
             host[slot:slot + 1].copy_(m, non_blocking=True)

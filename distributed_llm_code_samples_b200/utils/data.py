@@ -74,12 +74,28 @@ class PinnedPrefetcher:
     pageable ``.cuda()`` at ``train_ffns.py:106,158,231,294``).  ``next()`` returns device tensors whose copy has
     been ordered before the current stream."""
 
-    def __init__(self, batches: Iterator[Tuple[torch.Tensor, torch.Tensor]], device: torch.device):
+    def __init__(self, batches: Iterator[Tuple[torch.Tensor, torch.Tensor]], device: torch.device,
+                 rows: Optional[slice] = None):
+        """``rows``: copy only these token rows of each tensor (the rest of the device tensor is left uninitialised).
+        Sequence-parallel MP reads nothing but its own token shard of the batch, so it moves 1/world of the bytes."""
         self.it = iter(batches)
         self.device = device
+        self.rows = rows
         self.stream = torch.cuda.Stream(device=device)
+        self.last_bytes = 0          # host->device bytes of the batch most recently returned by next()
+        self._staged_bytes = 0
         self._next = None
         self._preload()
+
+    def _to_device(self, t: torch.Tensor) -> torch.Tensor:
+        if self.rows is None:
+            self._staged_bytes += t.numel() * t.element_size()
+            return t.to(self.device, non_blocking=True)
+        out = torch.empty(t.shape, dtype=t.dtype, device=self.device)
+        src = t[self.rows]
+        out[self.rows].copy_(src, non_blocking=True)
+        self._staged_bytes += src.numel() * src.element_size()
+        return out
 
     def _preload(self) -> None:
         try:
@@ -89,8 +105,9 @@ class PinnedPrefetcher:
             return
         if not x.is_pinned():
             x, dy = x.pin_memory(), dy.pin_memory()
+        self._staged_bytes = 0
         with torch.cuda.stream(self.stream):
-            self._next = (x.to(self.device, non_blocking=True), dy.to(self.device, non_blocking=True))
+            self._next = (self._to_device(x), self._to_device(dy))
 
     def __iter__(self):
         return self
@@ -100,6 +117,7 @@ class PinnedPrefetcher:
             raise StopIteration
         torch.cuda.current_stream(self.device).wait_stream(self.stream)
         x, dy = self._next
+        self.last_bytes = self._staged_bytes
         x.record_stream(torch.cuda.current_stream(self.device))
         dy.record_stream(torch.cuda.current_stream(self.device))
         self._preload()

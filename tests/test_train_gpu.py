@@ -109,3 +109,15 @@ def test_cuda_graph_replay_matches_eager_steps(cuda_device):
     for a, b in zip(eager.params, graphed.params):
         for p, q in zip(a, b):
             assert torch.equal(p, q)
+
+
+@queued
+def test_prefetcher_row_sliced_staging(cuda_device):
+    """Sequence-parallel MP stages only its token shard: those rows arrive, and only their bytes are counted."""
+    from distributed_llm_code_samples_b200.utils.data import PinnedPrefetcher
+    batches = [(torch.randn(64, 32).to(torch.bfloat16), torch.randn(64, 32).to(torch.bfloat16)) for _ in range(3)]
+    pf = PinnedPrefetcher(iter(batches), cuda_device, rows=slice(16, 32))
+    for (hx, hd), (x, d) in zip(batches, pf):
+        torch.cuda.synchronize()
+        assert x.shape == hx.shape and torch.equal(x[16:32].cpu(), hx[16:32]) and torch.equal(d[16:32].cpu(), hd[16:32])
+        assert pf.last_bytes == 2 * 16 * 32 * 2
