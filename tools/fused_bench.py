@@ -86,8 +86,47 @@ def case_mp(T, D, Fs, name):
     return res
 
 
+def case_ag(T, D, Fs, name):
+    """a[T,Fs] = relu(all_gather(x shards)[T,D] W1s[Fs,D]^T): all-gather + column-parallel GEMM (csrc/gather_gemm.cu), and the
+    reduce-scatter form of the row-parallel GEMM that feeds it.  FUSED_BENCH_ONLY=ag (not in the default run: the kernel
+    had not run on hardware when this case was written)."""
+    from distributed_llm_code_samples_b200.parallel.fused import GatherChannel
+    from distributed_llm_code_samples_b200.parallel.symm import CollChannel
+    xb = sw.alloc(T * D * 2 + 4096)
+    x, off = xb.carve((T, D), torch.bfloat16)
+    x.normal_(0, 1)
+    w1 = (torch.randn(Fs, D, device=dev) * 0.02).to(torch.bfloat16)
+    a = torch.empty(T, Fs, dtype=torch.bfloat16, device=dev)
+    mask = torch.empty(T, Fs // 8, dtype=torch.uint8, device=dev)
+    gch = GatherChannel(sw, T)
+    coll = CollChannel(sw)
+    peers = xb.peers_at(off)
+    Ts = T // world
+    res = {"case": name, "world": world, "M": T, "N": Fs, "K": D}
+    res["local_gemm_ms"] = timeit(lambda: nv.gemm(x, 0, w1, 0, a, T, Fs, D, nv.EPI_RELU_MASK, out2=mask))
+    res["fused_allgather_gemm_ms"] = timeit(lambda: gch.gemm(peers, w1, 0, a, T, Fs, D, nv.EPI_RELU_MASK, out2=mask))
+
+    def native_unfused():
+        nv._check(nv.load().b200_all_gather(xb.peers_c, off, T * D * 2, coll.flags.peers_c, rank, world, coll.next_epoch(), 0, nv._stream()), "ag")
+        nv.gemm(x, 0, w1, 0, a, T, Fs, D, nv.EPI_RELU_MASK, out2=mask)
+    res["native_allgather_then_gemm_ms"] = timeit(native_unfused)
+    full = torch.empty(T, D, dtype=torch.bfloat16, device=dev)
+    shard = x[rank * Ts:(rank + 1) * Ts]
+
+    def nccl_unfused():
+        dist.all_gather_into_tensor(full, shard)
+        nv.gemm(full, 0, w1, 0, a, T, Fs, D, nv.EPI_RELU_MASK, out2=mask)
+    res["nccl_allgather_then_gemm_ms"] = timeit(nccl_unfused)
+    res["compute_floor_ms"] = 2.0 * T * D * Fs / (PEAK_TF * 1e12) * 1e3
+    res["link_floor_allgather_ms"] = (world - 1) / world * T * D * 2 / (LINK_GBS * 1e9) * 1e3
+    res["roofline_frac_fused"] = max(res["compute_floor_ms"], res["link_floor_allgather_ms"]) / res["fused_allgather_gemm_ms"]
+    return res
+
+
 out = []
 only = os.environ.get("FUSED_BENCH_ONLY", "")
+if only == "ag":
+    out.append(case_ag(16384, 8192, 28672 // world, "mp-sp a = relu(AG(x) W1^T) (70B shape)"))
 if only in ("", "dw"):
     out.append(case_dw(16384, 4096, 16384, "ddp/fsdp dW1 [F,D]"))
     out.append(case_dw(4096, 16384, 16384, "ddp/fsdp dW2 [D,F]"))

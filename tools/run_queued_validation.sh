@@ -20,7 +20,10 @@ for k in barrier_and_flag_protocol_stress unfused_trainers_on_native_collectives
   step "multigpu: $k" 400 python -m pytest tests/test_multigpu.py -q -m gpu -k "$k" > $O/mgpu_$tag.log 2>&1; tail -4 $O/mgpu_$tag.log
 done
 
-# 3. MP forms, same config: ar (validated) vs sp (validated) vs spf (new); then the poll back-off on DDP
+# 3. per-kernel: all-gather + GEMM fused vs its unfused forms (only after the mp_spf test above passed)
+FUSED_BENCH_ONLY=ag FUSED_BENCH_TAG=_ag step "fused_bench ag" 300 $TR --master-port 29523 tools/fused_bench.py 2>&1 | grep "^{" | cut -c1-700
+
+# 4. MP forms, same config: ar (validated) vs sp (validated) vs spf (new); then the poll back-off on DDP
 for mode in ar sp spf; do
   step "bench mp $mode" 500 $TR --master-port 29521 bench.py --method mp --mp_mode $mode --gpus $N --steps 4 --warmup 3 --no-e2e 2> $O/bench_mp_$mode.err | grep "^{" > $O/bench_mp_$mode.json
   python -c "
