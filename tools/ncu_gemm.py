@@ -25,6 +25,11 @@ fn = {
     "cublas_G2": lambda: torch.matmul(a, w2.T, out=y),
     "cublas_G4": lambda: torch.matmul(dy.T, a, out=dw),
     "fused_dw": None,
+    "fused_adam": None,
+    "gather": None,
+    "sgd": None,
+    "adam": None,
+    "sumsq": None,
 }[case]
 if case == "fused_dw":
     # the fused GEMM + collective kernel in a world of ONE: pushes to its own inbox, side warps reduce + apply SGD
@@ -37,6 +42,35 @@ if case == "fused_dw":
     W, off = wbuf.carve((D, F), torch.bfloat16)
     tab = wbuf.peers_at(off)
     fn = lambda: chan.gemm(dy, 1, a, 1, D, F, T, tab, F, 0, 0, 1, True, 1e-6)
+if case == "fused_adam":
+    # same kernel family with the Adam update in the owner's reduction (world of one)
+    from distributed_llm_code_samples_b200.parallel.symm import SymmWorld
+    from distributed_llm_code_samples_b200.parallel.fused import FusedChannel, _owned_cap, _tiles
+    sw = SymmWorld(0, 1, dev)
+    chan = FusedChannel(sw, _owned_cap([(D, F)], 1, 0), _tiles(D, F))
+    wbuf = sw.alloc(D * F * 2 + 4096)
+    W, off = wbuf.carve((D, F), torch.bfloat16)
+    tab = wbuf.peers_at(off)
+    state = chan.adam_state(D, F, 0)
+    fn = lambda: chan.gemm_adam(dy, 1, a, 1, D, F, T, tab, F, 0, 0, True, state, 1e-6, 1)
+if case == "gather":
+    # the all-gather + GEMM kernel in a world of ONE: no remote rows, so this shows the cost of its extra warps and of the
+    # producer's hook on the plain G1 problem (compare with case G1)
+    from distributed_llm_code_samples_b200.parallel.symm import SymmWorld
+    from distributed_llm_code_samples_b200.parallel.fused import GatherChannel
+    sw = SymmWorld(0, 1, dev)
+    gch = GatherChannel(sw, T)
+    xb = sw.alloc(T * D * 2 + 4096)
+    xs, off = xb.carve((T, D), torch.bfloat16)
+    xs.copy_(x)
+    peers = xb.peers_at(off)
+    fn = lambda: gch.gemm(peers, w1, 0, h, T, F, D, nv.EPI_RELU)
+if case in ("sgd", "adam", "sumsq"):
+    # the standalone elementwise kernels at one weight's size (64 Mi elements)
+    g32 = torch.randn(D, F, device=dev)
+    m, v = torch.zeros(D, F, device=dev), torch.zeros(D, F, device=dev)
+    fn = {"sgd": lambda: nv.sgd_(w2, g32, 1e-6), "adam": lambda: nv.adam_(w2, g32, m, v, 1e-6, 0.9, 0.999, 1e-8, 1),
+          "sumsq": lambda: nv.sumsq(w2)}[case]
 for _ in range(iters):
     fn()
 torch.cuda.synchronize()
