@@ -11,6 +11,7 @@ metric on the device and reads it back (one step late, so the read never stalls 
 """
 from __future__ import annotations
 
+import os
 from typing import Iterable, Iterator, List, Optional, Sequence, Tuple
 
 import torch
@@ -21,7 +22,7 @@ from .ops import get_ops
 from .parallel.api import build_trainer
 from .parallel.comm import LocalComm, make_comm
 from .parallel.launcher import init_from_env
-from .utils.data import PinnedPrefetcher
+from .utils.data import PinnedPrefetcher, ShardedPrefetcher
 
 
 def init_params_on_device(cfg: TrainConfig, device: torch.device, seed: int = 1234,
@@ -87,7 +88,12 @@ class Engine:
             # sequence-parallel MP reads only its own token shard of the batch: stage 1/world of the bytes
             ts = self.cfg.tokens // self.world
             rows = slice(self.rank * ts, (self.rank + 1) * ts)
-        pf = PinnedPrefetcher(host_batches, self.device, rows=rows)
+        sw = getattr(self.trainer, "sw", None)
+        if self.method == "mp" and self.world > 1 and rows is None and sw is not None and os.environ.get("B200_MP_SHARDED_INPUT") == "1":
+            # all-reduce form: every rank needs the whole batch - stage 1/world of it over PCIe, gather the rest over NVLink
+            pf = ShardedPrefetcher(host_batches, self.device, sw, self.rank, self.world)
+        else:
+            pf = PinnedPrefetcher(host_batches, self.device, rows=rows)
         pending = None
         host = torch.empty(2, dtype=torch.float32).pin_memory()
         slot = 0

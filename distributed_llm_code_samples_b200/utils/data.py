@@ -122,3 +122,80 @@ class PinnedPrefetcher:
         dy.record_stream(torch.cuda.current_stream(self.device))
         self._preload()
         return x, dy
+
+
+class ShardedPrefetcher:
+    """Model-parallel input staging: every rank needs the WHOLE batch, but not from its own host copy.
+
+    Each rank stages 1/world of the token rows host->device into a symmetric slot (side stream, double-buffered) and the
+    ranks exchange the rest over NVLink with the native all-gather, so the node moves ONE batch per step over PCIe
+    instead of ``world`` copies of it (8 x 512 MiB per step at the 70B shape - more than the host side sustained in
+    round 1's measurements, where MP's end-to-end rate was 15 % below its device-timed rate in both arms).
+    Every rank must iterate the same batches.  The reference copies the full batch on every rank (``train_ffns.py:294``).
+
+    NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent); opt-in with ``B200_MP_SHARDED_INPUT=1``."""
+
+    def __init__(self, batches: Iterator[Tuple[torch.Tensor, torch.Tensor]], device: torch.device, sw, rank: int, world: int):
+        from ..parallel.symm import CollChannel
+        self.it, self.device, self.sw, self.rank, self.world = iter(batches), device, sw, rank, world
+        self.stream = torch.cuda.Stream(device=device)
+        self.coll = CollChannel(sw)
+        self.stage = None
+        self.free = [None, None]         # event per slot: the gather that read it (on every peer) has completed
+        self.k = 0
+        self.last_bytes = 0
+        self._next = None
+        self._preload()
+
+    def _preload(self) -> None:
+        try:
+            x, dy = next(self.it)
+        except StopIteration:
+            self._next = None
+            return
+        if not x.is_pinned():
+            x, dy = x.pin_memory(), dy.pin_memory()
+        T = x.shape[0]
+        if T % self.world:
+            raise ValueError(f"sharded input staging needs tokens ({T}) divisible by the world size ({self.world})")
+        ts = T // self.world
+        rows = slice(self.rank * ts, (self.rank + 1) * ts)
+        nb = [ts * t[0].numel() * t.element_size() for t in (x, dy)]
+        if self.stage is None:           # collective: every rank allocates the same block at its first batch
+            self.slot_bytes = [(b + 255) // 256 * 256 for b in nb]
+            self.stage = self.sw.alloc(2 * sum(self.slot_bytes))
+        slot = self.k % 2
+        offs = [slot * sum(self.slot_bytes), slot * sum(self.slot_bytes) + self.slot_bytes[0]]
+        if self.free[slot] is not None:
+            self.stream.wait_event(self.free[slot])
+        with torch.cuda.stream(self.stream):
+            for t, off in zip((x, dy), offs):
+                self.stage.tensor(off, (ts,) + tuple(t.shape[1:]), t.dtype).copy_(t[rows], non_blocking=True)
+        self._next = (x.shape, x.dtype, dy.shape, dy.dtype, offs, nb, slot)
+        self.k += 1
+
+    def __iter__(self):
+        return self
+
+    def __next__(self):
+        from ..ops import native as nv
+        if self._next is None:
+            raise StopIteration
+        xs, xd, ds, dd, offs, nb, slot = self._next
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_stream(self.stream)
+        outs = []
+        for shape, dtype, off, b in ((xs, xd, offs[0], nb[0]), (ds, dd, offs[1], nb[1])):
+            full = torch.empty(shape, dtype=dtype, device=self.device)
+            e = self.coll.next_epoch()
+            # opening barrier: every peer's staging copy is complete; closing barrier: every peer has read my slot
+            nv._check(nv.load().b200_all_gather_into(full.data_ptr(), self.stage.peers_c, off, b, self.coll.flags.peers_c,
+                                                     self.rank, self.world, e, 0, nv._stream()), "b200_all_gather_into")
+            nv.launch_count += 1
+            outs.append(full)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.free[slot] = ev
+        self.last_bytes = sum(nb)
+        self._preload()
+        return outs[0], outs[1]

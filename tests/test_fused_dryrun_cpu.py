@@ -163,3 +163,21 @@ def test_native_collective_wrappers_are_well_formed(dry):
     assert names.count("b200_all_reduce") == 4 and names.count("b200_all_gather_into") == 2 and names.count("b200_reduce_scatter") == 2
     assert names.count("b200_barrier") == 1 and all(rc != 0 for _, rc in dry)
     assert comm.chan.epoch == 9, "every collective consumed exactly one epoch"
+
+
+def test_sharded_input_staging_is_well_formed(dry, monkeypatch):
+    """utils/data.py::ShardedPrefetcher: double-buffered staging of 1/world of the rows + two native all-gathers per batch."""
+    from distributed_llm_code_samples_b200.utils.data import ShardedPrefetcher
+    monkeypatch.setattr(torch.Tensor, "is_pinned", lambda self: True)
+    batches = [(torch.full((T, D), float(i)).to(torch.bfloat16), torch.full((T, D), -float(i)).to(torch.bfloat16)) for i in range(4)]
+    sw = _FakeWorld(1, WORLD)
+    pf = ShardedPrefetcher(iter(batches), torch.device("cpu"), sw, 1, WORLD)
+    seen = 0
+    for i, (x, dy) in enumerate(pf):
+        assert x.shape == (T, D) and dy.shape == (T, D) and pf.last_bytes == 2 * (T // WORLD) * D * 2
+        # the staging copy itself is real even here: my rows of batch i+1 are already in the other slot
+        seen += 1
+    assert seen == 4 and _names(dry).count("b200_all_gather_into") == 8
+    ts = T // WORLD
+    last = pf.stage.tensor(pf.slot_bytes[0] * 0 + (3 % 2) * sum(pf.slot_bytes), (ts, D), torch.bfloat16)
+    assert torch.equal(last, batches[3][0][ts:2 * ts]), "slot 1 holds rank 1's rows of the last batch"

@@ -44,3 +44,14 @@ except Exception as e:
     print('ddp poll=$poll FAILED', e); print(open('$O/bench_ddp_poll$poll.err').read()[-1200:])
 "
 done
+# 6. MP end to end: full-batch staging on every rank vs 1/world staged + NVLink all-gather
+for sh in 0 1; do
+  B200_MP_SHARDED_INPUT=$sh step "bench mp e2e sharded_input=$sh" 500 $TR --master-port 29524 bench.py --method mp --gpus $N --steps 4 --warmup 3 2> $O/bench_mp_e2e_sh$sh.err | grep "^{" > $O/bench_mp_e2e_sh$sh.json
+  python -c "
+import json
+try:
+    d=json.load(open('$O/bench_mp_e2e_sh$sh.json')); print('mp sharded_input=$sh device', round(d['value']), 'e2e', round(d['e2e']['value']), 'h2d/step', d['e2e']['h2d_bytes_per_step'])
+except Exception as e:
+    print('mp sharded_input=$sh FAILED', e); print(open('$O/bench_mp_e2e_sh$sh.err').read()[-1200:])
+"
+done
