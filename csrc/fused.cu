@@ -19,6 +19,10 @@
 //   MP    row-parallel GEMM + all_reduce       (:57 + :303, :68 + :309)              interleaved owners, broadcast, SUM
 //   MP-SP row-parallel GEMM + reduce_scatter   (sequence-parallel extension)         row-sharded owners, local, SUM
 //
+// Variants (template parameters of FusedEpiT, all sharing the protocol above): the number of side warps, the side
+// warps' polling back-off, and the optimizer applied in the owner's reduction (SGD from FusedParams, or Adam with the
+// owner holding the fp32 moments of its tiles - FusedAdamParams).
+//
 // Inbox slots are double-buffered by call parity so a fast rank may start the next call while a slow one is still
 // reducing; flags carry a per-channel sequence number (monotonic, never reset).  With row-sharded owners ranks rotate
 // their tile order so that at any moment they push to different owners (interleaved owners spread by construction).
