@@ -17,8 +17,12 @@
 //                exchanged; the kernel never waits for a peer to finish READING (see the reuse rules in
 //                docs/KERNELS.md section 2.5 - callers keep a barrier-ed collective between reuse of a shard buffer).
 //
+// The same kernel serves FSDP's forward parameter all-gather (train_ffns.py:203-209): there the WEIGHT is the row-sharded
+// A operand (activations are kept transposed, [features, tokens], so that every forward GEMM is W * act^T) -
+// parallel/fused_fsdp_t.py.
+//
 // STATUS: written after round 1's GPU budget was spent - compiles for sm_100a, host-side maps are tested on the CPU,
-// never run on hardware.  Opt-in (TrainConfig.mp_mode = "spf").
+// never run on hardware.  Opt-in (TrainConfig.mp_mode = "spf"; B200_FSDP_FUSED_GATHER=1).
 #include "gemm_kernel.cuh"
 #include "peer_sync.cuh"
 #include "../include/b200ffn.h"
@@ -184,8 +188,8 @@ extern "C" int b200_gather_gemm_bf16(void* const* a_peers, const void* B, long l
     if (K % BK) { set_last_error("gather_gemm: K (%d) must be a multiple of 64", K); return B200_ERR_ARG; }
     GatherParams p{};
     for (int i = 0; i < world; ++i) {
-        if (a_peers[i] == nullptr || started_peers[i] == nullptr || (reinterpret_cast<uintptr_t>(a_peers[i]) & 127)) {
-            set_last_error("gather_gemm: peer %d pointer null or not 128-byte aligned", i); return B200_ERR_ARG;
+        if (a_peers[i] == nullptr || started_peers[i] == nullptr || (reinterpret_cast<uintptr_t>(a_peers[i]) & 15)) {
+            set_last_error("gather_gemm: peer %d pointer null or not 16-byte aligned", i); return B200_ERR_ARG;
         }
         p.src[i] = reinterpret_cast<const uint4*>(a_peers[i]);
         p.started[i] = reinterpret_cast<uint32_t*>(started_peers[i]);
@@ -200,12 +204,12 @@ extern "C" int b200_gather_gemm_bf16(void* const* a_peers, const void* B, long l
     p.rank = rank; p.world = world; p.seq = seq;
     p.base.C = Cout; p.base.ldc = ldc; p.base.aux = reinterpret_cast<const __nv_bfloat16*>(aux); p.base.ldaux = ldaux;
     p.base.C2 = reinterpret_cast<__nv_bfloat16*>(out2); p.base.ldc2 = ldc2; p.base.bias = bias; p.base.alpha = alpha;
-    const bool needs_aux = epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD || epilogue == EPI_RELU_BWD_MASK;
+    const bool needs_aux = epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD || epilogue == EPI_RELU_BWD_MASK || epilogue == EPI_ADD;
     const bool needs_out2 = epilogue == EPI_GELU || epilogue == EPI_RELU_MASK;
     if (needs_aux && (aux == nullptr || (reinterpret_cast<uintptr_t>(aux) & 15))) { set_last_error("gather_gemm: epilogue %d needs a 16-byte aligned aux", epilogue); return B200_ERR_ARG; }
     if (needs_out2 && (out2 == nullptr || (reinterpret_cast<uintptr_t>(out2) & 15))) { set_last_error("gather_gemm: epilogue %d needs a 16-byte aligned out2", epilogue); return B200_ERR_ARG; }
     const long long mask_pitch = ((N + 127) / 128) * 16;             // bytes per row of a packed ReLU sign mask
-    if ((epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD) && (ldaux % 8 || ldaux < N)) { set_last_error("gather_gemm: ldaux must be >= N and a multiple of 8"); return B200_ERR_ARG; }
+    if ((epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD || epilogue == EPI_ADD) && (ldaux % 8 || ldaux < N)) { set_last_error("gather_gemm: ldaux must be >= N and a multiple of 8"); return B200_ERR_ARG; }
     if (epilogue == EPI_GELU && (ldc2 % 8 || ldc2 < N)) { set_last_error("gather_gemm: ldc2 must be >= N and a multiple of 8"); return B200_ERR_ARG; }
     if (epilogue == EPI_RELU_MASK && (ldc2 % 16 || ldc2 < mask_pitch)) { set_last_error("gather_gemm: RELU_MASK needs out2 = uint8 mask with pitch %% 16 == 0 and >= %lld bytes", mask_pitch); return B200_ERR_ARG; }
     if (epilogue == EPI_RELU_BWD_MASK && (ldaux % 16 || ldaux < mask_pitch)) { set_last_error("gather_gemm: RELU_BWD_MASK needs aux = uint8 mask with pitch %% 16 == 0 and >= %lld bytes", mask_pitch); return B200_ERR_ARG; }
@@ -222,6 +226,7 @@ extern "C" int b200_gather_gemm_bf16(void* const* a_peers, const void* B, long l
         case EPI_GELU: return launch_kind<EPI_GELU>(o, p, max_ctas, st);
         case EPI_RELU_BWD: return launch_kind<EPI_RELU_BWD>(o, p, max_ctas, st);
         case EPI_GELU_BWD: return launch_kind<EPI_GELU_BWD>(o, p, max_ctas, st);
+        case EPI_ADD: return launch_kind<EPI_ADD>(o, p, max_ctas, st);
         case EPI_RELU_MASK: return launch_kind<EPI_RELU_MASK>(o, p, max_ctas, st);
         case EPI_RELU_BWD_MASK: return launch_kind<EPI_RELU_BWD_MASK>(o, p, max_ctas, st);
         default: set_last_error("gather_gemm: unsupported epilogue %d", epilogue); return B200_ERR_ARG;

@@ -53,6 +53,10 @@ def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Seque
     if method == "fsdp":
         shards = [[fsdp_shard(p, r, n) for p in lp] for lp in layers_params]
         if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg, "fsdp"):
+            if os.environ.get("B200_FSDP_FUSED_GATHER") == "1" and cfg.tokens % 8 == 0:
+                # forward parameter all-gather inside the consuming GEMMs (not yet run on hardware)
+                from .fused_fsdp_t import FusedFSDPGatherTrainer
+                return FusedFSDPGatherTrainer(ops, comm, cfg, place(shards, device, dtype), device)
             from .fused import FusedFSDPTrainer
             return FusedFSDPTrainer(ops, comm, cfg, place(shards, device, dtype), device)
         return FSDPTrainer(ops, comm, cfg, place(shards, device, dtype))

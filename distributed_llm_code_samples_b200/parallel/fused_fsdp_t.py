@@ -1,0 +1,139 @@
+"""FSDP with the forward parameter all-gather INSIDE the GEMM that consumes the gathered weight.
+
+The all-gather + GEMM kernel (``csrc/gather_gemm.cu``) gathers a row-sharded, K-major **A** operand.  FSDP shards every
+weight along dim 0 (``train_ffns.py:265-266``), i.e. along its rows, so the weight can be that A operand if each
+forward GEMM is written as ``W @ act^T``: activations are kept TRANSPOSED, ``[features, tokens]``, for the whole step.
+
+    forward   a^T [F,T] = act(W1 [F,D] @ x^T [D,T])        W1 gathered in the kernel      (:55-56 + :203-209)
+              y^T [D,T] = W2 [D,F] @ a^T [F,T] (+ x^T)     W2 gathered in the kernel      (:57)
+    backward  dh^T [F,T] = act'(W2^T @ dy^T)                W2 from the forward / prefetch (:66-67)
+              W2 shard  -= lr * rows of (dy^T @ a)          fused reduce-scatter + SGD/Adam (:253-259)
+              dx^T [D,T] = W1^T @ dh^T (+ dy^T)                                            (:68)
+              W1 shard  -= lr * rows of (dh^T @ x)
+
+Every product is one of the operand-layout combinations the tcgen05 kernel already runs (K- or MN-major A and B).  In
+the backward pass the sharded dimension is the CONTRACTED one, so a tile needs every shard at once: there the weights
+come from the forward pass (last two layers) or from the copy-engine prefetch one layer ahead, as in
+``FusedFSDPTrainer``.  The schedule is ``fsdp_t_step`` below, written against four primitives so that it is checked on
+CPU (``tests/test_fsdp_t_schedule_cpu.py``).
+
+NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent); opt-in with ``B200_FSDP_FUSED_GATHER=1``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Tuple
+
+import torch
+
+from ..ops import native as nv
+from .fused import FOP_SGD, OWN_ROW_SHARDED, FusedFSDPTrainer, GatherChannel
+
+K_, MN_ = nv.MAJOR_K, nv.MAJOR_MN
+
+
+def fsdp_t_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+    """One optimizer step in transposed-activation space.  ``t`` provides ``L, opts`` and
+
+    * ``t.gather_w_gemm(l, k, B, N, epi, aux)``   ``epi(W[l][k] @ B)`` with ``W``'s row shards gathered in the kernel;
+      ``B`` is ``[K, N]`` (MN-major); returns ``(out [rows(W), N], out2)`` and leaves the full ``W`` for the backward pass
+    * ``t.gemm(A, a_major, B, b_major, M, N, K, epi, aux)``   a local GEMM ``epi(sum_k A(m,k) B(n,k))``
+    * ``t.update(l, k, A, B)``   ``W[l][k] shard -= lr * (rows of A @ B^T summed over ranks)``, A ``[M, T]``, B ``[N, T]``
+    * ``t.backward_weights(i)``  full ``(W1, W2)`` of layer ``i`` (forward leftovers or prefetch)
+    """
+    act, residual, L = t.opts.activation, t.opts.residual, t.L
+    T = x.shape[0]
+    xT = x.t().contiguous()                                               # [D, T]
+    saved = []
+    for l in range(L):
+        fwd = {"relu": nv.EPI_RELU_MASK if T % 128 == 0 else nv.EPI_RELU, "gelu": nv.EPI_GELU}[act]
+        aT, aux = t.gather_w_gemm(l, 0, xT, T, fwd, None)                 # [F, T]
+        if aux is None:
+            aux = aT                                                      # plain ReLU: the output itself carries the sign
+        yT, _ = t.gather_w_gemm(l, 1, aT, T, nv.EPI_ADD if residual else nv.EPI_STORE, xT if residual else None)   # [D, T]
+        saved.append((xT, aT, aux))
+        xT = yT
+    y = xT.t().contiguous()
+    dT = dloss_dx.t().contiguous()                                        # [D, T]
+    for i in reversed(range(L)):
+        W1, W2 = t.backward_weights(i)
+        xin, aT, aux = saved[i]
+        F_, D_ = W1.shape
+        bwd = (nv.EPI_RELU_BWD_MASK if aux.dtype == torch.uint8 else nv.EPI_RELU_BWD) if act == "relu" else nv.EPI_GELU_BWD
+        # dh^T[f,t] = act'( sum_d W2[d,f] dy^T[d,t] ): A = W2 read MN-major (storage [K=D, M=F]), B = dy^T MN-major ([K=D, N=T])
+        dhT = t.gemm(W2, MN_, dT, MN_, F_, T, D_, bwd, aux)
+        t.update(i, 1, dT, aT)                                            # dW2[d,f] = sum_t dy^T[d,t] a^T[f,t]
+        dn = None
+        if i > 0:
+            # dx^T[d,t] = sum_f W1[f,d] dh^T[f,t] (+ dy^T): A = W1 read MN-major ([K=F, M=D]), B = dh^T MN-major ([K=F, N=T])
+            dn = t.gemm(W1, MN_, dhT, MN_, D_, T, F_, nv.EPI_ADD if residual else nv.EPI_STORE, dT if residual else None)
+        t.update(i, 0, dhT, xin)                                          # dW1[f,d] = sum_t dh^T[f,t] x^T[d,t]
+        saved[i] = None
+        dT = dn
+    return y
+
+
+class FusedFSDPGatherTrainer(FusedFSDPTrainer):
+    """``FusedFSDPTrainer`` (fused reduce-scatter + sharded optimizer step, copy-engine prefetch in the backward pass)
+    with the forward parameter all-gather inside the consuming GEMMs."""
+
+    comm_name = ("fused: parameter all-gather inside the forward GEMMs; dW GEMM + reduce-scatter + sharded update in one kernel; "
+                 "P2P-DMA prefetch in the backward pass")
+
+    def __init__(self, ops, comm, cfg, shards, device):
+        super().__init__(ops, comm, cfg, shards, device)
+        if self.adam:
+            self.comm_name = self.comm_name.replace("sharded update", "sharded Adam")
+        self.device = device
+        self.gchan = GatherChannel(self.sw, max(cfg.model_size, cfg.ffn_dim))
+        self.sw.host_barrier()
+
+    # ---- primitives of fsdp_t_step ---------------------------------------------------------------------------
+    def _peers_of_weight(self, l: int, k: int, full: torch.Tensor):
+        """Per-rank base pointers such that ``base[q] + q * shard_bytes`` is rank q's shard: peers' point into their shard
+        storage (never dereferenced outside their own rows), mine is the full buffer the kernel completes."""
+        sh = self.shards[l][k]
+        sb = sh.numel() * 2
+        ptrs = [full.data_ptr() if q == self.rank else self.sbuf.peer_ptrs[q] + self.shard_off[l][k] - q * sb for q in range(self.world)]
+        return (C.c_void_p * self.world)(*ptrs)
+
+    def gather_w_gemm(self, l: int, k: int, B: torch.Tensor, N: int, epi: int, aux: Optional[torch.Tensor]):
+        full = self.full[l % 2][k]
+        sh = self.shards[l][k]
+        rows = sh.shape[0]
+        full[self.rank * rows:(self.rank + 1) * rows].copy_(sh)           # my rows; the kernel pulls the others
+        M, K = full.shape
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=self.device)
+        out2 = None
+        if epi == nv.EPI_RELU_MASK:
+            out2 = torch.empty(M, N // 8, dtype=torch.uint8, device=self.device)
+        elif epi == nv.EPI_GELU:
+            out2 = torch.empty_like(out)
+        self.gchan.gemm(self._peers_of_weight(l, k, full), B, MN_, out, M, N, K, epi, aux=aux, out2=out2)
+        return out, out2
+
+    def gemm(self, A, a_major, B, b_major, M, N, K, epi, aux=None):
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=self.device)
+        return nv.gemm(A, a_major, B, b_major, out, M, N, K, epi, aux=aux)
+
+    def update(self, l: int, k: int, A: torch.Tensor, B: torch.Tensor) -> None:
+        M, T = A.shape
+        N = B.shape[0]
+        out, row0 = self.local_out[2 * l + k], self.rank * (M // self.world)
+        if self.adam:
+            self.chan.gemm_adam(A, K_, B, K_, M, N, T, out, N, row0, OWN_ROW_SHARDED, False, self.state[l][k], self.lr, self.t)
+        else:
+            self.chan.gemm(A, K_, B, K_, M, N, T, out, N, row0, OWN_ROW_SHARDED, FOP_SGD, False, self.lr)
+
+    def backward_weights(self, i: int) -> List[torch.Tensor]:
+        if i >= self.L - 2:
+            params = self.full[i % 2]                                     # completed by the forward kernels of layer i
+        else:
+            params = self._finish_gather(i)
+        if i <= self.L - 2:
+            self._start_gather(i - 1)                                     # into the slot layer i+1 has just released
+        return params
+
+    def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
+        self.t += 1
+        return fsdp_t_step(self, x, dloss_dx)

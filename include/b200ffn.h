@@ -184,10 +184,11 @@ int b200_gemm_allreduce_adam_bf16(const void* A, long long lda, int a_major, con
 
 /* ---- all-gather -> GEMM in one kernel (csrc/gather_gemm.cu) -------------------------------------------------------
  * C[M,N] = epilogue(A_full[M,K] * B^T) where A is token-sharded: a_peers[q] is rank q's [M,K] bf16 buffer (K-major,
- * contiguous, 128-byte aligned, same symmetric offset everywhere) in which only rows [q*M/world, (q+1)*M/world) are
- * final when q's call starts.  The kernel pulls the other shards into a_peers[rank] (complete when it returns) while
+ * contiguous, 16-byte aligned; 128 for whole-line chunks) in which only rows [q*M/world, (q+1)*M/world) are
+ * final when q's call starts (a_peers[q] for q != rank is only ever read inside those rows, so it may be a shard's
+ * address minus q shards: that is how FSDP's row-sharded weights are gathered, parallel/fused_fsdp_t.py).  The kernel pulls the other shards into a_peers[rank] (complete when it returns) while
  * the MMAs start on the local rows.  M % (128*world) == 0, K % 64 == 0.  B / epilogue / aux / out2 / bias / alpha as
- * b200_gemm_bf16 (epilogues STORE, RELU, GELU, RELU_BWD, GELU_BWD, RELU_MASK, RELU_BWD_MASK).
+ * b200_gemm_bf16 (epilogues STORE, RELU, GELU, RELU_BWD, GELU_BWD, ADD, RELU_MASK, RELU_BWD_MASK).
  * `started_peers[q]`: symmetric array of >= `world` uint32 reserved for this stream of calls, zero-initialised;
  * `seq` starts at 1 and increases by one per call (same on every rank).  `ready`: LOCAL scratch of
  * b200_gather_gemm_ready_bytes(M) bytes, cleared by the call itself (stream-ordered).

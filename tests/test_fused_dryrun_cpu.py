@@ -88,7 +88,9 @@ def dry(monkeypatch):
 
 
 def _cfg(**kw):
-    return TrainConfig(model_size=D, ffn_dim=FF, layers=L, dtype="bf16", lr=1e-3, world_size=WORLD, **kw)
+    base = dict(model_size=D, ffn_dim=FF, layers=L, dtype="bf16", lr=1e-3, world_size=WORLD)
+    base.update(kw)
+    return TrainConfig(**base)
 
 
 def _batch():
@@ -181,3 +183,20 @@ def test_sharded_input_staging_is_well_formed(dry, monkeypatch):
     ts = T // WORLD
     last = pf.stage.tensor(pf.slot_bytes[0] * 0 + (3 % 2) * sum(pf.slot_bytes), (ts, D), torch.bfloat16)
     assert torch.equal(last, batches[3][0][ts:2 * ts]), "slot 1 holds rank 1's rows of the last batch"
+
+
+@pytest.mark.parametrize("rank", [0, 1])
+@pytest.mark.parametrize("act,residual,optimizer", [("relu", False, "sgd"), ("gelu", True, "adam")])
+def test_fused_fsdp_with_in_kernel_forward_gather_is_well_formed(dry, rank, act, residual, optimizer):
+    from distributed_llm_code_samples_b200.parallel.fused_fsdp_t import FusedFSDPGatherTrainer
+    shards = [[fsdp_shard(p, rank, WORLD) for p in l] for l in _params()]
+    cfg = _cfg(activation=act, residual=residual, optimizer=optimizer, layers=3)
+    three = shards + [[p.clone() for p in shards[0]]]
+    tr = FusedFSDPGatherTrainer(get_ops("torch", "cpu"), _Comm(rank, WORLD), cfg, three, torch.device("cpu"))
+    y = tr.step(*_batch())
+    assert y.shape == (T, D)
+    names = _names(dry)
+    assert names.count("b200_gather_gemm_bf16") == 2 * 3, "both weights of every layer are gathered inside their forward GEMM"
+    assert names.count("b200_gemm_bf16") == 3 + 2, "dh^T per layer, dx^T for all but the first layer"
+    assert names.count("b200_gemm_allreduce_adam_bf16" if optimizer == "adam" else "b200_gemm_allreduce_bf16") == 2 * 3
+    assert names.count("b200_all_gather_into_dma") == 2, "only layer 0 needs a backward prefetch when L = 3 (layers 2 and 1 are left by the forward pass)"

@@ -144,6 +144,23 @@ def test_fused_trainer_matches_nccl_trainer(method):
 
 
 @queued
+def test_fsdp_with_in_kernel_forward_gather_matches_nccl(monkeypatch):
+    """parallel/fused_fsdp_t.py: transposed activations, the weight is the gathered A operand of every forward GEMM."""
+    from distributed_llm_code_samples_b200.parallel import api
+    monkeypatch.setenv("B200_FSDP_FUSED_GATHER", "1")
+    lp, seeds = _init()
+    T = 512
+    fused = api.train_fsdp(lp, seeds, T, DM, _cfg(comm="fused"))
+    nccl = api.train_fsdp(lp, seeds, T, DM, _cfg(comm="nccl"))
+    oracle = _oracle(lp, seeds, T, "fsdp")
+    upd = lambda res: [[p.float() - q for p, q in zip(a, b)] for a, b in zip(res, lp)]
+    uf, un, uo = upd(fused), upd(nccl), upd(oracle)
+    assert all(torch.isfinite(u).all() for l in uf for u in l)
+    err_f, err_n = _rel(uf, uo), _rel(un, uo)
+    assert err_f < 0.35 and err_f <= 1.3 * err_n + 0.01, (err_f, err_n)
+
+
+@queued
 @pytest.mark.parametrize("mp_mode", ["ar", "sp", "spf"])
 def test_fused_mp_with_gelu_and_residual_matches_nccl(mp_mode, monkeypatch):
     """The north-star block (Linear -> GELU -> Linear, residual) under fused MP: the residual rides on the kernels'

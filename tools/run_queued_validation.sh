@@ -15,7 +15,7 @@ step "graph replay test" 300 python -m pytest tests/test_train_gpu.py -q -m gpu 
 step "1-GPU suite (queued on)" 900 python -m pytest tests -q -m gpu --deselect tests/test_multigpu.py > $O/suite_1gpu.log 2>&1; tail -3 $O/suite_1gpu.log
 
 # 2. multi GPU, one queued test per process so that a hang / trap is attributed
-for k in barrier_and_flag_protocol_stress unfused_trainers_on_native_collectives fused_adam_matches_unfused_adam fused_mp_with_gelu_and_residual vmm_multicast_all_reduce "fused_trainer_matches_nccl_trainer and mp_spf"; do
+for k in barrier_and_flag_protocol_stress unfused_trainers_on_native_collectives fused_adam_matches_unfused_adam fused_mp_with_gelu_and_residual vmm_multicast_all_reduce "fused_trainer_matches_nccl_trainer and mp_spf" fsdp_with_in_kernel_forward_gather; do
   tag=$(echo "$k" | tr ' ' '_')
   step "multigpu: $k" 400 python -m pytest tests/test_multigpu.py -q -m gpu -k "$k" > $O/mgpu_$tag.log 2>&1; tail -4 $O/mgpu_$tag.log
 done
@@ -53,5 +53,16 @@ try:
     d=json.load(open('$O/bench_mp_e2e_sh$sh.json')); print('mp sharded_input=$sh device', round(d['value']), 'e2e', round(d['e2e']['value']), 'h2d/step', d['e2e']['h2d_bytes_per_step'])
 except Exception as e:
     print('mp sharded_input=$sh FAILED', e); print(open('$O/bench_mp_e2e_sh$sh.err').read()[-1200:])
+"
+done
+# 7. FSDP: copy-engine prefetch (validated) vs forward all-gather inside the GEMMs
+for fg in 0 1; do
+  B200_FSDP_FUSED_GATHER=$fg step "bench fsdp fused_gather=$fg" 500 $TR --master-port 29525 bench.py --method fsdp --gpus $N --steps 4 --warmup 3 --no-e2e 2> $O/bench_fsdp_fg$fg.err | grep "^{" > $O/bench_fsdp_fg$fg.json
+  python -c "
+import json
+try:
+    d=json.load(open('$O/bench_fsdp_fg$fg.json')); print('fsdp fused_gather=$fg', round(d['value']), 'tok/s', round(d['ms_per_step'],2), 'ms/step')
+except Exception as e:
+    print('fsdp fused_gather=$fg FAILED', e); print(open('$O/bench_fsdp_fg$fg.err').read()[-1200:])
 "
 done
