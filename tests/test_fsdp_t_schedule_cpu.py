@@ -87,7 +87,7 @@ def _worker(rank, world, dev, lp, seeds, cfg_dict, out):
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("act,residual", [("relu", False), ("gelu", False), ("gelu", True), ("relu", True)])
+@pytest.mark.parametrize("act,residual", [("relu", False), ("gelu", True)])
 def test_transposed_fsdp_schedule_equals_ddp(act, residual):
     g = torch.Generator().manual_seed(17)
     lp = ffn.init_stack(L, D, FF, g)

@@ -83,8 +83,7 @@ def _worker(rank, world, dev, lp, seeds, cfg_dict, out):
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("act,recompute,residual", [("relu", False, False), ("gelu", False, False), ("relu", True, False),
-                                                    ("gelu", False, True), ("relu", True, True)])
+@pytest.mark.parametrize("act,recompute,residual", [("relu", False, False), ("gelu", False, True), ("relu", True, True)])
 def test_spf_schedule_equals_single_device(act, recompute, residual):
     g = torch.Generator().manual_seed(17)
     lp = ffn.init_stack(L, D, FF, g)
