@@ -116,6 +116,8 @@ struct FusedEpiT {
     };
 
     static __device__ __forceinline__ void before_loads(const Params&, const GemmCore&, int, int) {}
+    struct ProducerState {};
+    static __device__ __forceinline__ int kblock(const Params&, const GemmCore&, int kb, int, ProducerState&) { return kb; }
     static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx&, State& st) {
         st.k_local = 0;
         st.owner = 0;

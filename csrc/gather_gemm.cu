@@ -5,6 +5,8 @@
 //   A is [M, K] bf16, K-major, contiguous, and lives at the SAME offset of a symmetric block on every rank.  Rank q
 //   holds the final values of rows [q*M/world, (q+1)*M/world) only (its token shard).  The kernel computes
 //   C = epilogue(A_full * B^T) and, as a side effect, completes the local copy of A_full.
+//   (Second form, FSDP backward: A is MN-major, storage [K, M], sharded along K - the contracted dimension.  The side
+//   warps work exactly as below on storage rows; the producer then waits per k-block instead of per tile, see kblock.)
 //
 //   side warps   (2 per CTA, concurrently with the TMA / MMA / epilogue warps) pull the other ranks' shards over NVLink
 //                into the local buffer, 16/32 KiB chunks in the order the GEMM will need them (ring order starting at
@@ -41,9 +43,12 @@ struct GatherParams {
     long long shard_vecs;                   // 16-byte vectors per token shard
     int chunk_vecs;                         // vectors per pull chunk
     int chunks_per_block;                   // chunks per 128-row block
-    int blocks_per_shard;                   // 128-row blocks per token shard
+    int blocks_per_shard;                   // 128-row blocks per shard
     int rank, world;
     uint32_t seq;
+    int k_sharded;                          // 0: A is K-major [M, K], shards = row blocks of M (tokens / weight rows)
+                                            // 1: A is MN-major [K, M], shards = row blocks of K (FSDP backward: the contracted dim)
+    int kb_rot;                             // k_sharded: first k-block of my own shard (every tile's k-loop starts there)
 };
 
 __device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
@@ -95,7 +100,7 @@ struct GatherEpi {
 
     // TMA producer thread: the A rows of blocks [m_blk, m_blk + n) must be complete in the local buffer
     static __device__ __forceinline__ void before_loads(const Params& p, const GemmCore& g, int m_blk, int n) {
-        if (p.world == 1) return;
+        if (p.world == 1 || p.k_sharded) return;
         for (int i = 0; i < n; ++i) {
             const int b = m_blk + i;
             if (b >= g.tiles_m || b / p.blocks_per_shard == p.rank) continue;      // ragged tail / my own shard
@@ -107,6 +112,31 @@ struct GatherEpi {
             }
         }
         fence_proxy_async_global();          // the rows were written with generic stores; TMA reads them via the async proxy
+    }
+
+    // K-sharded A (storage rows = k): a tile needs every shard, in any order.  Each tile's k-loop starts at my own
+    // shard's k-range and walks the ring, the same order the side warps pull in; a block is waited for once (blocks
+    // are visited in ring order, so "complete up to ring position p" is all the producer has to remember).
+    struct ProducerState {
+        int known_upto = 0;
+    };
+    static __device__ __forceinline__ int kblock(const Params& p, const GemmCore& g, int kb, int num_kb, ProducerState& ps) {
+        if (!p.k_sharded || p.world == 1) return kb;
+        int kbe = kb + p.kb_rot;
+        if (kbe >= num_kb) kbe -= num_kb;
+        const int ring = (kb * BK) >> 7;                         // ring position of the 128-row block holding this k-block
+        if (ring >= p.blocks_per_shard && ring >= ps.known_upto) {
+            const int b = (kbe * BK) >> 7;
+            long long t0 = clock64();
+            uint32_t spins = 0;
+            while (ld_acquire_gpu(p.ready + b) < (uint32_t)p.chunks_per_block) {
+                __nanosleep(64);
+                if (((++spins) & 0xff) == 0 && (clock64() - t0) > B200_FLAG_TIMEOUT_CYCLES) device_fail(g.err, ERR_FLAG_TIMEOUT, 0xB00 + (b & 0xff));
+            }
+            fence_proxy_async_global();
+            ps.known_upto = ring + 1;
+        }
+        return kbe;
     }
 
     static __device__ __forceinline__ void side_loop(const Params& p, const GemmCore& g, int swarp, int lane, uint32_t*) {
@@ -149,6 +179,7 @@ struct GatherEpi {
 
 template <int KIND>
 static int launch_kind(const GemmOperands& o, const GatherParams& p, int max_ctas, cudaStream_t st) {
+    if (p.k_sharded) return launch_gemm<GatherEpi<KIND>>(o, p, max_ctas, st);      // any tile order: every tile needs every shard
     // walk the tiles starting at my own shard; rasterisation groups no larger than a shard keep the walk shard by shard
     const int group_m = p.blocks_per_shard < 16 ? p.blocks_per_shard : 16;
     return launch_gemm<GatherEpi<KIND>>(o, p, max_ctas, st, p.rank, p.world, false, group_m);
@@ -160,9 +191,9 @@ using namespace b200;
 
 // Pull-chunk size for a K-wide bf16 A operand: 32 KiB when a 128-row block is a whole number of them, else 16 KiB
 // (K % 64 == 0 makes a block a multiple of 16 KiB).
-static int gather_chunk_bytes(int K) { return (256ll * K) % 32768 == 0 ? 32768 : 16384; }
+static int gather_chunk_bytes(int row_len) { return (256ll * row_len) % 32768 == 0 ? 32768 : 16384; }
 
-extern "C" long long b200_gather_gemm_ready_bytes(int M) { return (long long)((M + BM - 1) / BM) * 4; }
+extern "C" long long b200_gather_gemm_ready_bytes(int rows) { return (long long)((rows + BM - 1) / BM) * 4; }
 
 // Host mirror of the pull order for CPU tests: out = {peer, first_vec, block, chunk_vecs, chunks_per_block, total_chunks}
 extern "C" int b200_debug_gather_chunk(int M, int K, int rank, int world, long long u, long long* out) {
@@ -177,15 +208,18 @@ extern "C" int b200_debug_gather_chunk(int M, int K, int rank, int world, long l
     return 0;
 }
 
-extern "C" int b200_gather_gemm_bf16(void* const* a_peers, const void* B, long long ldb, int b_major, void* Cout, long long ldc,
+extern "C" int b200_gather_gemm_bf16(void* const* a_peers, int a_major, const void* B, long long ldb, int b_major, void* Cout, long long ldc,
                                      int M, int N, int K, int epilogue, const void* aux, long long ldaux, void* out2, long long ldc2,
                                      const float* bias, float alpha, void* const* started_peers, void* ready, int rank, int world,
                                      unsigned int seq, int max_ctas, void* stream) {
     if (world < 1 || world > MAX_WORLD || rank < 0 || rank >= world) { set_last_error("gather_gemm: bad rank/world"); return B200_ERR_ARG; }
     if (a_peers == nullptr || started_peers == nullptr || ready == nullptr || Cout == nullptr) { set_last_error("gather_gemm: null argument"); return B200_ERR_ARG; }
     if (seq == 0) { set_last_error("gather_gemm: seq must start at 1"); return B200_ERR_ARG; }
-    if (M % (BM * world)) { set_last_error("gather_gemm: M (%d) must be a multiple of 128 * world (%d)", M, BM * world); return B200_ERR_ARG; }
-    if (K % BK) { set_last_error("gather_gemm: K (%d) must be a multiple of 64", K); return B200_ERR_ARG; }
+    if (a_major != MAJOR_K && a_major != MAJOR_MN) { set_last_error("gather_gemm: a_major must be 0 (K) or 1 (MN)"); return B200_ERR_ARG; }
+    // storage of A: `rows` rows of `row_len` contiguous elements, sharded by rows
+    const int rows = a_major == MAJOR_K ? M : K, row_len = a_major == MAJOR_K ? K : M;
+    if (rows % (BM * world)) { set_last_error("gather_gemm: the sharded dimension (%d) must be a multiple of 128 * world (%d)", rows, BM * world); return B200_ERR_ARG; }
+    if (row_len % BK) { set_last_error("gather_gemm: the row length of A (%d) must be a multiple of 64", row_len); return B200_ERR_ARG; }
     GatherParams p{};
     for (int i = 0; i < world; ++i) {
         if (a_peers[i] == nullptr || started_peers[i] == nullptr || (reinterpret_cast<uintptr_t>(a_peers[i]) & 15)) {
@@ -196,12 +230,14 @@ extern "C" int b200_gather_gemm_bf16(void* const* a_peers, const void* B, long l
     }
     p.dst = reinterpret_cast<uint4*>(a_peers[rank]);
     p.ready = reinterpret_cast<uint32_t*>(ready);
-    const int cb = gather_chunk_bytes(K);
-    p.shard_vecs = (long long)(M / world) * K * 2 / 16;
+    const int cb = gather_chunk_bytes(row_len);
+    p.shard_vecs = (long long)(rows / world) * row_len * 2 / 16;
     p.chunk_vecs = cb / 16;
-    p.chunks_per_block = (int)(256ll * K / cb);
-    p.blocks_per_shard = M / world / BM;
+    p.chunks_per_block = (int)(256ll * row_len / cb);
+    p.blocks_per_shard = rows / world / BM;
     p.rank = rank; p.world = world; p.seq = seq;
+    p.k_sharded = a_major == MAJOR_MN ? 1 : 0;
+    p.kb_rot = p.k_sharded ? rank * (K / BK / world) : 0;
     p.base.C = Cout; p.base.ldc = ldc; p.base.aux = reinterpret_cast<const __nv_bfloat16*>(aux); p.base.ldaux = ldaux;
     p.base.C2 = reinterpret_cast<__nv_bfloat16*>(out2); p.base.ldc2 = ldc2; p.base.bias = bias; p.base.alpha = alpha;
     const bool needs_aux = epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD || epilogue == EPI_RELU_BWD_MASK || epilogue == EPI_ADD;
@@ -215,10 +251,10 @@ extern "C" int b200_gather_gemm_bf16(void* const* a_peers, const void* B, long l
     if (epilogue == EPI_RELU_BWD_MASK && (ldaux % 16 || ldaux < mask_pitch)) { set_last_error("gather_gemm: RELU_BWD_MASK needs aux = uint8 mask with pitch %% 16 == 0 and >= %lld bytes", mask_pitch); return B200_ERR_ARG; }
     if (reinterpret_cast<uintptr_t>(Cout) & 15) { set_last_error("gather_gemm: C must be 16-byte aligned"); return B200_ERR_ARG; }
     if (ldc % 8 || ldc < N) { set_last_error("gather_gemm: ldc must be >= N and a multiple of 8"); return B200_ERR_ARG; }
-    GemmOperands o{a_peers[rank], (long long)K, MAJOR_K, B, ldb, b_major, M, N, K};
+    GemmOperands o{a_peers[rank], (long long)row_len, a_major, B, ldb, b_major, M, N, K};
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (world > 1) {
-        if (int rc = check_cuda(cudaMemsetAsync(ready, 0, (size_t)b200_gather_gemm_ready_bytes(M), st), "gather_gemm: clear ready counters")) return rc;
+        if (int rc = check_cuda(cudaMemsetAsync(ready, 0, (size_t)b200_gather_gemm_ready_bytes(rows), st), "gather_gemm: clear ready counters")) return rc;
     }
     switch (epilogue) {
         case EPI_STORE: return launch_kind<EPI_STORE>(o, p, max_ctas, st);

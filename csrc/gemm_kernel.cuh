@@ -102,6 +102,9 @@ __device__ __forceinline__ SmemView carve_smem(uint8_t* raw) {
 //   static __device__ void before_loads(const Params&, const GemmCore&, int m_blk, int n_blks)
 //        called by the TMA producer thread before it loads A rows of 128-row blocks [m_blk, m_blk + n_blks) for a
 //        tile: a policy whose A operand is still being assembled (gather_gemm.cu) waits here; empty otherwise
+//   struct ProducerState;  static __device__ int kblock(const Params&, const GemmCore&, int kb, int num_kb, ProducerState&)
+//        the k-block loaded in iteration kb of a tile's k-loop.  Identity by default; a policy whose A operand is sharded
+//        along K (gather_gemm.cu, FSDP backward) starts every tile at its own shard's k-range and waits here for the rest
 // ---------------------------------------------------------------------------------------------
 struct EpiCtx {
     int tile;        // linear tile index in the scheduler's order
@@ -153,6 +156,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // ===================== TMA producer (one thread) =====================
         int s = 0;
         uint32_t phase = 0;
+        [[maybe_unused]] typename Epi::ProducerState pst{};
         for (int it = blockIdx.x; it < num_tiles; it += gridDim.x) {
             int tile = it + g.tile_offset;
             if (tile >= num_tiles) tile -= num_tiles;
@@ -161,9 +165,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int m0 = m_blk * BM, n0 = n_blk * BN;
             Epi::before_loads(ep, g, m_blk, 1);
             for (int kb = 0; kb < num_kb; ++kb) {
+                const int kbe = Epi::kblock(ep, g, kb, num_kb, pst);     // which k-block this iteration loads (kb itself by default)
                 mbar_wait(&sm.empty[s], phase ^ 1, g.err, 0x100 + s);
                 mbar_arrive_expect_tx(&sm.full[s], STAGE_BYTES);
-                const int k0 = kb * BK;
+                const int k0 = kbe * BK;
                 if (g.a_major == MAJOR_K) {
                     tma_load_2d(sm.a(s), &tmA, &sm.full[s], k0, m0);          // box {64 k, 128 m}
                 } else {
@@ -340,6 +345,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         // ===================== TMA producer (one thread in EACH CTA) =====================
         int s = 0;
         uint32_t phase = 0;
+        [[maybe_unused]] typename Epi::ProducerState pst{};
         for (int it = pair; it < num_tiles; it += num_pairs) {
             int tile = it + g.tile_offset;
             if (tile >= num_tiles) tile -= num_tiles;
@@ -349,11 +355,12 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const int n0 = n_blk * BN + (int)rank * 128;         // my 128 rows of B
             Epi::before_loads(ep, g, pm * 4 + (int)rank * 2, 2);
             for (int kb = 0; kb < num_kb; ++kb) {
+                const int kbe = Epi::kblock(ep, g, kb, num_kb, pst);
                 mbar_wait(&empty[s], phase ^ 1, g.err, 0x100 + s);
                 // The peer's bytes may land before this arrival: the transaction count just goes negative for a
                 // moment, and the phase cannot complete until the one pending arrival (this one) has happened.
                 if (rank == 0) mbar_arrive_expect_tx(&full[s], 2 * P_STAGE_BYTES);
-                const int k0 = kb * BK;
+                const int k0 = kbe * BK;
                 uint8_t* a_dst = sA + s * P_A_STAGE_BYTES;
                 uint8_t* b_dst = sB + s * P_B_STAGE_BYTES;
                 if (g.a_major == MAJOR_K) {
@@ -552,6 +559,8 @@ struct LocalEpi {
     static constexpr int LAUNCH_BOUND_PAD = 0;
     static __device__ __forceinline__ void side_loop(const Params&, const GemmCore&, int, int, uint32_t*) {}
     static __device__ __forceinline__ void before_loads(const Params&, const GemmCore&, int, int) {}
+    struct ProducerState {};
+    static __device__ __forceinline__ int kblock(const Params&, const GemmCore&, int kb, int, ProducerState&) { return kb; }
     // a second bf16 [M,N] operand is read by these epilogues: aux, or (SGD) the weight tile itself
     static constexpr bool READS = (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD || KIND == EPI_SGD);
     struct State {};

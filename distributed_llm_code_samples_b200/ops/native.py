@@ -121,7 +121,7 @@ def _optional_declare(lib) -> None:
         "b200_gemm_allreduce_adam_bf16": ([vp, ll, i, vp, ll, i, i, i, i, pp, ll, i, pp, pp, i, i, i, i, u, i, i,
                                           vp, vp, f, f, f, f, i, f, i, vp], i),
         "b200_gather_gemm_ready_bytes": ([i], ll),
-        "b200_gather_gemm_bf16": ([pp, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp], i),
+        "b200_gather_gemm_bf16": ([pp, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp], i),
         "b200_debug_gather_chunk": ([i, i, i, i, ll, C.POINTER(ll)], i),
     }
     for name, sig in table.items():

@@ -104,13 +104,16 @@ class GatherChannel:
         self.seq = 0
 
     def gemm(self, a_peers, B: torch.Tensor, b_major: int, out: torch.Tensor, M: int, N: int, K: int, epilogue: int,
-             aux: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None, max_ctas: int = 0) -> torch.Tensor:
-        """``out = epilogue(A_full @ B^T)``; ``a_peers[q]`` = rank q's ``[M, K]`` buffer holding its token shard."""
-        assert M <= self.max_rows and B.dtype == torch.bfloat16 and B.stride(-1) == 1 and out.stride(-1) == 1
+             aux: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None, max_ctas: int = 0,
+             a_major: int = nv.MAJOR_K) -> torch.Tensor:
+        """``out = epilogue(A_full @ B^T)``; ``a_peers[q]`` = rank q's buffer holding its row shard of A: ``[M, K]`` sharded
+        along M (``a_major`` K) or ``[K, M]`` sharded along K (``a_major`` MN)."""
+        rows = M if a_major == nv.MAJOR_K else K
+        assert rows <= self.max_rows and B.dtype == torch.bfloat16 and B.stride(-1) == 1 and out.stride(-1) == 1
         self.seq += 1
         sw = self.sw
         rc = nv.load().b200_gather_gemm_bf16(
-            a_peers, B.data_ptr(), B.stride(0), b_major, out.data_ptr(), out.stride(0), M, N, K, epilogue,
+            a_peers, a_major, B.data_ptr(), B.stride(0), b_major, out.data_ptr(), out.stride(0), M, N, K, epilogue,
             nv._ptr(aux), aux.stride(0) if aux is not None else 0, nv._ptr(out2), out2.stride(0) if out2 is not None else 0,
             None, 1.0, self.started.peers_c, self.ready.data_ptr(), sw.rank, sw.world, self.seq, int(max_ctas), nv._stream())
         nv._check(rc, "b200_gather_gemm_bf16")

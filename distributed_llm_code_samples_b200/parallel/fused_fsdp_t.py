@@ -6,23 +6,24 @@ forward GEMM is written as ``W @ act^T``: activations are kept TRANSPOSED, ``[fe
 
     forward   a^T [F,T] = act(W1 [F,D] @ x^T [D,T])        W1 gathered in the kernel      (:55-56 + :203-209)
               y^T [D,T] = W2 [D,F] @ a^T [F,T] (+ x^T)     W2 gathered in the kernel      (:57)
-    backward  dh^T [F,T] = act'(W2^T @ dy^T)                W2 from the forward / prefetch (:66-67)
+    backward  dh^T [F,T] = act'(W2^T @ dy^T)                W2 gathered in the kernel      (:66-67 + :244-249)
               W2 shard  -= lr * rows of (dy^T @ a)          fused reduce-scatter + SGD/Adam (:253-259)
-              dx^T [D,T] = W1^T @ dh^T (+ dy^T)                                            (:68)
+              dx^T [D,T] = W1^T @ dh^T (+ dy^T)             W1 gathered in the kernel      (:68)
               W1 shard  -= lr * rows of (dh^T @ x)
 
 Every product is one of the operand-layout combinations the tcgen05 kernel already runs (K- or MN-major A and B).  In
-the backward pass the sharded dimension is the CONTRACTED one, so a tile needs every shard at once: there the weights
-come from the forward pass (last two layers) or from the copy-engine prefetch one layer ahead, as in
-``FusedFSDPTrainer``.  The schedule is ``fsdp_t_step`` below, written against four primitives so that it is checked on
-CPU (``tests/test_fsdp_t_schedule_cpu.py``).
+the backward pass the weight is read MN-major and its sharded dimension is the CONTRACTED one: the kernel's second form
+(K-sharded A) starts every tile's k-loop at the rank's own shard and waits per k-block for the rest.  The last two
+layers' weights are still complete from the forward pass and are used as they are (as the reference reuses the last
+layer's, ``:244``).  No copy-engine prefetch is left in this trainer.  The schedule is ``fsdp_t_step`` below, written
+against three primitives so that it is checked on CPU (``tests/test_fsdp_t_schedule_cpu.py``).
 
 NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent); opt-in with ``B200_FSDP_FUSED_GATHER=1``.
 """
 from __future__ import annotations
 
 import ctypes as C
-from typing import List, Optional, Tuple
+from typing import Optional
 
 import torch
 
@@ -37,9 +38,9 @@ def fsdp_t_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
 
     * ``t.gather_w_gemm(l, k, B, N, epi, aux)``   ``epi(W[l][k] @ B)`` with ``W``'s row shards gathered in the kernel;
       ``B`` is ``[K, N]`` (MN-major); returns ``(out [rows(W), N], out2)`` and leaves the full ``W`` for the backward pass
-    * ``t.gemm(A, a_major, B, b_major, M, N, K, epi, aux)``   a local GEMM ``epi(sum_k A(m,k) B(n,k))``
+    * ``t.bwd_w_gemm(l, k, B, N, epi, aux)``   ``epi(W[l][k]^T @ B)``: ``W`` read MN-major, sharded along the contracted
+      dimension; gathered in the kernel unless it is still complete from the forward pass; returns ``out [cols(W), N]``
     * ``t.update(l, k, A, B)``   ``W[l][k] shard -= lr * (rows of A @ B^T summed over ranks)``, A ``[M, T]``, B ``[N, T]``
-    * ``t.backward_weights(i)``  full ``(W1, W2)`` of layer ``i`` (forward leftovers or prefetch)
     """
     act, residual, L = t.opts.activation, t.opts.residual, t.L
     T = x.shape[0]
@@ -56,17 +57,15 @@ def fsdp_t_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
     y = xT.t().contiguous()
     dT = dloss_dx.t().contiguous()                                        # [D, T]
     for i in reversed(range(L)):
-        W1, W2 = t.backward_weights(i)
         xin, aT, aux = saved[i]
-        F_, D_ = W1.shape
         bwd = (nv.EPI_RELU_BWD_MASK if aux.dtype == torch.uint8 else nv.EPI_RELU_BWD) if act == "relu" else nv.EPI_GELU_BWD
         # dh^T[f,t] = act'( sum_d W2[d,f] dy^T[d,t] ): A = W2 read MN-major (storage [K=D, M=F]), B = dy^T MN-major ([K=D, N=T])
-        dhT = t.gemm(W2, MN_, dT, MN_, F_, T, D_, bwd, aux)
+        dhT = t.bwd_w_gemm(i, 1, dT, T, bwd, aux)
         t.update(i, 1, dT, aT)                                            # dW2[d,f] = sum_t dy^T[d,t] a^T[f,t]
         dn = None
         if i > 0:
             # dx^T[d,t] = sum_f W1[f,d] dh^T[f,t] (+ dy^T): A = W1 read MN-major ([K=F, M=D]), B = dh^T MN-major ([K=F, N=T])
-            dn = t.gemm(W1, MN_, dhT, MN_, D_, T, F_, nv.EPI_ADD if residual else nv.EPI_STORE, dT if residual else None)
+            dn = t.bwd_w_gemm(i, 0, dhT, T, nv.EPI_ADD if residual else nv.EPI_STORE, dT if residual else None)
         t.update(i, 0, dhT, xin)                                          # dW1[f,d] = sum_t dh^T[f,t] x^T[d,t]
         saved[i] = None
         dT = dn
@@ -74,11 +73,10 @@ def fsdp_t_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
 
 
 class FusedFSDPGatherTrainer(FusedFSDPTrainer):
-    """``FusedFSDPTrainer`` (fused reduce-scatter + sharded optimizer step, copy-engine prefetch in the backward pass)
-    with the forward parameter all-gather inside the consuming GEMMs."""
+    """``FusedFSDPTrainer``'s fused reduce-scatter + sharded optimizer step, with every parameter all-gather inside the
+    GEMM that consumes the gathered weight (forward: row-sharded A; backward: K-sharded A)."""
 
-    comm_name = ("fused: parameter all-gather inside the forward GEMMs; dW GEMM + reduce-scatter + sharded update in one kernel; "
-                 "P2P-DMA prefetch in the backward pass")
+    comm_name = "fused: parameter all-gather inside the consuming GEMMs (forward and backward); dW GEMM + reduce-scatter + sharded update in one kernel"
 
     def __init__(self, ops, comm, cfg, shards, device):
         super().__init__(ops, comm, cfg, shards, device)
@@ -112,9 +110,17 @@ class FusedFSDPGatherTrainer(FusedFSDPTrainer):
         self.gchan.gemm(self._peers_of_weight(l, k, full), B, MN_, out, M, N, K, epi, aux=aux, out2=out2)
         return out, out2
 
-    def gemm(self, A, a_major, B, b_major, M, N, K, epi, aux=None):
+    def bwd_w_gemm(self, l: int, k: int, B: torch.Tensor, N: int, epi: int, aux: Optional[torch.Tensor]):
+        full = self.full[l % 2][k]
+        Kd, M = full.shape                                                # read MN-major: storage [K, M]
         out = torch.empty(M, N, dtype=torch.bfloat16, device=self.device)
-        return nv.gemm(A, a_major, B, b_major, out, M, N, K, epi, aux=aux)
+        if l >= self.L - 2:                                               # still complete from this step's forward kernels
+            return nv.gemm(full, MN_, B, MN_, out, M, N, Kd, epi, aux=aux)
+        sh = self.shards[l][k]
+        rows = sh.shape[0]
+        full[self.rank * rows:(self.rank + 1) * rows].copy_(sh)
+        self.gchan.gemm(self._peers_of_weight(l, k, full), B, MN_, out, M, N, Kd, epi, aux=aux, a_major=MN_)
+        return out
 
     def update(self, l: int, k: int, A: torch.Tensor, B: torch.Tensor) -> None:
         M, T = A.shape
@@ -124,15 +130,6 @@ class FusedFSDPGatherTrainer(FusedFSDPTrainer):
             self.chan.gemm_adam(A, K_, B, K_, M, N, T, out, N, row0, OWN_ROW_SHARDED, False, self.state[l][k], self.lr, self.t)
         else:
             self.chan.gemm(A, K_, B, K_, M, N, T, out, N, row0, OWN_ROW_SHARDED, FOP_SGD, False, self.lr)
-
-    def backward_weights(self, i: int) -> List[torch.Tensor]:
-        if i >= self.L - 2:
-            params = self.full[i % 2]                                     # completed by the forward kernels of layer i
-        else:
-            params = self._finish_gather(i)
-        if i <= self.L - 2:
-            self._start_gather(i - 1)                                     # into the slot layer i+1 has just released
-        return params
 
     def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         self.t += 1

@@ -189,6 +189,10 @@ int b200_gemm_allreduce_adam_bf16(const void* A, long long lda, int a_major, con
  * address minus q shards: that is how FSDP's row-sharded weights are gathered, parallel/fused_fsdp_t.py).  The kernel pulls the other shards into a_peers[rank] (complete when it returns) while
  * the MMAs start on the local rows.  M % (128*world) == 0, K % 64 == 0.  B / epilogue / aux / out2 / bias / alpha as
  * b200_gemm_bf16 (epilogues STORE, RELU, GELU, RELU_BWD, GELU_BWD, ADD, RELU_MASK, RELU_BWD_MASK).
+ * a_major = 1 (MN-major) selects the second form: A is stored [K, M] and sharded along K (FSDP's backward pass, where
+ * the sharded dimension of the weight is the contracted one); K % (128*world) == 0, M % 64 == 0; every tile's k-loop then
+ * starts at the rank's own k-range and waits per k-block.  `ready` holds one counter per 128 storage rows in both forms
+ * (b200_gather_gemm_ready_bytes(M) or (K)).
  * `started_peers[q]`: symmetric array of >= `world` uint32 reserved for this stream of calls, zero-initialised;
  * `seq` starts at 1 and increases by one per call (same on every rank).  `ready`: LOCAL scratch of
  * b200_gather_gemm_ready_bytes(M) bytes, cleared by the call itself (stream-ordered).
@@ -197,7 +201,7 @@ int b200_gemm_allreduce_adam_bf16(const void* A, long long lda, int a_major, con
  * No counterpart in the reference (it all-reduces, train_ffns.py:303,:309); this is the sequence-parallel form
  * SURVEY.md 2.6 plans for C4/C5.  NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent). */
 long long b200_gather_gemm_ready_bytes(int M);
-int b200_gather_gemm_bf16(void* const* a_peers, const void* B, long long ldb, int b_major, void* C, long long ldc,
+int b200_gather_gemm_bf16(void* const* a_peers, int a_major, const void* B, long long ldb, int b_major, void* C, long long ldc,
                           int M, int N, int K, int epilogue, const void* aux, long long ldaux, void* out2, long long ldc2,
                           const float* bias, float alpha, void* const* started_peers, void* ready, int rank, int world,
                           unsigned int seq, int max_ctas, void* stream);

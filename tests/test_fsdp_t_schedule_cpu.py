@@ -59,8 +59,9 @@ class _GlooFsdpT:
         W = self._full(l, k)
         return _gemm(W, nv.MAJOR_K, B, nv.MAJOR_MN, W.shape[0], N, W.shape[1], epi, aux)
 
-    def gemm(self, A, a_major, B, b_major, M, N, K, epi, aux=None):
-        return _gemm(A, a_major, B, b_major, M, N, K, epi, aux)[0]
+    def bwd_w_gemm(self, l, k, B, N, epi, aux):
+        W = self._full(l, k)                   # storage [K, M], read MN-major
+        return _gemm(W, nv.MAJOR_MN, B, nv.MAJOR_MN, W.shape[1], N, W.shape[0], epi, aux)[0]
 
     def update(self, l, k, A, B):
         G, _ = _gemm(A, nv.MAJOR_K, B, nv.MAJOR_K, A.shape[0], B.shape[0], A.shape[1], nv.EPI_STORE)
@@ -68,9 +69,6 @@ class _GlooFsdpT:
         rows = G.shape[0] // self.world
         assert self.shards[l][k].shape == (rows, G.shape[1])
         self.shards[l][k].add_(G[self.rank * rows:(self.rank + 1) * rows], alpha=-self.lr)
-
-    def backward_weights(self, i):
-        return [self._full(i, 0), self._full(i, 1)]
 
 
 def _worker(rank, world, dev, lp, seeds, cfg_dict, out):

@@ -190,13 +190,15 @@ def test_sharded_input_staging_is_well_formed(dry, monkeypatch):
 def test_fused_fsdp_with_in_kernel_forward_gather_is_well_formed(dry, rank, act, residual, optimizer):
     from distributed_llm_code_samples_b200.parallel.fused_fsdp_t import FusedFSDPGatherTrainer
     shards = [[fsdp_shard(p, rank, WORLD) for p in l] for l in _params()]
-    cfg = _cfg(activation=act, residual=residual, optimizer=optimizer, layers=3)
-    three = shards + [[p.clone() for p in shards[0]]]
-    tr = FusedFSDPGatherTrainer(get_ops("torch", "cpu"), _Comm(rank, WORLD), cfg, three, torch.device("cpu"))
+    cfg = _cfg(activation=act, residual=residual, optimizer=optimizer, layers=4)
+    four = shards + [[p.clone() for p in l] for l in shards]
+    tr = FusedFSDPGatherTrainer(get_ops("torch", "cpu"), _Comm(rank, WORLD), cfg, four, torch.device("cpu"))
     y = tr.step(*_batch())
     assert y.shape == (T, D)
     names = _names(dry)
-    assert names.count("b200_gather_gemm_bf16") == 2 * 3, "both weights of every layer are gathered inside their forward GEMM"
-    assert names.count("b200_gemm_bf16") == 3 + 2, "dh^T per layer, dx^T for all but the first layer"
-    assert names.count("b200_gemm_allreduce_adam_bf16" if optimizer == "adam" else "b200_gemm_allreduce_bf16") == 2 * 3
-    assert names.count("b200_all_gather_into_dma") == 2, "only layer 0 needs a backward prefetch when L = 3 (layers 2 and 1 are left by the forward pass)"
+    # forward: both weights of all 4 layers; backward: layers 3 and 2 are still complete from the forward pass, layer 1
+    # gathers W2 and W1 (K-sharded form), layer 0 gathers W2 only (its input gradient is not needed, :88)
+    assert names.count("b200_gather_gemm_bf16") == 2 * 4 + 2 + 1
+    assert names.count("b200_gemm_bf16") == 2 + 2, "dh^T and dx^T of the two layers whose weights the forward pass left behind"
+    assert names.count("b200_gemm_allreduce_adam_bf16" if optimizer == "adam" else "b200_gemm_allreduce_bf16") == 2 * 4
+    assert names.count("b200_all_gather_into_dma") == 0, "no copy-engine prefetch is left"

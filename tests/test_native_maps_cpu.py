@@ -101,16 +101,20 @@ def test_gather_gemm_argument_validation_without_a_gpu(lib):
     lib.b200_last_error.restype = C.c_char_p
     pp = C.POINTER(C.c_void_p)
     vp, ll, i, f, u = C.c_void_p, C.c_longlong, C.c_int, C.c_float, C.c_uint
-    lib.b200_gather_gemm_bf16.argtypes = [pp, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp]
+    lib.b200_gather_gemm_bf16.argtypes = [pp, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp]
     two = (C.c_void_p * 2)(0x1000, 0x2000)
     args = dict(M=1024, N=256, K=64, seq=1, world=2, rank=0)
 
     def call(**kw):
         a = dict(args, **kw)
-        return lib.b200_gather_gemm_bf16(two, 0x3000, 64, 0, 0x4000, a["N"], a["M"], a["N"], a["K"], 0, None, 0, None, 0, None, 1.0,
-                                         two, 0x5000, a["rank"], a["world"], a["seq"], 0, None)
+        return lib.b200_gather_gemm_bf16(two, a.get("a_major", 0), 0x3000, 64, 0, 0x4000, a["N"], a["M"], a["N"], a["K"], 0, None, 0, None, 0,
+                                         None, 1.0, two, 0x5000, a["rank"], a["world"], a["seq"], 0, None)
     assert call(M=1000) == -1 and b"128 * world" in lib.b200_last_error()
     assert call(K=72) == -1 and b"multiple of 64" in lib.b200_last_error()
+    # K-sharded form: the sharded dimension is K, the row length is M
+    assert call(a_major=1, K=320) == -1 and b"128 * world" in lib.b200_last_error()
+    assert call(a_major=1, K=512, M=1000) == -1 and b"multiple of 64" in lib.b200_last_error()
+    assert call(a_major=2) == -1
     assert call(seq=0) == -1 and b"seq" in lib.b200_last_error()
     assert call(rank=2) == -1
 
