@@ -145,7 +145,8 @@ def test_fused_trainer_matches_nccl_trainer(method):
 
 @queued
 def test_fsdp_with_in_kernel_forward_gather_matches_nccl(monkeypatch):
-    """parallel/fused_fsdp_t.py: transposed activations, the weight is the gathered A operand of every forward GEMM."""
+    """parallel/fused_fsdp_t.py: transposed activations; the weight is the gathered A operand of every forward GEMM
+    (row-sharded form) and of the backward GEMMs of the layers the forward pass no longer holds (K-sharded form)."""
     from distributed_llm_code_samples_b200.parallel import api
     monkeypatch.setenv("B200_FSDP_FUSED_GATHER", "1")
     lp, seeds = _init()
