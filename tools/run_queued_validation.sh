@@ -8,7 +8,7 @@ mkdir -p $O
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 export B200_QUEUED_TESTS=1
 exec 3>&1                                  # step() reports on the real stdout even when the command's output is redirected
-step() { echo "== $1" >&3; shift; timeout "$@"; echo "rc=$?" >&3; }
+step() { echo "== $1" >&3; shift; timeout -k 15 "$@"; echo "rc=$?" >&3; }   # timeout signals the whole process group, ranks included
 
 # 1. single GPU: CUDA-graph replay (bitwise vs eager), then the whole 1-GPU suite with the queued tests on
 step "graph replay test" 300 python -m pytest tests/test_train_gpu.py -q -m gpu -k cuda_graph > $O/graph.log 2>&1; tail -3 $O/graph.log
