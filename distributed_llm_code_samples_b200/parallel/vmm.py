@@ -58,11 +58,17 @@ class VmmBuffer:
         for q in range(world):
             if q != rank:
                 nv._check(lib.b200_fd_send(_sock_path(tag, q).encode(), fd.value, rank), "b200_fd_send")
-        for _ in range(world - 1):
+        early_mc_fd = None             # datagrams from different senders are not ordered: rank 0's multicast fd (tag -1)
+        got = 0                        # may arrive before the last peer's block fd
+        while got < world - 1:
             src = C.c_int()
             rfd = lib.b200_fd_recv(sock, C.byref(src))
             if rfd < 0:
                 raise nv.NativeError(lib.b200_last_error().decode())
+            if src.value == -1:
+                early_mc_fd = rfd
+                continue
+            got += 1
             p, h = C.c_void_p(), C.c_ulonglong()
             nv._check(lib.b200_vmm_import(rfd, self.nbytes, C.byref(p), C.byref(h)), "b200_vmm_import")
             lib.b200_fd_close(rfd)
@@ -79,8 +85,12 @@ class VmmBuffer:
                     nv._check(lib.b200_fd_send(_sock_path(tag, q).encode(), mfd.value, -1), "b200_fd_send(mc)")
                 lib.b200_fd_close(mfd.value)
             else:
-                src = C.c_int()
-                rfd = lib.b200_fd_recv(sock, C.byref(src))
+                rfd = early_mc_fd
+                if rfd is None:
+                    src = C.c_int()
+                    rfd = lib.b200_fd_recv(sock, C.byref(src))
+                    if rfd < 0 or src.value != -1:
+                        raise nv.NativeError("expected the multicast descriptor from rank 0: " + lib.b200_last_error().decode())
                 nv._check(lib.b200_mc_import(rfd, C.byref(mc)), "b200_mc_import")
                 lib.b200_fd_close(rfd)
             nv._check(lib.b200_mc_attach(mc.value, 1, 0, 0, None), "b200_mc_attach(add device)")
