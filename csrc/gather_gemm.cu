@@ -81,6 +81,15 @@ __host__ __device__ __forceinline__ ChunkRef chunk_ref(long long u, int rank, in
     return r;
 }
 
+// K-sharded form: iteration kb of a tile's k-loop loads k-block kbe; `ring` is the position, counted from the start of
+// my own shard, of the 128-row storage block that holds it, and `block` that block's index (= the `ready` counter).
+__host__ __device__ __forceinline__ void k_walk(int kb, int kb_rot, int num_kb, int& kbe, int& ring, int& block) {
+    kbe = kb + kb_rot;
+    if (kbe >= num_kb) kbe -= num_kb;
+    ring = (kb * BK) >> 7;
+    block = (kbe * BK) >> 7;
+}
+
 template <int KIND>
 struct GatherEpi {
     using Local = LocalEpi<KIND>;
@@ -122,11 +131,9 @@ struct GatherEpi {
     };
     static __device__ __forceinline__ int kblock(const Params& p, const GemmCore& g, int kb, int num_kb, ProducerState& ps) {
         if (!p.k_sharded || p.world == 1) return kb;
-        int kbe = kb + p.kb_rot;
-        if (kbe >= num_kb) kbe -= num_kb;
-        const int ring = (kb * BK) >> 7;                         // ring position of the 128-row block holding this k-block
+        int kbe, ring, b;
+        k_walk(kb, p.kb_rot, num_kb, kbe, ring, b);
         if (ring >= p.blocks_per_shard && ring >= ps.known_upto) {
-            const int b = (kbe * BK) >> 7;
             long long t0 = clock64();
             uint32_t spins = 0;
             while (ld_acquire_gpu(p.ready + b) < (uint32_t)p.chunks_per_block) {
@@ -205,6 +212,16 @@ extern "C" int b200_debug_gather_chunk(int M, int K, int rank, int world, long l
     if (u < 0 || u >= out[5]) return 0;
     const ChunkRef c = chunk_ref(u, rank, world, shard_vecs, chunk_vecs, cpb, bps);
     out[0] = c.peer; out[1] = c.first_vec; out[2] = c.block;
+    return 0;
+}
+
+// Host mirror of the K-sharded k-loop walk: out = {kbe, ring, block, kb_rot, num_kb, blocks_per_shard}
+extern "C" int b200_debug_gather_kwalk(int K, int rank, int world, int kb, int* out) {
+    if (world < 1 || world > MAX_WORLD || K % (BM * world) || rank < 0 || rank >= world) return B200_ERR_ARG;
+    const int num_kb = K / BK, kb_rot = rank * (num_kb / world);
+    out[3] = kb_rot; out[4] = num_kb; out[5] = K / world / BM;
+    if (kb < 0 || kb >= num_kb) return 0;
+    k_walk(kb, kb_rot, num_kb, out[0], out[1], out[2]);
     return 0;
 }
 

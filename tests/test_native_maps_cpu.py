@@ -135,3 +135,37 @@ def test_fused_adam_entry_validation_without_a_gpu(lib):
     assert lib.b200_gemm_allreduce_adam_bf16(0x100, 8, 1, 0x200, 8, 1, 256, 256, 64, two, 256, 0, two, two, 4, 4, 0, 2, 0, 0, 1,
                                              0x300, 0x400, 1e-3, 0.9, 0.999, 1e-8, 1, 1.0, 0, None) == -1
     assert b"seq" in lib.b200_last_error()
+
+
+@pytest.mark.parametrize("K,M", [(1024, 64), (4096, 512), (16384, 4096)])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_gather_gemm_k_sharded_walk_follows_the_pull_order(lib, K, M, world):
+    """K-sharded form (FSDP backward): every tile's k-loop is a rotation of 0..num_kb-1 that starts at the rank's own
+    shard, visits storage blocks in ring order, and that order is the order in which the side warps complete them."""
+    lib.b200_debug_gather_kwalk.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]
+    lib.b200_debug_gather_chunk.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_longlong, C.POINTER(C.c_longlong)]
+    o = (C.c_int * 6)()
+    c = (C.c_longlong * 6)()
+    for rank in range(world):
+        assert lib.b200_debug_gather_kwalk(K, rank, world, -1, o) == 0
+        kb_rot, num_kb, bps = o[3], o[4], o[5]
+        assert num_kb == K // 64 and kb_rot == rank * num_kb // world
+        seen, block_order, last_ring = [], [], -1
+        for kb in range(num_kb):
+            lib.b200_debug_gather_kwalk(K, rank, world, kb, o)
+            kbe, ring, block = o[0], o[1], o[2]
+            seen.append(kbe)
+            assert ring in (last_ring, last_ring + 1), "ring positions never jump: one integer of producer state is enough"
+            last_ring = ring
+            assert (ring < bps) == (block // bps == rank), "ring positions below blocks_per_shard are exactly my own shard"
+            if not block_order or block_order[-1] != block:
+                block_order.append(block)
+        assert sorted(seen) == list(range(num_kb))
+        # the side warps' pull order (storage rows = K, row length = M): blocks in order of first appearance
+        lib.b200_debug_gather_chunk(K, M, rank, world, -1, c)
+        pulled = []
+        for u in range(c[5]):
+            lib.b200_debug_gather_chunk(K, M, rank, world, u, c)
+            if not pulled or pulled[-1] != c[2]:
+                pulled.append(c[2])
+        assert block_order[bps:] == pulled, "the k-loop needs remote blocks in exactly the order they are pulled"
