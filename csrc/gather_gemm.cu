@@ -215,6 +215,28 @@ extern "C" int b200_debug_gather_chunk(int M, int K, int rank, int world, long l
     return 0;
 }
 
+// Host mirror of the row-sharded form's tile walk in the CTA-pair kernel: first_row[i] / n_blk[i] of the i-th pair tile
+// (512 rows) that rank `rank` visits, with the rotation and rasterisation group launch_kind() chooses.
+extern "C" int b200_debug_gather_tile_walk(int M, int N, int rank, int world, int* first_row, int* n_blk, int capacity) {
+    if (world < 1 || world > MAX_WORLD || M % (BM * world) || rank < 0 || rank >= world) return B200_ERR_ARG;
+    GemmCore g{};
+    g.M = M; g.N = N;
+    g.tiles_m = M / BM; g.tiles_n = (N + BN - 1) / BN;
+    const int bps = M / world / BM;
+    g.group_m = bps < 16 ? bps : 16;
+    const int pair_tiles_m = (g.tiles_m + 3) >> 2, tiles = pair_tiles_m * g.tiles_n;
+    const int offset = (int)((long long)tiles * rank / world);
+    for (int i = 0; i < tiles && i < capacity; ++i) {
+        int t = i + offset;
+        if (t >= tiles) t -= tiles;
+        int pm = 0, nb = 0;
+        pair_tile_coords(g, pair_tiles_m, t, pm, nb);
+        first_row[i] = pm * 4 * BM;
+        n_blk[i] = nb;
+    }
+    return tiles;
+}
+
 // Host mirror of the K-sharded k-loop walk: out = {kbe, ring, block, kb_rot, num_kb, blocks_per_shard}
 extern "C" int b200_debug_gather_kwalk(int K, int rank, int world, int kb, int* out) {
     if (world < 1 || world > MAX_WORLD || K % (BM * world) || rank < 0 || rank >= world) return B200_ERR_ARG;

@@ -54,6 +54,19 @@ __host__ __device__ __forceinline__ void tile_coords(const GemmCore& g, int tile
     n_blk = in_group / gsize;
 }
 
+// pair-tile index -> (pair row, n block) for the CTA-pair kernel (512-row pair tiles); groups of 4 pair rows (= 16 m
+// blocks) keep ~74 live tiles near-square
+__host__ __device__ __forceinline__ void pair_tile_coords(const GemmCore& g, int pair_tiles_m, int tile, int& pm, int& n_blk) {
+    const int gm = g.group_m >> 2 > 0 ? g.group_m >> 2 : 1;
+    const int per_group = gm * g.tiles_n;
+    const int group = tile / per_group;
+    const int first = group * gm;
+    const int gsize = (pair_tiles_m - first) < gm ? (pair_tiles_m - first) : gm;
+    const int in_group = tile - group * per_group;
+    pm = first + in_group % gsize;
+    n_blk = in_group / gsize;
+}
+
 struct SmemView {
     uint8_t* a0;           // stage s of A at a0 + s * A_STAGE_BYTES
     uint8_t* b0;           // stage s of B at b0 + s * B_STAGE_BYTES
@@ -329,17 +342,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    // pair-tile index -> (pair row, n block); groups of 4 pair rows (= 16 m blocks) keep ~74 live tiles near-square
-    auto pair_coords = [&](int tile, int& pm, int& n_blk) {
-        const int gm = g.group_m >> 2 > 0 ? g.group_m >> 2 : 1;
-        const int per_group = gm * g.tiles_n;
-        const int group = tile / per_group;
-        const int first = group * gm;
-        const int gsize = min(pair_tiles_m - first, gm);
-        const int in_group = tile - group * per_group;
-        pm = first + in_group % gsize;
-        n_blk = in_group / gsize;
-    };
+    auto pair_coords = [&](int tile, int& pm, int& n_blk) { pair_tile_coords(g, pair_tiles_m, tile, pm, n_blk); };
 
     if (threadIdx.x == 0) {
         // ===================== TMA producer (one thread in EACH CTA) =====================

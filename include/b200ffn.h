@@ -208,6 +208,8 @@ int b200_gather_gemm_bf16(void* const* a_peers, int a_major, const void* B, long
 /* host mirror of the pull order (CPU tests): out = {peer, first 16-byte vector, 128-row block, vectors per chunk,
  * chunks per block, total chunks} for pull chunk `u` */
 int b200_debug_gather_chunk(int M, int K, int rank, int world, long long u, long long* out);
+/* host mirror of the row-sharded form's rotated pair-tile walk (CPU tests); returns the number of pair tiles */
+int b200_debug_gather_tile_walk(int M, int N, int rank, int world, int* first_row, int* n_blk, int capacity);
 /* host mirror of the K-sharded form's k-loop walk: out = {k-block loaded in iteration kb, ring position of its 128-row
  * storage block, that block's index, kb_rot, num_kb, blocks per shard} */
 int b200_debug_gather_kwalk(int K, int rank, int world, int kb, int* out);

@@ -169,3 +169,23 @@ def test_gather_gemm_k_sharded_walk_follows_the_pull_order(lib, K, M, world):
             if not pulled or pulled[-1] != c[2]:
                 pulled.append(c[2])
         assert block_order[bps:] == pulled, "the k-loop needs remote blocks in exactly the order they are pulled"
+
+
+@pytest.mark.parametrize("M,N", [(16384, 3584), (16384, 14336), (4096, 1024), (2048, 512)])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_gather_gemm_tile_walk_starts_in_the_own_shard(lib, M, N, world):
+    """Row-sharded form: with the rotation and rasterisation group the launcher picks, a rank visits every pair tile once,
+    its own shard's tiles first, then the shards in ring order - the order the side warps pull them in."""
+    lib.b200_debug_gather_tile_walk.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int]
+    cap = ((M // 128 + 3) // 4) * ((N + 255) // 256)
+    rows, nbs = (C.c_int * cap)(), (C.c_int * cap)()
+    shard = M // world
+    for rank in range(world):
+        tiles = lib.b200_debug_gather_tile_walk(M, N, rank, world, rows, nbs, cap)
+        assert tiles == cap
+        assert len({(rows[i], nbs[i]) for i in range(tiles)}) == tiles
+        if shard % 512:
+            continue                           # a 512-row pair tile then spans two shards: any order is correct, none is ideal
+        ring = [((rows[i] // shard) - rank) % world for i in range(tiles)]
+        assert ring == sorted(ring), "own shard first, then the ring"
+        assert ring[: (shard // 512) * ((N + 255) // 256)] == [0] * ((shard // 512) * ((N + 255) // 256))
