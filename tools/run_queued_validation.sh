@@ -14,6 +14,9 @@ step() { echo "== $1" >&3; shift; timeout -k 15 "$@"; echo "rc=$?" >&3; }   # ti
 step "graph replay test" 300 python -m pytest tests/test_train_gpu.py -q -m gpu -k cuda_graph > $O/graph.log 2>&1; tail -3 $O/graph.log
 step "1-GPU suite (queued on)" 900 python -m pytest tests -q -m gpu --deselect tests/test_multigpu.py > $O/suite_1gpu.log 2>&1; tail -3 $O/suite_1gpu.log
 
+# 2a. is NVLS there at all?  (decides whether the vmm test below can do more than the peer-table half)
+NCCL_DEBUG=INFO NCCL_DEBUG_SUBSYS=INIT,COLL step "nvls probe" 200 $TR --master-port 29526 tools/nvls_probe.py > $O/nvls_probe.log 2>&1; grep -iE "nvls|multicast|probe:" $O/nvls_probe.log | head -12
+
 # 2. multi GPU, one queued test per process so that a hang / trap is attributed
 for k in barrier_and_flag_protocol_stress unfused_trainers_on_native_collectives fused_adam_matches_unfused_adam fused_mp_with_gelu_and_residual vmm_multicast_all_reduce "fused_trainer_matches_nccl_trainer and mp_spf" fsdp_with_in_kernel_forward_gather; do
   tag=$(echo "$k" | tr ' ' '_')
