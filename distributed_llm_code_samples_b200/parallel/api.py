@@ -72,8 +72,9 @@ def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Seque
 def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
     """The peer-memory fused kernels need the native ops, bf16, >1 rank, SGD, no bias and TMA-legal shapes
     (FSDP additionally needs every row shard to be a whole number of 128-row tiles)."""
-    # Adam inside the fused kernels (DDP / FSDP) is written but has not run on hardware yet: opt-in via B200_FUSED_ADAM=1
-    opt_ok = cfg.optimizer == "sgd" or (cfg.optimizer == "adam" and method in ("ddp", "fsdp") and os.environ.get("B200_FUSED_ADAM") == "1")
+    # Adam with the fused trainers (inside the kernel for DDP / FSDP; MP: fused collectives + the native Adam kernel on the
+    # local dW) is written but has not run on hardware yet: opt-in via B200_FUSED_ADAM=1
+    opt_ok = cfg.optimizer == "sgd" or (cfg.optimizer == "adam" and os.environ.get("B200_FUSED_ADAM") == "1")
     ok = (getattr(ops, "name", "") == "native" and comm.world > 1 and cfg.dtype in ("bf16", "bfloat16")
           and opt_ok and not cfg.bias and cfg.model_size % 8 == 0 and cfg.ffn_dim % 8 == 0)
     if method == "fsdp":

@@ -21,7 +21,7 @@ import torch
 from ..config import TrainConfig
 from ..models.ffn import Params
 from ..ops import native as nv
-from .base import block_opts
+from .base import Optimizer, block_opts
 from .symm import CollChannel, SymmBuffer, SymmWorld, _Handle, get_symm_world
 
 OWN_INTERLEAVED, OWN_ROW_SHARDED = 0, 1
@@ -333,6 +333,8 @@ class FusedMPTrainer:
         # Residual: the output buffer is pre-filled with the residual and the kernel runs its in-place update mode with
         # alpha = -1 (out = out + sum over ranks), i.e. the DDP / FSDP code path of the same kernel.
         self.residual = cfg.residual
+        # dW is shard-local under MP (:311-312): SGD rides in the dW GEMM's epilogue; Adam = dW GEMM + the native Adam kernel
+        self.opt = Optimizer(ops, cfg) if cfg.optimizer == "adam" else None
         self.sp = cfg.mp_mode == "sp"
         self.spf = cfg.mp_mode == "spf"
         if self.sp:
@@ -346,6 +348,13 @@ class FusedMPTrainer:
         self.device = device
         self.T = 0
         self.chan: Optional[FusedChannel] = None
+
+    def update_local(self, W: torch.Tensor, dy: torch.Tensor, x: torch.Tensor) -> None:
+        """``W -= update(dy^T @ x)`` on this rank's shard; no communication."""
+        if self.opt is None:
+            self.ops.grad_weight_sgd_(W, dy, x, self.lr)
+        else:
+            self.opt.update(W.data_ptr(), W, self.ops.grad_weight(dy, x))
 
     def _ensure_buffers(self, T: int) -> None:
         if self.T == T:
@@ -430,7 +439,7 @@ class FusedMPTrainer:
             if a is None:
                 a, pre = ops.linear_act(xin, W1, self.opts.activation)
             dh = ops.grad_input(d, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
-            ops.grad_weight_sgd_(W2, d, a, self.lr)                       # shard-local, no communication (:311-312)
+            self.update_local(W2, d, a)                                   # shard-local, no communication (:311-312)
             dn = None
             if i > 0:
                 slot = i % 2
@@ -441,7 +450,7 @@ class FusedMPTrainer:
                 else:
                     self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
                 dn = self.dx[slot]
-            ops.grad_weight_sgd_(W1, dh, xin, self.lr)
+            self.update_local(W1, dh, xin)
             saved[i] = None
             d = dn
         return y
@@ -488,7 +497,7 @@ class FusedMPTrainer:
             if a is None:
                 a, pre = ops.linear_act(xfull, W1, self.opts.activation)
             dh = ops.grad_input(dfull, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
-            ops.grad_weight_sgd_(W2, dfull, a, self.lr)
+            self.update_local(W2, dfull, a)
             if i > 0:
                 slot = i % 2
                 if self.residual:
@@ -497,7 +506,7 @@ class FusedMPTrainer:
                 else:
                     self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.local_tab(self.dxs[slot]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
                 d_off, d_shard = self.dxs_off[slot], self.dxs[slot]
-            ops.grad_weight_sgd_(W1, dh, xfull, self.lr)
+            self.update_local(W1, dh, xfull)
             saved[i] = None
         return self._gather_tokens(self.ys_off[self.L - 1], T, D)
 
@@ -553,6 +562,8 @@ class FusedMPTrainer:
 
     def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         self._ensure_buffers(x.shape[0])
+        if self.opt is not None:
+            self.opt.begin_step()
         if self.spf:
             return spf_step(self, x, dloss_dx)
         return self._step_sp(x, dloss_dx) if self.sp else self._step_ar(x, dloss_dx)
@@ -574,7 +585,7 @@ def spf_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
     * ``t.rs_gemm(A, W, b_major, dst, res)``     ``dst[own rows] = sum_ranks A @ W^T (+ res[own rows])``
     * ``t.gather_out(buf)``                      all-gather the final output
 
-    ``t`` also provides ``shards, L, rank, world, ops, opts, lr`` and the full-size activation buffers ``X[0..L]``,
+    ``t`` also provides ``shards, L, rank, world, ops, opts, update_local`` and the full-size activation buffers ``X[0..L]``,
     ``DX[0..1]``.  Per layer, forward: [all-gather x -> x W1^T -> act] one kernel, [a W2^T -> reduce-scatter] one
     kernel; backward: [all-gather dy -> dy W2 -> act'] one kernel, dW2 / dW1 GEMM+SGD local, [dh W1 -> reduce-scatter]
     one kernel.  Same math as the reference's TP loop (``train_ffns.py:296-312``) with AR split into RS + AG.
@@ -600,10 +611,10 @@ def spf_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         else:
             a, aux = saved[i]
         dh, _ = t.ag_gemm(t.DX[cur], W2, nv.MAJOR_MN, act + "_bwd", aux)  # completes DX[cur] = the full upstream gradient
-        t.ops.grad_weight_sgd_(W2, t.DX[cur], a, t.lr)
+        t.update_local(W2, t.DX[cur], a)
         if i > 0:
             t.rs_gemm(dh, W1, nv.MAJOR_MN, t.DX[1 - cur], t.DX[cur] if t.opts.residual else None)
-        t.ops.grad_weight_sgd_(W1, dh, t.X[i], t.lr)
+        t.update_local(W1, dh, t.X[i])
         saved[i] = None
         cur = 1 - cur
     return t.gather_out(t.X[t.L])

@@ -132,10 +132,10 @@ def test_fused_fsdp_calls_are_well_formed(dry, rank, optimizer):
 
 @pytest.mark.parametrize("rank", [0, 1])
 @pytest.mark.parametrize("mp_mode", ["ar", "sp", "spf"])
-@pytest.mark.parametrize("residual,act", [(False, "relu"), (True, "gelu")])
-def test_fused_mp_calls_are_well_formed(dry, rank, mp_mode, residual, act):
+@pytest.mark.parametrize("residual,act,optimizer", [(False, "relu", "sgd"), (True, "gelu", "adam")])
+def test_fused_mp_calls_are_well_formed(dry, rank, mp_mode, residual, act, optimizer):
     shards = [[tp_shard(p, j, rank, WORLD).contiguous() for j, p in enumerate(l)] for l in _params()]
-    cfg = _cfg(mp_mode=mp_mode, residual=residual, activation=act)
+    cfg = _cfg(mp_mode=mp_mode, residual=residual, activation=act, optimizer=optimizer)
     tr = fused.FusedMPTrainer(get_ops("torch", "cpu"), _Comm(rank, WORLD), cfg, shards, torch.device("cpu"))
     y = tr.step(*_batch())
     assert y.shape == (T, D)

@@ -181,16 +181,16 @@ def test_fused_mp_with_gelu_and_residual_matches_nccl(mp_mode, monkeypatch):
 
 
 @queued
-@pytest.mark.parametrize("method", ["ddp", "fsdp"])
+@pytest.mark.parametrize("method", ["ddp", "fsdp", "mp"])
 def test_fused_adam_matches_unfused_adam(method, monkeypatch):
-    """Adam inside the fused kernel's owner reduction (moments sharded by tile owner) vs the unfused trainer (bf16
-    all-reduce / reduce-scatter, then b200_adam_bf16).  Adam's first step moves every weight by ~lr regardless of the
+    """Adam inside the fused kernel's owner reduction (moments sharded by tile owner; MP: fused collectives + the native
+    Adam kernel on the shard-local dW) vs the unfused trainer (bf16 all-reduce / reduce-scatter, then b200_adam_bf16).  Adam's first step moves every weight by ~lr regardless of the
     gradient scale, so the two must agree closely; two steps exercise the stored moments."""
     from distributed_llm_code_samples_b200.parallel import api
     monkeypatch.setenv("B200_FUSED_ADAM", "1")
     lp, _ = _init()
-    seeds = torch.arange(2 * WORLD)
-    fn = {"ddp": api.train_ddp, "fsdp": api.train_fsdp}[method]
+    seeds = torch.arange(2 if method == "mp" else 2 * WORLD)      # two optimizer steps either way (MP: every rank sees every seed)
+    fn = {"ddp": api.train_ddp, "fsdp": api.train_fsdp, "mp": api.train_tp}[method]
     fused = fn(lp, seeds, 512, DM, _cfg(comm="fused", optimizer="adam", lr=1e-3))
     unfused = fn(lp, seeds, 512, DM, _cfg(comm="nccl", optimizer="adam", lr=1e-3))
     upd = lambda res: [[p.float() - q for p, q in zip(a, b)] for a, b in zip(res, lp)]

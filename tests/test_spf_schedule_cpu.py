@@ -28,6 +28,9 @@ class _GlooSpf:
         self.X = [torch.full((T, D), nan) for _ in range(self.L + 1)]
         self.DX = [torch.full((T, D), nan) for _ in range(2)]
 
+    def update_local(self, W, dy, x):
+        self.ops.grad_weight_sgd_(W, dy, x, self.lr)
+
     def _gather_rows(self, buf):
         Ts = buf.shape[0] // self.world
         parts = [torch.empty(Ts, buf.shape[1]) for _ in range(self.world)]
