@@ -30,6 +30,8 @@ fn = {
     "sgd": None,
     "adam": None,
     "sumsq": None,
+    "coll_ar": None,
+    "coll_ag": None,
 }[case]
 if case == "fused_dw":
     # the fused GEMM + collective kernel in a world of ONE: pushes to its own inbox, side warps reduce + apply SGD
@@ -71,6 +73,16 @@ if case in ("sgd", "adam", "sumsq"):
     m, v = torch.zeros(D, F, device=dev), torch.zeros(D, F, device=dev)
     fn = {"sgd": lambda: nv.sgd_(w2, g32, 1e-6), "adam": lambda: nv.adam_(w2, g32, m, v, 1e-6, 0.9, 0.999, 1e-8, 1),
           "sumsq": lambda: nv.sumsq(w2)}[case]
+if case in ("coll_ar", "coll_ag"):
+    # the standalone collective kernels in a world of ONE (flag protocol against itself, local loads instead of peer loads):
+    # shows their instruction mix and HBM-side behaviour; NVLink-side numbers come from tools/coll_sweep.py
+    from distributed_llm_code_samples_b200.parallel.symm import SymmComm, SymmWorld
+    sw = SymmWorld(0, 1, dev)
+    comm = SymmComm(sw, staging_bytes=1 << 20)
+    buf = sw.alloc(128 << 20)
+    t = buf.tensor(0, (64 << 20,), torch.bfloat16)
+    full = torch.empty(64 << 20, dtype=torch.bfloat16, device=dev)
+    fn = (lambda: comm.all_reduce(t)) if case == "coll_ar" else (lambda: comm.all_gather_into(full, t))
 for _ in range(iters):
     fn()
 torch.cuda.synchronize()
