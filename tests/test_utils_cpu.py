@@ -27,3 +27,34 @@ def test_sampler_survives_a_box_without_nvidia_smi():
 
 def test_tokens_per_second():
     assert tokens_per_second(1000, 4, 2000.0) == 2000.0
+
+
+def test_benchmark_shapes_take_the_fused_paths_at_every_world_size():
+    """The driver runs bench.py at 1, 2, 4 and 8 GPUs: at every multi-GPU size the headline configurations must satisfy
+    the fused trainers' shape rules (so the run measures the fused kernels, not a fallback), with sane buffer sizes."""
+    import ctypes as C
+    from distributed_llm_code_samples_b200.config import TrainConfig
+    from distributed_llm_code_samples_b200.ops import native as nv
+    from distributed_llm_code_samples_b200.parallel import api
+    lib = nv.load()
+
+    class Ops:
+        name = "native"
+
+    class Comm:
+        def __init__(self, world):
+            self.rank, self.world = 0, world
+
+    shapes = {"ddp": (4096, 16384, 32), "fsdp": (4096, 16384, 32), "mp": (8192, 28672, 16)}
+    for world in (2, 4, 8):
+        for method, (d, f, l) in shapes.items():
+            cfg = TrainConfig(batch_size=8, seq_len=2048, layers=l, model_size=d, ffn_dim=f, dtype="bf16", comm="fused", impl="native")
+            assert api._fused_available(Ops(), Comm(world), cfg, method), (method, world)
+            T = cfg.tokens
+            outs = [(f, d), (d, f)] if method != "mp" else [(T, d)]
+            mode = {"ddp": 0, "fsdp": 1, "mp": 0}[method]
+            cap = max(lib.b200_fused_owned_tiles(M, N, world, mode) for M, N in outs)
+            inbox = lib.b200_fused_inbox_bytes(cap, world)
+            assert 0 < inbox <= 2 << 30, (method, world, inbox)
+            grid = 148
+            assert (cap + grid - 1) // grid <= 64, "owned tiles per CTA fit the done-counter scratch"
