@@ -18,6 +18,9 @@ from distributed_llm_code_samples_b200.ops import get_ops, native as nv
 from distributed_llm_code_samples_b200.parallel import fused, symm
 from distributed_llm_code_samples_b200.parallel.base import fsdp_shard, tp_shard
 
+# On a GPU box the "first CUDA call" would really launch kernels on CPU pointers: this harness is for GPU-less boxes only.
+pytestmark = pytest.mark.skipif(torch.cuda.is_available(), reason="dry run is meant for boxes without a GPU")
+
 D, FF, L, T, WORLD = 256, 1024, 2, 512, 2
 
 
