@@ -36,7 +36,7 @@ namespace b200 {
 constexpr int MAX_WORLD_F = 8;
 constexpr int TILE_ELEMS = BM * BN;                 // 32768 bf16 = 64 KiB per partial tile
 constexpr int EPI_THREADS = EPI_WARPS * 32;
-constexpr int MAX_OWNED_PER_CTA = 64;               // done counters live in the 256-byte epilogue scratch
+constexpr int MAX_OWNED_PER_CTA = 64;               // the poller tracks its owned tiles in a 64-bit mask
 
 enum FusedOp : int { FOP_SUM = 0, FOP_SGD = 1 };
 enum OwnerMode : int { OWN_INTERLEAVED = 0, OWN_ROW_SHARDED = 1 };
@@ -101,18 +101,33 @@ __device__ __forceinline__ uint4 pack_row8(const uint32_t* a) {
     return v;
 }
 
-// POLL = 0: side warps re-scan their owned tiles every 200 ns while nothing is ready (the validated default).
-// POLL = 1: exponential back-off 256 ns -> 4 us while nothing is ready, reset on progress (B200_FUSED_POLL=1; written
-//           after round 1's GPU budget was spent to cut the polling instructions ncu shows - not yet run on hardware).
-template <int SIDE_WARPS, int POLL = 0, int OPT = 0>
+__device__ __forceinline__ void side_group_sync(int threads) {   // the side warps only (named barrier 2)
+    asm volatile("bar.sync 2, %0;" ::"r"(threads) : "memory");
+}
+
+// SIDE_WARPS: warps that reduce owned tiles under the MMAs.  PAD: threads added to the launch bound so that a one-warp
+// barrier kernel of a concurrent stream (FSDP's copy-engine prefetch) finds registers on every SM.  ptxas budgets
+// registers for the bound rounded up to 128 threads: 320 + 64 -> 168 per thread, anything above 384 -> 128.
+// OPT: 0 = SUM / SGD from FusedParams, 1 = Adam (FusedAdamParams).
+//
+// Round-2 changes, from the ncu captures of the round-1 kernel (profiles/ncu/prof_fused_dw_world1.*: tensor pipe 86 % vs 97 %
+// for the local kernel, 2.9x the instructions):
+//   * ONE side warp polls (in arrival order, exponential back-off 0.25 -> 2 us) while the others are parked on a hardware
+//     barrier; round 1 had every side warp re-scan all of its tiles every 200 ns.
+//   * In the CTA-pair kernel the arrival flags of a tile's two halves are published together AFTER the second half has
+//     been handed back to the MMA warp: the system-scope fence (microseconds over NVLink) no longer sits between the two
+//     halves' TMEM drains, i.e. on the path that gates the next tile's first MMAs.
+//   * Completion is counted with the barrier instead of shared-memory atomics.
+template <int SIDE_WARPS, int PAD, int OPT = 0>
 struct FusedEpiT {
     using Params = std::conditional_t<OPT == 1, FusedAdamParams, FusedParams>;
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
     static constexpr int EXTRA_WARPS = SIDE_WARPS;   // side warps reduce/broadcast owned tiles under the MMAs
-    static constexpr int LAUNCH_BOUND_PAD = 32;      // a one-warp barrier kernel of another stream (FSDP prefetch) must fit beside it
+    static constexpr int LAUNCH_BOUND_PAD = PAD;
     struct State {
         int k_local;               // inbox slot of the tile being pushed
         int owner;
+        int pend_k, pend_owner;    // first half of a pair tile, pushed but not yet published (owner < 0: none)
     };
 
     static __device__ __forceinline__ void before_loads(const Params&, const GemmCore&, int, int) {}
@@ -121,6 +136,8 @@ struct FusedEpiT {
     static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx&, State& st) {
         st.k_local = 0;
         st.owner = 0;
+        st.pend_k = 0;
+        st.pend_owner = -1;
     }
 
     // ---- push this warp's 32 rows x 128 columns of the accumulator into the owner's inbox ------------------
@@ -152,82 +169,98 @@ struct FusedEpiT {
         }
     }
 
-    // ---- after the accumulator is handed back: publish the push, then reduce whatever is ready -------------
-    static __device__ __forceinline__ void after_tile(const Params& p, const GemmCore& g, const EpiCtx& ctx, State& st) {
-        epi_group_sync();                                            // all 8 warps' stores are issued
-        if (ctx.ewarp == 0 && ctx.lane == 0) {
+    // ---- after the accumulator is handed back: publish the push ---------------------------------------------
+    // Pair kernel: the first half (ctx.h == 0) only notes what it pushed; the second half publishes both, so that the
+    // group barrier and the system-scope fence come after BOTH accumulators are back with the MMA warp.
+    static __device__ __forceinline__ void publish(const Params& p, const EpiCtx& ctx, State& st, bool current) {
+        epi_group_sync();                                            // all 8 warps' stores (both halves) are issued
+        if (ctx.ewarp == 0 && ctx.lane == 0 && (current || st.pend_owner >= 0)) {
             fence_acq_rel_sys();
-            st_release_sys(p.flags[st.owner] + (size_t)st.k_local * MAX_WORLD_F + p.rank, p.seq);
+            if (st.pend_owner >= 0) st_release_sys(p.flags[st.pend_owner] + (size_t)st.pend_k * MAX_WORLD_F + p.rank, p.seq);
+            if (current) st_release_sys(p.flags[st.owner] + (size_t)st.k_local * MAX_WORLD_F + p.rank, p.seq);
         }
+        st.pend_owner = -1;
     }
-
-    // a pair kernel's CTA whose half of the 256-row tile lies beyond M: nothing to push, but keep the epilogue
-    // warps in step (the group barrier in after_tile is counted per tile) and use the time to reduce
-    static __device__ __forceinline__ void after_skipped_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {
-        epi_group_sync();
+    static __device__ __forceinline__ void after_tile(const Params& p, const GemmCore&, const EpiCtx& ctx, State& st) {
+        if (ctx.h == 0) {
+            st.pend_owner = st.owner;
+            st.pend_k = st.k_local;
+            return;
+        }
+        publish(p, ctx, st, true);
+    }
+    // a pair kernel's CTA whose 128-row half lies beyond M: nothing was pushed for it, but the epilogue warps must stay
+    // in step (one group barrier per pair tile)
+    static __device__ __forceinline__ void after_skipped_tile(const Params& p, const GemmCore&, const EpiCtx& ctx, State& st) {
+        if (ctx.h == 0) {
+            st.pend_owner = -1;
+            return;
+        }
+        publish(p, ctx, st, false);
     }
 
     static __device__ __forceinline__ void tail(const Params& p, const GemmCore& g, const EpiCtx& ctx, State&) {
         if (p.broadcast) {                                           // every tile of MY output has been delivered
             const int num_tiles = g.tiles_m * g.tiles_n;
-            for (int t = blockIdx.x + ctx.ewarp * gridDim.x; t < num_tiles; t += gridDim.x * EPI_WARPS)
+            for (int t = g.cta + ctx.ewarp * g.ncta; t < num_tiles; t += g.ncta * EPI_WARPS)
                 if (ctx.lane == 0) wait_flag_ge(p.flags[p.rank] + p.ready_base + t, p.seq, g.err, 0x700);
         }
     }
 
-    static __device__ __forceinline__ bool arrived(const Params& p, const GemmCore& g, int k_local, int lane, bool block) {
+    static __device__ __forceinline__ bool arrived(const Params& p, int k_local, int lane) {
         const uint32_t* f = p.flags[p.rank] + (size_t)k_local * MAX_WORLD_F;
         bool ok = true;
-        if (lane < p.world) {
-            if (block) wait_flag_ge(f + lane, p.seq, g.err, 0x600 + lane);
-            else ok = (int32_t)(ld_acquire_sys(f + lane) - p.seq) >= 0;
-        }
+        if (lane < p.world) ok = (int32_t)(ld_acquire_sys(f + lane) - p.seq) >= 0;
         return __all_sync(0xffffffffu, ok);
     }
 
-    // Side warps: reduce this CTA's owned tiles as their partials land - in ANY order (ranks may walk their tiles in
-    // different orders), concurrently with the TMA/MMA/epilogue warps.  Returns when all of them are done.
+    // Side warps: reduce this CTA's owned tiles (k = cta + j * ncta) as their partials land - in ANY order (ranks may walk
+    // their tiles in different orders), concurrently with the TMA/MMA/epilogue warps.  Warp 0 finds the next complete tile
+    // and announces it through `scratch[0]`; all side warps then reduce their rows of it.  Returns when all are done.
     static __device__ __forceinline__ void side_loop(const Params& p, const GemmCore& g, int swarp, int lane, uint32_t* scratch) {
-        const int n_mine = (int)blockIdx.x < p.owned_count ? (p.owned_count - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-        unsigned long long done = 0ull;
+        const int n_mine = g.cta < p.owned_count ? (p.owned_count - 1 - g.cta) / g.ncta + 1 : 0;
+        volatile uint32_t* slot = scratch;
+        unsigned long long done = 0ull;                              // (leader only)
         int remaining = n_mine;
-        long long t0 = clock64();
-        [[maybe_unused]] unsigned int backoff = 256;
-        while (remaining > 0) {
-            bool progressed = false;
-            for (int j = 0; j < n_mine; ++j) {
-                if ((done >> j) & 1ull) continue;
-                const int k = blockIdx.x + j * gridDim.x;
-                if (!arrived(p, g, k, lane, /*block=*/false)) continue;
-                reduce_rows(p, g, k, swarp, lane);
-                done |= 1ull << j;
-                --remaining;
-                progressed = true;
-                __syncwarp();                                        // every lane's result stores are issued ...
-                unsigned int prev = 0;
-                if (lane == 0) {
-                    fence_acq_rel_sys();                             // ... and ordered system-wide before I count
-                    prev = atomicAdd(&scratch[j], 1u);
+        while (true) {
+            if (swarp == 0) {
+                int found = -1;
+                if (remaining > 0) {
+                    long long t0 = clock64();
+                    unsigned int backoff = 256, misses = 0;
+                    int cand = 0;
+                    while (((done >> cand) & 1ull) != 0ull) ++cand;  // lowest tile not yet reduced: the likeliest to be complete
+                    while (found < 0) {
+                        if (arrived(p, g.cta + cand * g.ncta, lane)) { found = cand; break; }
+                        if ((++misses & 3u) == 0u) {                 // every 4th miss: any other tile (row-sharded walks differ per rank)
+                            for (int j = cand + 1; j < n_mine; ++j) {
+                                if ((done >> j) & 1ull) continue;
+                                if (arrived(p, g.cta + j * g.ncta, lane)) { found = j; break; }
+                            }
+                            if (found >= 0) break;
+                        }
+                        __nanosleep(backoff);
+                        backoff = backoff < 2048 ? backoff * 2 : 2048;
+                        if ((clock64() - t0) > B200_FLAG_TIMEOUT_CYCLES) device_fail(g.err, ERR_FLAG_TIMEOUT, 0x680);
+                    }
+                    done |= 1ull << found;
+                    --remaining;
                 }
-                prev = __shfl_sync(0xffffffffu, prev, 0);
-                if (prev == EXTRA_WARPS - 1 && p.broadcast) {        // the last side warp to finish the tile publishes it
-                    int m_blk, n_blk;
-                    owned_tile_coords(p, g, k, m_blk, n_blk);
-                    fence_acq_rel_sys();
-                    if (lane < p.world) st_release_sys(p.flags[lane] + p.ready_base + m_blk * g.tiles_n + n_blk, p.seq);
-                }
+                if (lane == 0) *slot = (uint32_t)found;
             }
-            if (!progressed) {
-                if constexpr (POLL == 0) {
-                    __nanosleep(200);
-                } else {
-                    __nanosleep(backoff);
-                    backoff = backoff < 4096 ? backoff * 2 : 4096;
+            side_group_sync(32 * EXTRA_WARPS);                       // the announcement is visible to every side warp
+            const int j = (int)*slot;
+            if (j < 0) break;
+            const int k = g.cta + j * g.ncta;
+            reduce_rows(p, g, k, swarp, lane);
+            side_group_sync(32 * EXTRA_WARPS);                       // every side warp's result stores are issued; slot reusable
+            if (swarp == 0 && p.broadcast) {                         // publish the finished tile to every rank
+                int m_blk, n_blk;
+                owned_tile_coords(p, g, k, m_blk, n_blk);
+                if (lane < p.world) {
+                    fence_acq_rel_sys();                             // ... and ordered system-wide before the flag
+                    st_release_sys(p.flags[lane] + p.ready_base + m_blk * g.tiles_n + n_blk, p.seq);
                 }
-                if ((clock64() - t0) > B200_FLAG_TIMEOUT_CYCLES) device_fail(g.err, ERR_FLAG_TIMEOUT, 0x680);
-            } else {
-                t0 = clock64();
-                if constexpr (POLL != 0) backoff = 256;
             }
         }
     }
@@ -372,87 +405,122 @@ struct AdamArgs {
     int step;
 };
 
-static int fused_entry(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
-                       int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
-                       void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
-                       int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
-                       float alpha, int max_ctas, void* stream, const AdamArgs* adam) {
-    if (world < 1 || world > MAX_WORLD_F || rank < 0 || rank >= world) { set_last_error("gemm_allreduce: bad rank/world"); return B200_ERR_ARG; }
-    if (out_peers == nullptr || inbox_peers == nullptr || flag_peers == nullptr) { set_last_error("gemm_allreduce: null peer table"); return B200_ERR_ARG; }
-    if (seq == 0) { set_last_error("gemm_allreduce: seq must start at 1"); return B200_ERR_ARG; }
-    if (ldo % 8 || ldo < N) { set_last_error("gemm_allreduce: ldo must be >= N and a multiple of 8"); return B200_ERR_ARG; }
-    GemmOperands o{A, lda, a_major, B, ldb, b_major, M, N, K};
-    const int tm = (M + BM - 1) / BM, tn = (N + BN - 1) / BN;
+// Everything one rank's call needs, shared by the real entry points and the single-launch emulation.
+struct FusedCall {
+    const void* A; long long lda; int a_major;
+    const void* B; long long ldb; int b_major;
+    int M, N, K;
+    void* const* out_peers; long long ldo; int out_row_offset;
+    void* const* inbox_peers; void* const* flag_peers;
+    int owned_cap, ready_cap, rank, world;
+    unsigned int seq;
+    int owner_mode, op, broadcast;
+    float alpha;
+    int max_ctas;
+    const AdamArgs* adam;
+};
+
+// Runtime choice of the kernel variant (b200_fused_config): side warps 2 (384 threads, 168 registers) or 4 (448 threads,
+// 128 registers); overlap -1 = decide per call, 0 = CTA-pair mainloop, 1 = double-buffered 1-CTA mainloop.
+static int g_side_warps = -1, g_overlap = -2;
+static void fused_config_defaults() {
+    if (g_side_warps < 0) {
+        const char* e = getenv("B200_FUSED_SIDE_WARPS");
+        g_side_warps = (e != nullptr && e[0] == '2') ? 2 : 4;
+    }
+    if (g_overlap == -2) {
+        const char* e = getenv("B200_FUSED_OVERLAP");
+        g_overlap = e == nullptr ? -1 : (e[0] == '1' ? 1 : (e[0] == '0' ? 0 : -1));
+    }
+}
+extern "C" int b200_fused_config(int side_warps, int overlap) {
+    fused_config_defaults();
+    if (side_warps == 2 || side_warps == 4) g_side_warps = side_warps;
+    if (overlap >= -1 && overlap <= 1) g_overlap = overlap;
+    return g_side_warps * 10 + (g_overlap + 1);
+}
+
+static int fused_build(const FusedCall& c, FusedParams* out, int* grid_out) {
+    if (c.world < 1 || c.world > MAX_WORLD_F || c.rank < 0 || c.rank >= c.world) { set_last_error("gemm_allreduce: bad rank/world"); return B200_ERR_ARG; }
+    if (c.out_peers == nullptr || c.inbox_peers == nullptr || c.flag_peers == nullptr) { set_last_error("gemm_allreduce: null peer table"); return B200_ERR_ARG; }
+    if (c.seq == 0) { set_last_error("gemm_allreduce: seq must start at 1"); return B200_ERR_ARG; }
+    if (c.ldo % 8 || c.ldo < c.N) { set_last_error("gemm_allreduce: ldo must be >= N and a multiple of 8"); return B200_ERR_ARG; }
+    const int tm = (c.M + BM - 1) / BM, tn = (c.N + BN - 1) / BN;
     FusedParams p{};
-    p.ldo = ldo; p.out_row_offset = out_row_offset; p.rank = rank; p.world = world; p.seq = seq; p.parity = (int)(seq & 1u);
-    p.owner_mode = owner_mode; p.op = op; p.broadcast = broadcast; p.alpha = alpha; p.owned_cap = owned_cap;
-    if (owner_mode == OWN_ROW_SHARDED) {
-        if (tm % world || (M % (BM * world))) { set_last_error("gemm_allreduce: row-sharded owners need M %% (128*world) == 0 (M=%d world=%d)", M, world); return B200_ERR_ARG; }
-        p.mpo = tm / world;
+    p.ldo = c.ldo; p.out_row_offset = c.out_row_offset; p.rank = c.rank; p.world = c.world; p.seq = c.seq; p.parity = (int)(c.seq & 1u);
+    p.owner_mode = c.owner_mode; p.op = c.op; p.broadcast = c.broadcast; p.alpha = c.alpha; p.owned_cap = c.owned_cap;
+    if (c.owner_mode == OWN_ROW_SHARDED) {
+        if (tm % c.world || (c.M % (BM * c.world))) { set_last_error("gemm_allreduce: row-sharded owners need M %% (128*world) == 0 (M=%d world=%d)", c.M, c.world); return B200_ERR_ARG; }
+        p.mpo = tm / c.world;
         p.owned_count = p.mpo * tn;
     } else {
         p.mpo = 1;
         const int total = tm * tn;
-        p.owned_count = total / world + (rank < total % world ? 1 : 0);
+        p.owned_count = total / c.world + (c.rank < total % c.world ? 1 : 0);
     }
-    if (p.owned_count > owned_cap || b200_fused_owned_tiles(M, N, world, owner_mode) > owned_cap) { set_last_error("gemm_allreduce: inbox too small (%d owned tiles, capacity %d)", p.owned_count, owned_cap); return B200_ERR_ARG; }
-    if (broadcast && tm * tn > ready_cap) { set_last_error("gemm_allreduce: ready-flag capacity %d < %d tiles", ready_cap, tm * tn); return B200_ERR_ARG; }
-    p.ready_base = owned_cap * MAX_WORLD_F;
-    for (int i = 0; i < world; ++i) {
-        p.inbox[i] = inbox_peers[i];
-        p.flags[i] = reinterpret_cast<uint32_t*>(flag_peers[i]);
-        p.out[i] = (broadcast || i == rank) ? out_peers[i] : nullptr;
-        if (p.inbox[i] == nullptr || p.flags[i] == nullptr || ((broadcast || i == rank) && p.out[i] == nullptr)) { set_last_error("gemm_allreduce: null peer pointer for rank %d", i); return B200_ERR_ARG; }
-        if ((reinterpret_cast<uintptr_t>(p.inbox[i]) & 15) || ((broadcast || i == rank) && (reinterpret_cast<uintptr_t>(p.out[i]) & 15))) { set_last_error("gemm_allreduce: peer pointers must be 16-byte aligned"); return B200_ERR_ARG; }
+    if (p.owned_count > c.owned_cap || b200_fused_owned_tiles(c.M, c.N, c.world, c.owner_mode) > c.owned_cap) { set_last_error("gemm_allreduce: inbox too small (%d owned tiles, capacity %d)", p.owned_count, c.owned_cap); return B200_ERR_ARG; }
+    if (c.broadcast && tm * tn > c.ready_cap) { set_last_error("gemm_allreduce: ready-flag capacity %d < %d tiles", c.ready_cap, tm * tn); return B200_ERR_ARG; }
+    p.ready_base = c.owned_cap * MAX_WORLD_F;
+    for (int i = 0; i < c.world; ++i) {
+        p.inbox[i] = c.inbox_peers[i];
+        p.flags[i] = reinterpret_cast<uint32_t*>(c.flag_peers[i]);
+        p.out[i] = (c.broadcast || i == c.rank) ? c.out_peers[i] : nullptr;
+        if (p.inbox[i] == nullptr || p.flags[i] == nullptr || ((c.broadcast || i == c.rank) && p.out[i] == nullptr)) { set_last_error("gemm_allreduce: null peer pointer for rank %d", i); return B200_ERR_ARG; }
+        if ((reinterpret_cast<uintptr_t>(p.inbox[i]) & 15) || ((c.broadcast || i == c.rank) && (reinterpret_cast<uintptr_t>(p.out[i]) & 15))) { set_last_error("gemm_allreduce: peer pointers must be 16-byte aligned"); return B200_ERR_ARG; }
     }
-    int grid_cap = max_ctas > 0 ? max_ctas : num_sms();
+    // every rank must use the same grid: owned tile k is reduced by CTA k %% grid on its owner
+    int grid_cap = c.max_ctas > 0 ? c.max_ctas : num_sms();
     int grid = tm * tn < grid_cap ? tm * tn : grid_cap;
     if ((p.owned_count + grid - 1) / grid > MAX_OWNED_PER_CTA) { set_last_error("gemm_allreduce: too many owned tiles per CTA"); return B200_ERR_ARG; }
-    // every rank must use the same grid: owned tile k is reduced by CTA k %% grid on its owner
+    *out = p;
+    *grid_out = grid;
+    return 0;
+}
+
+static int fused_build_adam(const FusedCall& c, const FusedParams& p, FusedAdamParams* ap) {
+    const AdamArgs* adam = c.adam;
+    if (adam->m == nullptr || adam->v == nullptr || adam->step < 1 || (reinterpret_cast<uintptr_t>(adam->m) & 15) || (reinterpret_cast<uintptr_t>(adam->v) & 15)) {
+        set_last_error("gemm_allreduce_adam: moments must be 16-byte aligned device pointers and step >= 1"); return B200_ERR_ARG;
+    }
+    static_cast<FusedParams&>(*ap) = p;
+    ap->op = FOP_SGD;                      // (unused by the Adam instantiation; keeps the weight-tile load path identical)
+    ap->adam_m = adam->m; ap->adam_v = adam->v;
+    ap->lr = adam->lr; ap->beta1 = adam->beta1; ap->beta2 = adam->beta2; ap->eps = adam->eps; ap->gscale = adam->gscale;
+    ap->bc1 = 1.0f - powf(adam->beta1, (float)adam->step);
+    ap->bc2 = 1.0f - powf(adam->beta2, (float)adam->step);
+    return 0;
+}
+
+// Link-bound calls (NVLink time comparable to the MMA time, e.g. the MP all-reduce at 8 ranks) see bursts of store
+// back-pressure in the epilogue; the kernel with two accumulator stages absorbs them under the next tile's MMAs,
+// while compute-bound calls (the dW GEMMs) are faster on the 256x256-per-CTA pair kernel.
+static bool fused_pick_overlap(const FusedCall& c) {
+    fused_config_defaults();
+    if (g_overlap >= 0) return g_overlap == 1;
+    if (c.world <= 1) return false;
+    const double bytes = (c.broadcast ? 2.0 : 1.0) * (c.world - 1) / c.world * (double)c.M * c.N * 2.0;
+    const double link_ms = bytes / 770e9 * 1e3, mma_ms = 2.0 * c.M * c.N * (double)c.K / 1.4e15 * 1e3;
+    return link_ms > 0.6 * mma_ms;
+}
+
+static int fused_entry(const FusedCall& c, void* stream) {
+    FusedParams p{};
+    int grid = 0;
+    if (int rc = fused_build(c, &p, &grid)) return rc;
+    GemmOperands o{c.A, c.lda, c.a_major, c.B, c.ldb, c.b_major, c.M, c.N, c.K};
     // Interleaved owners already spread consecutive tiles over ranks; row-sharded owners would make every rank push to
     // the same owner at once, so there each rank starts its walk at a different offset.
-    const int rot = owner_mode == OWN_ROW_SHARDED ? rank : 0;
-    static int side = -1;                       // B200_FUSED_SIDE_WARPS=2|4 (default 4): warps that reduce under the MMAs
-    if (side < 0) {
-        const char* e = getenv("B200_FUSED_SIDE_WARPS");
-        side = (e != nullptr && e[0] == '2') ? 2 : 4;
-    }
-    // Link-bound calls (NVLink time comparable to the MMA time, e.g. the MP all-reduce at 8 ranks) see bursts of store
-    // back-pressure in the epilogue; the kernel with two accumulator stages absorbs them under the next tile's MMAs,
-    // while compute-bound calls (the dW GEMMs) are faster on the 256x256-per-CTA pair kernel.
-    static int overlap_mode = -1;               // B200_FUSED_OVERLAP=0|1 forces; default: decide per call
-    if (overlap_mode < 0) {
-        const char* e = getenv("B200_FUSED_OVERLAP");
-        overlap_mode = e == nullptr ? 2 : (e[0] == '1' ? 1 : (e[0] == '0' ? 0 : 2));
-    }
-    bool overlap = overlap_mode == 1;
-    if (overlap_mode == 2 && world > 1) {
-        const double bytes = (broadcast ? 2.0 : 1.0) * (world - 1) / world * (double)M * N * 2.0;
-        const double link_ms = bytes / 770e9 * 1e3, mma_ms = 2.0 * M * N * (double)K / 1.4e15 * 1e3;
-        overlap = link_ms > 0.6 * mma_ms;
-    }
+    const int rot = c.owner_mode == OWN_ROW_SHARDED ? c.rank : 0;
+    const bool overlap = fused_pick_overlap(c);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (adam != nullptr) {
-        if (adam->m == nullptr || adam->v == nullptr || adam->step < 1 || (reinterpret_cast<uintptr_t>(adam->m) & 15) || (reinterpret_cast<uintptr_t>(adam->v) & 15)) {
-            set_last_error("gemm_allreduce_adam: moments must be 16-byte aligned device pointers and step >= 1"); return B200_ERR_ARG;
-        }
+    if (c.adam != nullptr) {
         FusedAdamParams ap{};
-        static_cast<FusedParams&>(ap) = p;
-        ap.op = FOP_SGD;                      // (unused by the Adam instantiation; keeps the weight-tile load path identical)
-        ap.adam_m = adam->m; ap.adam_v = adam->v;
-        ap.lr = adam->lr; ap.beta1 = adam->beta1; ap.beta2 = adam->beta2; ap.eps = adam->eps; ap.gscale = adam->gscale;
-        ap.bc1 = 1.0f - powf(adam->beta1, (float)adam->step);
-        ap.bc2 = 1.0f - powf(adam->beta2, (float)adam->step);
-        return launch_gemm<FusedEpiT<4, 0, 1>>(o, ap, max_ctas, st, rot, world, overlap);
+        if (int rc = fused_build_adam(c, p, &ap)) return rc;
+        if (g_side_warps == 2) return launch_gemm<FusedEpiT<2, 0, 1>>(o, ap, c.max_ctas, st, rot, c.world, overlap);
+        return launch_gemm<FusedEpiT<4, 32, 1>>(o, ap, c.max_ctas, st, rot, c.world, overlap);
     }
-    static int poll = -1;                       // B200_FUSED_POLL=1: exponential back-off in the side warps (unvalidated)
-    if (poll < 0) {
-        const char* e = getenv("B200_FUSED_POLL");
-        poll = (e != nullptr && e[0] == '1') ? 1 : 0;
-    }
-    if (poll == 1 && side == 4) return launch_gemm<FusedEpiT<4, 1>>(o, p, max_ctas, st, rot, world, overlap);
-    if (side == 2) return launch_gemm<FusedEpiT<2>>(o, p, max_ctas, st, rot, world, overlap);
-    return launch_gemm<FusedEpiT<4>>(o, p, max_ctas, st, rot, world, overlap);
+    if (g_side_warps == 2) return launch_gemm<FusedEpiT<2, 0>>(o, p, c.max_ctas, st, rot, c.world, overlap);
+    return launch_gemm<FusedEpiT<4, 32>>(o, p, c.max_ctas, st, rot, c.world, overlap);
 }
 
 extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
@@ -460,8 +528,9 @@ extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_majo
                                         void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
                                         int rank, int world, unsigned int seq, int owner_mode, int op, int broadcast,
                                         float alpha, int max_ctas, void* stream) {
-    return fused_entry(A, lda, a_major, B, ldb, b_major, M, N, K, out_peers, ldo, out_row_offset, inbox_peers, flag_peers, owned_cap,
-                       ready_cap, rank, world, seq, owner_mode, op, broadcast, alpha, max_ctas, stream, nullptr);
+    FusedCall c{A, lda, a_major, B, ldb, b_major, M, N, K, out_peers, ldo, out_row_offset, inbox_peers, flag_peers, owned_cap, ready_cap,
+                rank, world, seq, owner_mode, op, broadcast, alpha, max_ctas, nullptr};
+    return fused_entry(c, stream);
 }
 
 // Same kernel with the Adam update in the owner's reduction: out = W - lr * mhat / (sqrt(vhat) + eps) with the gradient
@@ -475,6 +544,54 @@ extern "C" int b200_gemm_allreduce_adam_bf16(const void* A, long long lda, int a
                                              float* adam_m, float* adam_v, float lr, float beta1, float beta2, float eps, int step,
                                              float grad_scale, int max_ctas, void* stream) {
     AdamArgs a{adam_m, adam_v, lr, beta1, beta2, eps, grad_scale, step};
-    return fused_entry(A, lda, a_major, B, ldb, b_major, M, N, K, out_peers, ldo, out_row_offset, inbox_peers, flag_peers, owned_cap,
-                       ready_cap, rank, world, seq, owner_mode, FOP_SGD, broadcast, 1.0f, max_ctas, stream, &a);
+    FusedCall c{A, lda, a_major, B, ldb, b_major, M, N, K, out_peers, ldo, out_row_offset, inbox_peers, flag_peers, owned_cap, ready_cap,
+                rank, world, seq, owner_mode, FOP_SGD, broadcast, 1.0f, max_ctas, &a};
+    return fused_entry(c, stream);
+}
+
+// ---- single-launch emulation of `world` ranks on ONE GPU (tests, ncu) ------------------------------------------------
+// Every rank's call is built exactly as above (its own operands, owner maps, tile rotation); the `world` kernels then run
+// as slices of one cooperative grid (gemm_tcgen05_emu_kernel).  Per-rank inputs are arrays of `world` entries; the peer
+// tables are the same for every rank, as in a real run.  `table` = device scratch of b200_emu_table_bytes() bytes.
+extern "C" long long b200_emu_table_bytes(void) { return EMU_TABLE_BYTES; }
+
+extern "C" int b200_emu_gemm_allreduce_bf16(int world, const void* const* A, long long lda, int a_major, const void* const* B, long long ldb,
+                                            int b_major, int M, int N, int K, void* const* out_peers, long long ldo,
+                                            void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
+                                            unsigned int seq, int owner_mode, int op, int broadcast, float alpha,
+                                            float* const* adam_m, float* const* adam_v, float lr, float beta1, float beta2, float eps,
+                                            int step, float grad_scale, int ctas_per_rank, void* table, void* stream) {
+    if (world < 1 || world > MAX_WORLD_F || A == nullptr || B == nullptr || table == nullptr) { set_last_error("emu_gemm_allreduce: bad arguments"); return B200_ERR_ARG; }
+    if (ctas_per_rank < 2 || (ctas_per_rank & 1) || world * ctas_per_rank > num_sms()) { set_last_error("emu_gemm_allreduce: ctas_per_rank must be even and world * ctas_per_rank <= %d", num_sms()); return B200_ERR_ARG; }
+    fused_config_defaults();
+    const bool adam = adam_m != nullptr;
+    GemmOperands ops[MAX_WORLD_F];
+    FusedParams ps[MAX_WORLD_F];
+    FusedAdamParams aps[MAX_WORLD_F];
+    AdamArgs aa[MAX_WORLD_F];
+    int rots[MAX_WORLD_F];
+    bool overlap = false;
+    for (int r = 0; r < world; ++r) {
+        const int row0 = (owner_mode == OWN_ROW_SHARDED && !broadcast) ? r * (M / world) : 0;
+        aa[r] = AdamArgs{adam ? adam_m[r] : nullptr, adam ? adam_v[r] : nullptr, lr, beta1, beta2, eps, grad_scale, step};
+        FusedCall c{A[r], lda, a_major, B[r], ldb, b_major, M, N, K, out_peers, ldo, row0, inbox_peers, flag_peers, owned_cap, ready_cap,
+                    r, world, seq, owner_mode, op, broadcast, alpha, ctas_per_rank, adam ? &aa[r] : nullptr};
+        int grid = 0;
+        if (int rc = fused_build(c, &ps[r], &grid)) return rc;
+        if (!broadcast) {                   // a rank only ever dereferences its own output pointer; the table holds every rank's
+            for (int i = 0; i < world; ++i) ps[r].out[i] = i == r ? out_peers[i] : nullptr;
+        }
+        if (adam) { if (int rc = fused_build_adam(c, ps[r], &aps[r])) return rc; }
+        ops[r] = GemmOperands{A[r], lda, a_major, B[r], ldb, b_major, M, N, K};
+        rots[r] = owner_mode == OWN_ROW_SHARDED ? r : 0;
+        overlap = fused_pick_overlap(c);
+    }
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const bool pair = use_pair_kernel() && !overlap;
+    if (adam) {
+        if (g_side_warps == 2) return launch_gemm_emu<FusedEpiT<2, 0, 1>>(world, ops, aps, rots, ctas_per_rank, pair, 0, table, st);
+        return launch_gemm_emu<FusedEpiT<4, 32, 1>>(world, ops, aps, rots, ctas_per_rank, pair, 0, table, st);
+    }
+    if (g_side_warps == 2) return launch_gemm_emu<FusedEpiT<2, 0>>(world, ops, ps, rots, ctas_per_rank, pair, 0, table, st);
+    return launch_gemm_emu<FusedEpiT<4, 32>>(world, ops, ps, rots, ctas_per_rank, pair, 0, table, st);
 }

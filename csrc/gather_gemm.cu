@@ -148,14 +148,14 @@ struct GatherEpi {
 
     static __device__ __forceinline__ void side_loop(const Params& p, const GemmCore& g, int swarp, int lane, uint32_t*) {
         if (p.world == 1) return;
-        if (blockIdx.x == 0 && swarp == 0 && lane < p.world && lane != p.rank) {
+        if (g.cta == 0 && swarp == 0 && lane < p.world && lane != p.rank) {
             fence_acq_rel_sys();
             st_release_sys(p.started[lane] + p.rank, p.seq);     // "my shard is final" (this kernel is stream-ordered after its producer)
         }
         const long long total = (p.shard_vecs / p.chunk_vecs) * (p.world - 1);
-        const long long W = (long long)gridDim.x * EXTRA_WARPS;
+        const long long W = (long long)g.ncta * EXTRA_WARPS;
         uint32_t seen = 0;
-        for (long long u = (long long)swarp * gridDim.x + blockIdx.x; u < total; u += W) {
+        for (long long u = (long long)swarp * g.ncta + g.cta; u < total; u += W) {
             const ChunkRef c = chunk_ref(u, p.rank, p.world, p.shard_vecs, p.chunk_vecs, p.chunks_per_block, p.blocks_per_shard);
             if (!((seen >> c.peer) & 1u)) {
                 if (lane == 0) wait_flag_ge(p.started[p.rank] + c.peer, p.seq, g.err, 0x900 + c.peer);
@@ -247,50 +247,73 @@ extern "C" int b200_debug_gather_kwalk(int K, int rank, int world, int kb, int* 
     return 0;
 }
 
-extern "C" int b200_gather_gemm_bf16(void* const* a_peers, int a_major, const void* B, long long ldb, int b_major, void* Cout, long long ldc,
-                                     int M, int N, int K, int epilogue, const void* aux, long long ldaux, void* out2, long long ldc2,
-                                     const float* bias, float alpha, void* const* started_peers, void* ready, int rank, int world,
-                                     unsigned int seq, int max_ctas, void* stream) {
+struct GatherCall {
+    void* const* a_peers; int a_major;
+    const void* B; long long ldb; int b_major;
+    void* Cout; long long ldc;
+    int M, N, K, epilogue;
+    const void* aux; long long ldaux; void* out2; long long ldc2;
+    const float* bias; float alpha;
+    void* const* started_peers; void* ready;
+    int rank, world;
+    unsigned int seq;
+};
+
+static int gather_build(const GatherCall& c, GatherParams* out, GemmOperands* o) {
+    const int world = c.world, rank = c.rank, M = c.M, N = c.N, K = c.K, epilogue = c.epilogue;
     if (world < 1 || world > MAX_WORLD || rank < 0 || rank >= world) { set_last_error("gather_gemm: bad rank/world"); return B200_ERR_ARG; }
-    if (a_peers == nullptr || started_peers == nullptr || ready == nullptr || Cout == nullptr) { set_last_error("gather_gemm: null argument"); return B200_ERR_ARG; }
-    if (seq == 0) { set_last_error("gather_gemm: seq must start at 1"); return B200_ERR_ARG; }
-    if (a_major != MAJOR_K && a_major != MAJOR_MN) { set_last_error("gather_gemm: a_major must be 0 (K) or 1 (MN)"); return B200_ERR_ARG; }
+    if (c.a_peers == nullptr || c.started_peers == nullptr || c.ready == nullptr || c.Cout == nullptr) { set_last_error("gather_gemm: null argument"); return B200_ERR_ARG; }
+    if (c.seq == 0) { set_last_error("gather_gemm: seq must start at 1"); return B200_ERR_ARG; }
+    if (c.a_major != MAJOR_K && c.a_major != MAJOR_MN) { set_last_error("gather_gemm: a_major must be 0 (K) or 1 (MN)"); return B200_ERR_ARG; }
     // storage of A: `rows` rows of `row_len` contiguous elements, sharded by rows
-    const int rows = a_major == MAJOR_K ? M : K, row_len = a_major == MAJOR_K ? K : M;
+    const int rows = c.a_major == MAJOR_K ? M : K, row_len = c.a_major == MAJOR_K ? K : M;
     if (rows % (BM * world)) { set_last_error("gather_gemm: the sharded dimension (%d) must be a multiple of 128 * world (%d)", rows, BM * world); return B200_ERR_ARG; }
     if (row_len % BK) { set_last_error("gather_gemm: the row length of A (%d) must be a multiple of 64", row_len); return B200_ERR_ARG; }
     GatherParams p{};
     for (int i = 0; i < world; ++i) {
-        if (a_peers[i] == nullptr || started_peers[i] == nullptr || (reinterpret_cast<uintptr_t>(a_peers[i]) & 15)) {
+        if (c.a_peers[i] == nullptr || c.started_peers[i] == nullptr || (reinterpret_cast<uintptr_t>(c.a_peers[i]) & 15)) {
             set_last_error("gather_gemm: peer %d pointer null or not 16-byte aligned", i); return B200_ERR_ARG;
         }
-        p.src[i] = reinterpret_cast<const uint4*>(a_peers[i]);
-        p.started[i] = reinterpret_cast<uint32_t*>(started_peers[i]);
+        p.src[i] = reinterpret_cast<const uint4*>(c.a_peers[i]);
+        p.started[i] = reinterpret_cast<uint32_t*>(c.started_peers[i]);
     }
-    p.dst = reinterpret_cast<uint4*>(a_peers[rank]);
-    p.ready = reinterpret_cast<uint32_t*>(ready);
+    p.dst = reinterpret_cast<uint4*>(c.a_peers[rank]);
+    p.ready = reinterpret_cast<uint32_t*>(c.ready);
     const int cb = gather_chunk_bytes(row_len);
     p.shard_vecs = (long long)(rows / world) * row_len * 2 / 16;
     p.chunk_vecs = cb / 16;
     p.chunks_per_block = (int)(256ll * row_len / cb);
     p.blocks_per_shard = rows / world / BM;
-    p.rank = rank; p.world = world; p.seq = seq;
-    p.k_sharded = a_major == MAJOR_MN ? 1 : 0;
+    p.rank = rank; p.world = world; p.seq = c.seq;
+    p.k_sharded = c.a_major == MAJOR_MN ? 1 : 0;
     p.kb_rot = p.k_sharded ? rank * (K / BK / world) : 0;
-    p.base.C = Cout; p.base.ldc = ldc; p.base.aux = reinterpret_cast<const __nv_bfloat16*>(aux); p.base.ldaux = ldaux;
-    p.base.C2 = reinterpret_cast<__nv_bfloat16*>(out2); p.base.ldc2 = ldc2; p.base.bias = bias; p.base.alpha = alpha;
+    p.base.C = c.Cout; p.base.ldc = c.ldc; p.base.aux = reinterpret_cast<const __nv_bfloat16*>(c.aux); p.base.ldaux = c.ldaux;
+    p.base.C2 = reinterpret_cast<__nv_bfloat16*>(c.out2); p.base.ldc2 = c.ldc2; p.base.bias = c.bias; p.base.alpha = c.alpha;
     const bool needs_aux = epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD || epilogue == EPI_RELU_BWD_MASK || epilogue == EPI_ADD;
     const bool needs_out2 = epilogue == EPI_GELU || epilogue == EPI_RELU_MASK;
-    if (needs_aux && (aux == nullptr || (reinterpret_cast<uintptr_t>(aux) & 15))) { set_last_error("gather_gemm: epilogue %d needs a 16-byte aligned aux", epilogue); return B200_ERR_ARG; }
-    if (needs_out2 && (out2 == nullptr || (reinterpret_cast<uintptr_t>(out2) & 15))) { set_last_error("gather_gemm: epilogue %d needs a 16-byte aligned out2", epilogue); return B200_ERR_ARG; }
+    if (needs_aux && (c.aux == nullptr || (reinterpret_cast<uintptr_t>(c.aux) & 15))) { set_last_error("gather_gemm: epilogue %d needs a 16-byte aligned aux", epilogue); return B200_ERR_ARG; }
+    if (needs_out2 && (c.out2 == nullptr || (reinterpret_cast<uintptr_t>(c.out2) & 15))) { set_last_error("gather_gemm: epilogue %d needs a 16-byte aligned out2", epilogue); return B200_ERR_ARG; }
     const long long mask_pitch = ((N + 127) / 128) * 16;             // bytes per row of a packed ReLU sign mask
-    if ((epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD || epilogue == EPI_ADD) && (ldaux % 8 || ldaux < N)) { set_last_error("gather_gemm: ldaux must be >= N and a multiple of 8"); return B200_ERR_ARG; }
-    if (epilogue == EPI_GELU && (ldc2 % 8 || ldc2 < N)) { set_last_error("gather_gemm: ldc2 must be >= N and a multiple of 8"); return B200_ERR_ARG; }
-    if (epilogue == EPI_RELU_MASK && (ldc2 % 16 || ldc2 < mask_pitch)) { set_last_error("gather_gemm: RELU_MASK needs out2 = uint8 mask with pitch %% 16 == 0 and >= %lld bytes", mask_pitch); return B200_ERR_ARG; }
-    if (epilogue == EPI_RELU_BWD_MASK && (ldaux % 16 || ldaux < mask_pitch)) { set_last_error("gather_gemm: RELU_BWD_MASK needs aux = uint8 mask with pitch %% 16 == 0 and >= %lld bytes", mask_pitch); return B200_ERR_ARG; }
-    if (reinterpret_cast<uintptr_t>(Cout) & 15) { set_last_error("gather_gemm: C must be 16-byte aligned"); return B200_ERR_ARG; }
-    if (ldc % 8 || ldc < N) { set_last_error("gather_gemm: ldc must be >= N and a multiple of 8"); return B200_ERR_ARG; }
-    GemmOperands o{a_peers[rank], (long long)row_len, a_major, B, ldb, b_major, M, N, K};
+    if ((epilogue == EPI_RELU_BWD || epilogue == EPI_GELU_BWD || epilogue == EPI_ADD) && (c.ldaux % 8 || c.ldaux < N)) { set_last_error("gather_gemm: ldaux must be >= N and a multiple of 8"); return B200_ERR_ARG; }
+    if (epilogue == EPI_GELU && (c.ldc2 % 8 || c.ldc2 < N)) { set_last_error("gather_gemm: ldc2 must be >= N and a multiple of 8"); return B200_ERR_ARG; }
+    if (epilogue == EPI_RELU_MASK && (c.ldc2 % 16 || c.ldc2 < mask_pitch)) { set_last_error("gather_gemm: RELU_MASK needs out2 = uint8 mask with pitch %% 16 == 0 and >= %lld bytes", mask_pitch); return B200_ERR_ARG; }
+    if (epilogue == EPI_RELU_BWD_MASK && (c.ldaux % 16 || c.ldaux < mask_pitch)) { set_last_error("gather_gemm: RELU_BWD_MASK needs aux = uint8 mask with pitch %% 16 == 0 and >= %lld bytes", mask_pitch); return B200_ERR_ARG; }
+    if (reinterpret_cast<uintptr_t>(c.Cout) & 15) { set_last_error("gather_gemm: C must be 16-byte aligned"); return B200_ERR_ARG; }
+    if (c.ldc % 8 || c.ldc < N) { set_last_error("gather_gemm: ldc must be >= N and a multiple of 8"); return B200_ERR_ARG; }
+    *out = p;
+    *o = GemmOperands{c.a_peers[rank], (long long)row_len, c.a_major, c.B, c.ldb, c.b_major, M, N, K};
+    return 0;
+}
+
+extern "C" int b200_gather_gemm_bf16(void* const* a_peers, int a_major, const void* B, long long ldb, int b_major, void* Cout, long long ldc,
+                                     int M, int N, int K, int epilogue, const void* aux, long long ldaux, void* out2, long long ldc2,
+                                     const float* bias, float alpha, void* const* started_peers, void* ready, int rank, int world,
+                                     unsigned int seq, int max_ctas, void* stream) {
+    GatherCall c{a_peers, a_major, B, ldb, b_major, Cout, ldc, M, N, K, epilogue, aux, ldaux, out2, ldc2, bias, alpha, started_peers, ready, rank, world, seq};
+    GatherParams p{};
+    GemmOperands o{};
+    if (int rc = gather_build(c, &p, &o)) return rc;
+    const int rows = a_major == MAJOR_K ? M : K;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (world > 1) {
         if (int rc = check_cuda(cudaMemsetAsync(ready, 0, (size_t)b200_gather_gemm_ready_bytes(rows), st), "gather_gemm: clear ready counters")) return rc;
@@ -305,5 +328,44 @@ extern "C" int b200_gather_gemm_bf16(void* const* a_peers, int a_major, const vo
         case EPI_RELU_MASK: return launch_kind<EPI_RELU_MASK>(o, p, max_ctas, st);
         case EPI_RELU_BWD_MASK: return launch_kind<EPI_RELU_BWD_MASK>(o, p, max_ctas, st);
         default: set_last_error("gather_gemm: unsupported epilogue %d", epilogue); return B200_ERR_ARG;
+    }
+}
+
+// ---- single-launch emulation of `world` ranks on ONE GPU (tests, ncu); see gemm_kernel.cuh -----------------------------
+// Per-rank arrays of `world` entries: B (each rank's weight shard under MP, the same weight under FSDP), C, aux, out2, ready.
+// a_peers / started_peers are the shared peer tables.  Epilogues: STORE, RELU_MASK, RELU_BWD_MASK, GELU (the ones the
+// trainers use with this kernel).
+template <int KIND>
+static int emu_kind(int world, const GemmOperands* ops, const GatherParams* ps, int ctas_per_rank, void* table, cudaStream_t st) {
+    int rots[MAX_WORLD];
+    for (int r = 0; r < world; ++r) rots[r] = ps[0].k_sharded ? 0 : r;
+    const int group_m = ps[0].k_sharded ? 0 : (ps[0].blocks_per_shard < 16 ? ps[0].blocks_per_shard : 16);
+    return launch_gemm_emu<GatherEpi<KIND>>(world, ops, ps, rots, ctas_per_rank, use_pair_kernel(), group_m, table, st);
+}
+
+extern "C" int b200_emu_gather_gemm_bf16(int world, void* const* a_peers, int a_major, const void* const* B, long long ldb, int b_major,
+                                         void* const* C, long long ldc, int M, int N, int K, int epilogue, const void* const* aux,
+                                         long long ldaux, void* const* out2, long long ldc2, void* const* started_peers,
+                                         void* const* ready, unsigned int seq, int ctas_per_rank, void* table, void* stream) {
+    if (world < 1 || world > MAX_WORLD || B == nullptr || C == nullptr || ready == nullptr || table == nullptr) { set_last_error("emu_gather_gemm: bad arguments"); return B200_ERR_ARG; }
+    if (ctas_per_rank < 2 || (ctas_per_rank & 1) || world * ctas_per_rank > num_sms()) { set_last_error("emu_gather_gemm: ctas_per_rank must be even and world * ctas_per_rank <= %d", num_sms()); return B200_ERR_ARG; }
+    GatherParams ps[MAX_WORLD];
+    GemmOperands ops[MAX_WORLD];
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const int rows = a_major == MAJOR_K ? M : K;
+    for (int r = 0; r < world; ++r) {
+        GatherCall c{a_peers, a_major, B[r], ldb, b_major, C[r], ldc, M, N, K, epilogue, aux ? aux[r] : nullptr, ldaux, out2 ? out2[r] : nullptr, ldc2,
+                     nullptr, 1.0f, started_peers, ready[r], r, world, seq};
+        if (int rc = gather_build(c, &ps[r], &ops[r])) return rc;
+        if (world > 1) {
+            if (int rc = check_cuda(cudaMemsetAsync(ready[r], 0, (size_t)b200_gather_gemm_ready_bytes(rows), st), "emu_gather_gemm: clear ready counters")) return rc;
+        }
+    }
+    switch (epilogue) {
+        case EPI_STORE: return emu_kind<EPI_STORE>(world, ops, ps, ctas_per_rank, table, st);
+        case EPI_GELU: return emu_kind<EPI_GELU>(world, ops, ps, ctas_per_rank, table, st);
+        case EPI_RELU_MASK: return emu_kind<EPI_RELU_MASK>(world, ops, ps, ctas_per_rank, table, st);
+        case EPI_RELU_BWD_MASK: return emu_kind<EPI_RELU_BWD_MASK>(world, ops, ps, ctas_per_rank, table, st);
+        default: set_last_error("emu_gather_gemm: unsupported epilogue %d", epilogue); return B200_ERR_ARG;
     }
 }

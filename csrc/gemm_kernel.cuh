@@ -41,6 +41,10 @@ struct GemmCore {
     int tiles_m, tiles_n, group_m;
     int tile_offset;   // rotation of the tile order (fused kernels stagger ranks so pushes spread over owners)
     unsigned int* err;
+    // This CTA's index and the size of the grid AS THE KERNEL BODY SEES THEM.  A normal launch fills them from blockIdx /
+    // gridDim; the single-launch multi-rank emulation (emu kernels below) gives every emulated rank its own slice of one
+    // cooperative grid, so the bodies and the epilogue policies must never read blockIdx.x / gridDim.x themselves.
+    int cta, ncta;
 };
 
 // tile index -> (m_blk, n_blk) with grouped rasterisation so the ~148 tiles in flight share A/B panels in L2
@@ -125,6 +129,8 @@ struct EpiCtx {
     int m0, n0;      // first row / column of the tile
     int q;           // TMEM lane quarter (0..3) -> rows m0 + q*32 + lane
     int half;        // column half (0..1)
+    int h;           // pair kernel: which 128-row accumulator half of the CTA's 256 rows (0, 1); 1-CTA kernel: always 1
+                     // (so `h == 1` reads "this CTA has finished a whole scheduler tile")
     int ewarp;       // epilogue warp index 0..EPI_WARPS-1
     int lane;
     uint8_t* stage;  // this warp's EPI_STAGE_BYTES transpose buffer (staged launches only)
@@ -132,9 +138,8 @@ struct EpiCtx {
 };
 
 template <class Epi>
-__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + Epi::LAUNCH_BOUND_PAD, 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const GemmCore g, const typename Epi::Params ep) {
+__device__ __forceinline__ void gemm_1cta_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmCore& g,
+                                               const typename Epi::Params& ep) {
     extern __shared__ uint8_t smem_raw[];
     SmemView sm = carve_smem(smem_raw);
     const int warp = threadIdx.x >> 5;
@@ -170,7 +175,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         int s = 0;
         uint32_t phase = 0;
         [[maybe_unused]] typename Epi::ProducerState pst{};
-        for (int it = blockIdx.x; it < num_tiles; it += gridDim.x) {
+        for (int it = g.cta; it < num_tiles; it += g.ncta) {
             int tile = it + g.tile_offset;
             if (tile >= num_tiles) tile -= num_tiles;
             int m_blk, n_blk;
@@ -215,7 +220,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         uint32_t phase = 0;
         int as = 0;
         uint32_t aphase = 0;
-        for (int it = blockIdx.x; it < num_tiles; it += gridDim.x) {
+        for (int it = g.cta; it < num_tiles; it += g.ncta) {
             int tile = it + g.tile_offset;
             if (tile >= num_tiles) tile -= num_tiles;
             mbar_wait(&sm.tmem_empty[as], aphase ^ 1, g.err, 0x200 + as);
@@ -251,12 +256,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         ctx.stage = sm.epi_stage + ctx.ewarp * EPI_STAGE_BYTES;
         ctx.scratch = reinterpret_cast<uint32_t*>(sm.epi_stage + EPI_WARPS * EPI_STAGE_BYTES);
         ctx.tile = -1;
+        ctx.h = 1;
         ctx.m_blk = ctx.n_blk = ctx.m0 = ctx.n0 = 0;
         typename Epi::State est;
         Epi::init(ep, g, ctx, est);
         int as = 0;
         uint32_t aphase = 0;
-        for (int it = blockIdx.x; it < num_tiles; it += gridDim.x) {
+        for (int it = g.cta; it < num_tiles; it += g.ncta) {
             int tile = it + g.tile_offset;
             if (tile >= num_tiles) tile -= num_tiles;
             ctx.tile = tile;
@@ -282,6 +288,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 1) tmem_dealloc_512(tmem_base);
 }
 
+template <class Epi>
+__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + Epi::LAUNCH_BOUND_PAD, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmCore g_in, const typename Epi::Params ep) {
+    GemmCore g = g_in;
+    g.cta = (int)blockIdx.x;
+    g.ncta = (int)gridDim.x;
+    gemm_1cta_body<Epi>(tmA, tmB, g, ep);
+}
+
 // ---------------------------------------------------------------------------------------------
 // CTA-pair variant: two CTAs of a cluster (one TPC) cooperate on a 512x256 tile with tcgen05.mma.cta_group::2.
 // Each CTA stages 256 rows of A (two 128-row halves) and 128 of the tile's 256 B rows per k-block, and owns TWO
@@ -297,9 +313,8 @@ constexpr int P_STAGE_BYTES = P_A_STAGE_BYTES + P_B_STAGE_BYTES;
 static_assert(P_STAGES * P_STAGE_BYTES == STAGES * STAGE_BYTES, "both variants use the same smem carve-up");
 
 template <class Epi>
-__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + Epi::LAUNCH_BOUND_PAD, 1)
-gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                         const GemmCore g, const typename Epi::Params ep) {
+__device__ __forceinline__ void gemm_pair_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmCore& g,
+                                               const typename Epi::Params& ep) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = base;
@@ -315,8 +330,8 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();          // 0 = leader
-    const int pair = blockIdx.x >> 1;
-    const int num_pairs = gridDim.x >> 1;
+    const int pair = g.cta >> 1;
+    const int num_pairs = g.ncta >> 1;
     const int pair_tiles_m = (g.tiles_m + 3) >> 2;    // 512 rows = four 128-row blocks per pair tile
     const int num_tiles = pair_tiles_m * g.tiles_n;
     const int num_kb = (g.K + BK - 1) / BK;
@@ -432,6 +447,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         ctx.stage = epi_stage + ctx.ewarp * EPI_STAGE_BYTES;
         ctx.scratch = reinterpret_cast<uint32_t*>(epi_stage + EPI_WARPS * EPI_STAGE_BYTES);
         ctx.tile = -1;
+        ctx.h = 0;
         ctx.m_blk = ctx.n_blk = ctx.m0 = ctx.n0 = 0;
         typename Epi::State est;
         Epi::init(ep, g, ctx, est);
@@ -447,6 +463,7 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             tc_fence_after();
 #pragma unroll 1
             for (int h = 0; h < 2; ++h) {
+                ctx.h = h;
                 ctx.m_blk = pm * 4 + (int)rank * 2 + h;
                 ctx.m0 = ctx.m_blk * BM;
                 const uint32_t taddr = tmem_base + ((uint32_t)(ctx.q * 32) << 16) + (uint32_t)(h * BN + ctx.half * (BN / 2));
@@ -470,6 +487,42 @@ gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     cluster_sync_all();                               // neither CTA may retire while its pair still uses its smem / barriers
     tc_fence_after();
     if (warp == 1) tmem_dealloc_512_pair(tmem_base);
+}
+
+template <class Epi>
+__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + Epi::LAUNCH_BOUND_PAD, 1)
+gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const GemmCore g_in, const typename Epi::Params ep) {
+    GemmCore g = g_in;
+    g.cta = (int)blockIdx.x;
+    g.ncta = (int)gridDim.x;
+    gemm_pair_body<Epi>(tmA, tmB, g, ep);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Single-launch multi-rank emulation (tests, ncu): ONE cooperative grid in which CTAs [r*cpr, (r+1)*cpr) run the body
+// exactly as rank r's kernel would - its own tensor maps, tile walk and policy parameters, read from a table in global
+// memory.  Kernels that spin on one another's flags must not be separate launches on one GPU (nothing makes them
+// co-resident); this is how the cross-rank protocols of fused.cu / gather_gemm.cu are exercised on a single B200, with
+// every "peer" pointer resolving to local memory.  Same code, same protocol; only NVLink is missing.
+// ---------------------------------------------------------------------------------------------
+template <class Epi>
+struct alignas(64) EmuRank {
+    CUtensorMap tmA, tmB;
+    GemmCore core;
+    typename Epi::Params ep;
+};
+
+template <class Epi, bool PAIR>
+__global__ void __launch_bounds__(GEMM_THREADS + 32 * Epi::EXTRA_WARPS + Epi::LAUNCH_BOUND_PAD, 1)
+gemm_tcgen05_emu_kernel(const EmuRank<Epi>* __restrict__ ranks, const int ctas_per_rank) {
+    const int r = (int)blockIdx.x / ctas_per_rank;
+    const EmuRank<Epi>& R = ranks[r];
+    GemmCore g = R.core;
+    g.cta = (int)blockIdx.x - r * ctas_per_rank;
+    g.ncta = ctas_per_rank;
+    if constexpr (PAIR) gemm_pair_body<Epi>(R.tmA, R.tmB, g, R.ep);
+    else gemm_1cta_body<Epi>(R.tmA, R.tmB, g, R.ep);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -601,7 +654,9 @@ struct LocalEpi {
 
         // packed ReLU sign mask: this lane's row, this warp's 128 columns = 16 bytes at mask[row][colbase / 8]
         uint32_t mbits[4] = {0u, 0u, 0u, 0u};
-        const bool mrow_ok = (row0 + lane) < g.M;
+        // colbase < N: with N % 256 == 128 the second column half of the last n-tile lies wholly outside the matrix; its
+        // 16 mask bytes would be the NEXT row's first 16 (pitch N/8) - never touch them
+        const bool mrow_ok = (row0 + lane) < g.M && colbase < g.N;
         if constexpr (KIND == EPI_RELU_BWD_MASK) {
             if (mrow_ok) {
                 const uint4 mv = ld_nc_u4(reinterpret_cast<const uint8_t*>(p.aux) + (long long)(row0 + lane) * p.ldaux + colbase / 8);
@@ -752,5 +807,49 @@ int launch_gemm(const GemmOperands& o, const typename Epi::Params& ep, int max_c
     cfg.numAttrs = 1;
     return check_cuda(cudaLaunchKernelEx(&cfg, gemm_tcgen05_pair_kernel<Epi>, tmA, tmB, core, ep), "gemm pair launch");
 }
+
+// Host side of the emulation: build every rank's tensor maps / core / policy parameters, upload the table, launch ONE
+// cooperative grid of world * ctas_per_rank CTAs.  `rots[r] / world` is rank r's tile-walk rotation (launch_gemm's
+// tile_offset_num / tile_offset_den).  `table`: device scratch of EMU_TABLE_BYTES.
+constexpr int EMU_MAX_WORLD = 8;
+constexpr int EMU_TABLE_BYTES = 8 * 1024;
+template <class Epi, class P>
+int launch_gemm_emu(int world, const GemmOperands* ops, const P* params, const int* rots, int ctas_per_rank, bool pair,
+                      int group_m, void* table, cudaStream_t st) {
+    static_assert(sizeof(EmuRank<Epi>) * EMU_MAX_WORLD <= EMU_TABLE_BYTES, "emulation table too small");
+    EmuRank<Epi> host[EMU_MAX_WORLD];
+    for (int r = 0; r < world; ++r) {
+        if (int rc = make_core_and_maps(ops[r], &host[r].core, &host[r].tmA, &host[r].tmB, pair)) return rc;
+        if (group_m > 0) host[r].core.group_m = group_m;
+        const int tiles = pair ? ((host[r].core.tiles_m + 3) / 4) * host[r].core.tiles_n : host[r].core.tiles_m * host[r].core.tiles_n;
+        host[r].core.tile_offset = (int)((long long)tiles * rots[r] / world);
+        host[r].ep = params[r];
+    }
+    if (int rc = check_cuda(cudaMemcpyAsync(table, host, sizeof(EmuRank<Epi>) * world, cudaMemcpyHostToDevice, st), "emu: table upload")) return rc;
+    if (int rc = check_cuda(cudaStreamSynchronize(st), "emu: table upload sync")) return rc;   // `host` is a stack array
+    void* fn = pair ? (void*)gemm_tcgen05_emu_kernel<Epi, true> : (void*)gemm_tcgen05_emu_kernel<Epi, false>;
+    if (int rc = check_cuda(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, Epi::SMEM_BYTES), "emu: smem attribute")) return rc;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(world * ctas_per_rank);
+    cfg.blockDim = dim3(GEMM_THREADS + 32 * Epi::EXTRA_WARPS);
+    cfg.dynamicSmemBytes = Epi::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    at[na].id = cudaLaunchAttributeCooperative;     // all CTAs co-resident, or the launch fails: the slices wait on each other
+    at[na].val.cooperative = 1;
+    ++na;
+    if (pair) {
+        at[na].id = cudaLaunchAttributeClusterDimension;
+        at[na].val.clusterDim.x = 2; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;
+        ++na;
+    }
+    cfg.attrs = at;
+    cfg.numAttrs = na;
+    const EmuRank<Epi>* tab = reinterpret_cast<const EmuRank<Epi>*>(table);
+    if (pair) return check_cuda(cudaLaunchKernelEx(&cfg, gemm_tcgen05_emu_kernel<Epi, true>, tab, ctas_per_rank), "emu launch (pair)");
+    return check_cuda(cudaLaunchKernelEx(&cfg, gemm_tcgen05_emu_kernel<Epi, false>, tab, ctas_per_rank), "emu launch (1-CTA)");
+}
+
 
 }  // namespace b200

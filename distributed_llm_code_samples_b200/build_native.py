@@ -43,8 +43,8 @@ def _newest_header_mtime() -> float:
     return max((h.stat().st_mtime for h in hs), default=0.0)
 
 
-def _compile_one(nvcc: str, src: Path, obj: Path, verbose: bool) -> str:
-    cmd = [nvcc, *NVCC_FLAGS, "-c", str(src), "-o", str(obj)]
+def _compile_one(nvcc: str, src: Path, obj: Path, verbose: bool, defines: tuple = ()) -> str:
+    cmd = [nvcc, *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-c", str(src), "-o", str(obj)]
     p = subprocess.run(cmd, capture_output=True, text=True)
     log = p.stdout + p.stderr
     (obj.with_suffix(".ptxas.log")).write_text(log)
@@ -84,11 +84,34 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     return LIB_PATH
 
 
+def build_variant(tag: str, defines: tuple) -> Path:
+    """A/B builds: the same sources with extra ``-D`` defines -> ``_native/variants/<tag>/libb200ffn_<tag>.so``
+    (select it at run time with ``B200_NATIVE_LIB=<path>``)."""
+    nvcc = find_nvcc()
+    out = OUT_DIR / "variants" / tag
+    out.mkdir(parents=True, exist_ok=True)
+    srcs = sorted(CSRC.glob("*.cu"))
+    objs = [out / (s.stem + ".o") for s in srcs]
+    with cf.ThreadPoolExecutor(max_workers=min(len(srcs), os.cpu_count() or 4)) as ex:
+        for f in [ex.submit(_compile_one, nvcc, s, o, False, tuple(defines)) for s, o in zip(srcs, objs)]:
+            f.result()
+    lib = out / f"libb200ffn_{tag}.so"
+    p = subprocess.run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(lib), *map(str, objs)], capture_output=True, text=True)
+    if p.returncode != 0:
+        raise RuntimeError(f"link failed:\n{p.stdout}{p.stderr}")
+    return lib
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--force", action="store_true")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--variant", default=None, help="TAG:DEFINE[=V][,DEFINE...]  e.g. hint20k:B200_MBAR_HINT_NS=20000")
     a = ap.parse_args()
+    if a.variant:
+        tag, _, defs = a.variant.partition(":")
+        print(build_variant(tag, tuple(d for d in defs.split(",") if d)))
+        return 0
     path = build(force=a.force, verbose=a.verbose)
     print(path)
     return 0

@@ -52,6 +52,10 @@ class TrainConfig:
     comm: str = "auto"                     # auto | fused (collective inside the GEMM) | native (peer-memory collectives) | nccl
     recompute: bool = False                # reference recomputes h in backward (:63); we keep it by default
     mp_mode: str = "ar"                    # ar = reference all-reduce form (:303,:309); sp = AG/RS sequence-parallel; spf = sp with the AG inside the GEMM
+    fsdp_gather: str = "dma"               # fused FSDP parameter all-gather: dma = copy-engine prefetch one layer ahead (:236-249);
+                                           # fused = inside the consuming GEMMs, forward and backward (parallel/fused_fsdp_t.py)
+    mp_input: str = "full"                 # Engine.train under MP all-reduce form: full = every rank stages the whole batch (:294, :324);
+                                           # sharded = 1/world over PCIe + NVLink all-gather (ShardedPrefetcher)
     master_port: int = 29500               # train_ffns.py:124
     save_path: Optional[str] = None
     load_path: Optional[str] = None
@@ -70,6 +74,10 @@ class TrainConfig:
             raise ValueError("optimizer must be sgd or adam")
         if self.mp_mode not in ("ar", "sp", "spf"):
             raise ValueError("mp_mode must be ar, sp or spf")
+        if self.fsdp_gather not in ("dma", "fused"):
+            raise ValueError("fsdp_gather must be dma or fused")
+        if self.mp_input not in ("full", "sharded"):
+            raise ValueError("mp_input must be full or sharded")
         parse_dtype(self.dtype)
 
     @property

@@ -11,7 +11,6 @@ metric on the device and reads it back (one step late, so the read never stalls 
 """
 from __future__ import annotations
 
-import os
 from typing import Iterable, Iterator, List, Optional, Sequence, Tuple
 
 import torch
@@ -89,7 +88,7 @@ class Engine:
             ts = self.cfg.tokens // self.world
             rows = slice(self.rank * ts, (self.rank + 1) * ts)
         sw = getattr(self.trainer, "sw", None)
-        if self.method == "mp" and self.world > 1 and rows is None and sw is not None and os.environ.get("B200_MP_SHARDED_INPUT") == "1":
+        if self.method == "mp" and self.world > 1 and rows is None and sw is not None and self.cfg.mp_input == "sharded":
             # all-reduce form: every rank needs the whole batch - stage 1/world of it over PCIe, gather the rest over NVLink
             pf = ShardedPrefetcher(host_batches, self.device, sw, self.rank, self.world)
         else:

@@ -13,7 +13,10 @@ from typing import Optional
 
 import torch
 
-_LIB_PATH = Path(__file__).resolve().parent.parent / "_native" / "libb200ffn.so"
+import os
+
+# B200_NATIVE_LIB selects an A/B build of the same sources (build_native.build_variant); default = the in-tree library
+_LIB_PATH = Path(os.environ.get("B200_NATIVE_LIB") or (Path(__file__).resolve().parent.parent / "_native" / "libb200ffn.so"))
 _lib = None
 _lock = threading.Lock()
 
@@ -123,6 +126,11 @@ def _optional_declare(lib) -> None:
         "b200_gather_gemm_ready_bytes": ([i], ll),
         "b200_gather_gemm_bf16": ([pp, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp], i),
         "b200_debug_gather_chunk": ([i, i, i, i, ll, C.POINTER(ll)], i),
+        "b200_fused_config": ([i, i], i),
+        "b200_emu_table_bytes": ([], ll),
+        "b200_emu_gemm_allreduce_bf16": ([i, pp, ll, i, pp, ll, i, i, i, i, pp, ll, pp, pp, i, i, u, i, i, i, f,
+                                         pp, pp, f, f, f, f, i, f, i, vp, vp], i),
+        "b200_emu_gather_gemm_bf16": ([i, pp, i, pp, ll, i, pp, ll, i, i, i, i, pp, ll, pp, ll, pp, pp, u, i, vp, vp], i),
     }
     for name, sig in table.items():
         if not hasattr(lib, name):

@@ -10,7 +10,6 @@ per-rank trainer and writes the result back into CPU shared-memory tensors owned
 from __future__ import annotations
 
 import copy
-import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -53,8 +52,8 @@ def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Seque
     if method == "fsdp":
         shards = [[fsdp_shard(p, r, n) for p in lp] for lp in layers_params]
         if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg, "fsdp"):
-            if os.environ.get("B200_FSDP_FUSED_GATHER") == "1" and cfg.tokens % 8 == 0:
-                # forward parameter all-gather inside the consuming GEMMs (not yet run on hardware)
+            if cfg.fsdp_gather == "fused" and cfg.tokens % 8 == 0:
+                # parameter all-gather inside the consuming GEMMs, forward and backward
                 from .fused_fsdp_t import FusedFSDPGatherTrainer
                 return FusedFSDPGatherTrainer(ops, comm, cfg, place(shards, device, dtype), device)
             from .fused import FusedFSDPTrainer
@@ -72,24 +71,23 @@ def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Seque
 def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
     """The peer-memory fused kernels need the native ops, bf16, >1 rank, SGD, no bias and TMA-legal shapes
     (FSDP additionally needs every row shard to be a whole number of 128-row tiles)."""
-    # Adam with the fused trainers (inside the kernel for DDP / FSDP; MP: fused collectives + the native Adam kernel on the
-    # local dW) is written but has not run on hardware yet: opt-in via B200_FUSED_ADAM=1
-    opt_ok = cfg.optimizer == "sgd" or (cfg.optimizer == "adam" and os.environ.get("B200_FUSED_ADAM") == "1")
+    # Adam: inside the kernel for DDP / FSDP (the tile owner applies it and owns the moments); MP: fused collectives + the
+    # native Adam kernel on the shard-local dW.
     ok = (getattr(ops, "name", "") == "native" and comm.world > 1 and cfg.dtype in ("bf16", "bfloat16")
-          and opt_ok and not cfg.bias and cfg.model_size % 8 == 0 and cfg.ffn_dim % 8 == 0)
+          and not cfg.bias and cfg.model_size % 8 == 0 and cfg.ffn_dim % 8 == 0)
     if method == "fsdp":
         ok = ok and cfg.model_size % (128 * comm.world) == 0 and cfg.ffn_dim % (128 * comm.world) == 0
     if method == "mp":
-        # the residual form of the fused MP trainer reuses the kernels' in-place update mode; not yet run on hardware
-        ok = ok and (not cfg.residual or os.environ.get("B200_FUSED_MP_RESIDUAL") == "1") and (cfg.ffn_dim // comm.world) % 8 == 0
+        # (a residual rides on the kernels' in-place update mode: output pre-filled with the residual, alpha = -1)
+        ok = ok and (cfg.ffn_dim // comm.world) % 8 == 0
         if cfg.mp_mode in ("sp", "spf"):
             ok = ok and cfg.tokens % (128 * comm.world) == 0
         if cfg.mp_mode == "spf":
             ok = ok and cfg.model_size % 64 == 0
     if not ok:
         if cfg.comm == "fused":
-            raise RuntimeError("comm=fused needs impl=native, bf16, SGD (Adam for DDP/FSDP with B200_FUSED_ADAM=1), no bias, world>1, dims % 8 == 0 "
-                               "(FSDP: dims % (128*world) == 0; MP: residual needs B200_FUSED_MP_RESIDUAL=1, sp forms need tokens % (128*world) == 0)")
+            raise RuntimeError("comm=fused needs impl=native, bf16, no bias, world>1, dims % 8 == 0 "
+                               "(FSDP: dims % (128*world) == 0; MP sp forms: tokens % (128*world) == 0)")
         return False
     try:
         from . import fused  # noqa: F401

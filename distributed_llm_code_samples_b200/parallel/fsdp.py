@@ -28,7 +28,6 @@ class FSDPTrainer:
         # two staging sets of full parameters (double buffer for the one-layer-ahead prefetch)
         self.full = [[torch.empty((s.shape[0] * self.world, *s.shape[1:]), dtype=s.dtype, device=s.device)
                       for s in shards[0]] for _ in range(2)]
-        self.shard_grads = [torch.empty_like(s) for s in shards[0]]        # reduce-scatter outputs (:227)
         self._pending = {}
 
     # -- parameter all-gather with one-layer-ahead prefetch ------------------------------------------------
@@ -68,7 +67,8 @@ class FSDPTrainer:
             acts[i] = None
             if rs_prev is not None:                              # apply layer i+1's update while layer i ran
                 self._apply(*rs_prev)
-            outs = [torch.empty_like(s) for s in self.shards[i]] if i > 0 else self.shard_grads
+            # reduce-scatter outputs (:227) in the GRADIENT's dtype: bias gradients are fp32 sums whatever the parameters are
+            outs = [torch.empty(s.shape, dtype=g.dtype, device=s.device) for s, g in zip(self.shards[i], grads)]
             hs = [self.comm.reduce_scatter_into(o, g, async_op=True) for o, g in zip(outs, grads)]
             rs_prev = (i, outs, hs, grads)
         self._apply(*rs_prev)

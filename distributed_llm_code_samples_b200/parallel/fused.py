@@ -13,7 +13,6 @@ collectives (``csrc/comm.cu``) - no NCCL on the data path.
 from __future__ import annotations
 
 import ctypes as C
-import os
 from typing import Iterable, List, Optional, Tuple
 
 import torch
@@ -238,9 +237,6 @@ class FusedFSDPTrainer:
 
     def _start_gather(self, layer: int) -> None:
         if not (0 <= layer < self.L) or layer in self._pending:
-            return
-        if os.environ.get("B200_DEBUG_SKIP_GATHER") == "1":      # timing experiments only: parameters go stale
-            self._pending[layer] = _Handle(None)
             return
         lib = nv.load()
         slot = layer % 2

@@ -85,7 +85,7 @@ def test_epilogues(cuda_device):
     assert (o32 - 0.5 * ref).abs().max().item() < 1e-2
 
 
-@pytest.mark.parametrize("M,N,K", [(384, 512, 320), (200, 384, 136), (1024, 1280, 512)])
+@pytest.mark.parametrize("M,N,K", [(384, 512, 320), (200, 384, 136), (1024, 1280, 512), (8192, 384, 136), (16384, 5504, 64)])
 def test_relu_bitmask_epilogues(cuda_device, M, N, K):
     """ReLU forward that also packs the sign mask (1 bit/element) and the backward that consumes it (:47-52)."""
     x, w = _rand((M, K), cuda_device, seed=31), _rand((N, K), cuda_device, 0.1, seed=32)
@@ -100,6 +100,63 @@ def test_relu_bitmask_epilogues(cuda_device, M, N, K):
     out = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
     nv.gemm(dy, 0, w2, 1, out, M, N, K, nv.EPI_RELU_BWD_MASK, aux=mask)
     _check(out, (dy.float() @ w2.float()) * bits, K, "relu_bwd from mask")
+
+
+def _tile_rel_err(out, ref):
+    """max over 128x256 tiles of (max |out - ref| in the tile) / (max |ref| in the tile)."""
+    M, N = ref.shape
+    d = (out.float() - ref).abs().reshape(M // 128, 128, N // 256, 256).amax(dim=(1, 3))
+    s = ref.abs().reshape(M // 128, 128, N // 256, 256).amax(dim=(1, 3)).clamp_min(1e-30)
+    return float((d / s).max())
+
+
+@pytest.mark.parametrize("layout", ["tn", "nn", "nt", "relu_mask", "relu_bwd_mask", "sgd"])
+def test_gemm_benchmark_size(cuda_device, layout):
+    """Numerics at the benchmark's size, 16384 x 16384 x 4096 (148 CTAs x 14 pair tiles each, several rasterisation
+    groups), per 128x256 tile against torch's fp32 GEMM of the same bf16 inputs - every layout of the training step."""
+    M, N, K = 16384, 16384, 4096
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
+        if layout in ("tn", "relu_mask"):
+            a, b = _rand((M, K), cuda_device, seed=41), _rand((N, K), cuda_device, 0.1, seed=42)
+            ref = a.float() @ b.float().T
+            if layout == "tn":
+                nv.gemm(a, 0, b, 0, out, M, N, K)
+            else:
+                mask = torch.zeros(M, N // 8, dtype=torch.uint8, device=cuda_device)
+                nv.gemm(a, 0, b, 0, out, M, N, K, nv.EPI_RELU_MASK, out2=mask)
+                ref = torch.relu(ref)
+                bits = ((mask.unsqueeze(-1) >> torch.arange(8, device=cuda_device, dtype=torch.uint8)) & 1).reshape(M, N).bool()
+                assert torch.equal(bits, out > 0)
+        elif layout in ("nn", "relu_bwd_mask"):
+            a, b = _rand((M, K), cuda_device, seed=43), _rand((K, N), cuda_device, 0.1, seed=44)
+            ref = a.float() @ b.float()
+            if layout == "nn":
+                nv.gemm(a, 0, b, 1, out, M, N, K)
+            else:
+                keep = torch.rand(M, N, device=cuda_device) > 0.5
+                w = (1 << torch.arange(8, device=cuda_device, dtype=torch.int32))
+                mask = (keep.reshape(M, N // 8, 8).int() * w).sum(-1).to(torch.uint8)
+                nv.gemm(a, 0, b, 1, out, M, N, K, nv.EPI_RELU_BWD_MASK, aux=mask)
+                ref = ref * keep
+        else:
+            a, b = _rand((K, M), cuda_device, seed=45), _rand((K, N), cuda_device, 0.1, seed=46)
+            ref = a.float().T @ b.float()
+            if layout == "nt":
+                nv.gemm(a, 1, b, 1, out, M, N, K)
+            else:
+                out.copy_(_rand((M, N), cuda_device, 0.5, seed=47))
+                w0 = out.float().clone()
+                nv.gemm(a, 1, b, 1, out, M, N, K, nv.EPI_SGD, alpha=0.01)
+                ref = w0 - 0.01 * ref
+        torch.cuda.synchronize()
+        assert torch.isfinite(out.float()).all()
+        assert _tile_rel_err(out, ref) <= 1e-2, (layout, _tile_rel_err(out, ref))
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    assert nv.device_error()[0] == 0
 
 
 def test_gemm_strided_views(cuda_device):

@@ -8,7 +8,8 @@ pytestmark = [pytest.mark.gpu, pytest.mark.skipif(torch.cuda.device_count() < 2,
 import os
 
 WORLD = min(torch.cuda.device_count(), 8) if torch.cuda.is_available() else 0
-# Tests written after round 1's GPU budget was spent have never run on hardware: they are opt-in until validated.
+# Tests of code that has not run on hardware yet are opt-in until validated (none at present: round 2's first 2-GPU call
+# ran everything round 1 had queued - log in profiles/tests/r2_call1_2gpu/).
 queued = pytest.mark.skipif(os.environ.get("B200_QUEUED_TESTS") != "1", reason="queued for the next GPU round (set B200_QUEUED_TESTS=1)")
 DM = max(256, 128 * max(WORLD, 1))
 
@@ -116,7 +117,7 @@ def _oracle(lp, seeds, T, method):
     return tr.params
 
 
-@pytest.mark.parametrize("method", ["ddp", "fsdp", "mp", "mp_sp", pytest.param("mp_spf", marks=queued)])
+@pytest.mark.parametrize("method", ["ddp", "fsdp", "mp", "mp_sp", "mp_spf"])
 def test_fused_trainer_matches_nccl_trainer(method):
     """Same initial weights and data through the fused peer-memory path, the NCCL path and an fp32 oracle.  The two GPU
     paths round differently (fused: fp32 sum of bf16 partials, one rounding; NCCL: bf16 at every hop), and a bf16 weight
@@ -143,15 +144,13 @@ def test_fused_trainer_matches_nccl_trainer(method):
     assert max(u.abs().max().item() for l in uf for u in l) > 0
 
 
-@queued
-def test_fsdp_with_in_kernel_forward_gather_matches_nccl(monkeypatch):
+def test_fsdp_with_in_kernel_forward_gather_matches_nccl():
     """parallel/fused_fsdp_t.py: transposed activations; the weight is the gathered A operand of every forward GEMM
     (row-sharded form) and of the backward GEMMs of the layers the forward pass no longer holds (K-sharded form)."""
     from distributed_llm_code_samples_b200.parallel import api
-    monkeypatch.setenv("B200_FSDP_FUSED_GATHER", "1")
     lp, seeds = _init()
     T = 512
-    fused = api.train_fsdp(lp, seeds, T, DM, _cfg(comm="fused"))
+    fused = api.train_fsdp(lp, seeds, T, DM, _cfg(comm="fused", fsdp_gather="fused"))
     nccl = api.train_fsdp(lp, seeds, T, DM, _cfg(comm="nccl"))
     oracle = _oracle(lp, seeds, T, "fsdp")
     upd = lambda res: [[p.float() - q for p, q in zip(a, b)] for a, b in zip(res, lp)]
@@ -161,13 +160,11 @@ def test_fsdp_with_in_kernel_forward_gather_matches_nccl(monkeypatch):
     assert err_f < 0.35 and err_f <= 1.3 * err_n + 0.01, (err_f, err_n)
 
 
-@queued
 @pytest.mark.parametrize("mp_mode", ["ar", "sp", "spf"])
-def test_fused_mp_with_gelu_and_residual_matches_nccl(mp_mode, monkeypatch):
+def test_fused_mp_with_gelu_and_residual_matches_nccl(mp_mode):
     """The north-star block (Linear -> GELU -> Linear, residual) under fused MP: the residual rides on the kernels'
     in-place update mode (output pre-filled with the residual, alpha = -1)."""
     from distributed_llm_code_samples_b200.parallel import api
-    monkeypatch.setenv("B200_FUSED_MP_RESIDUAL", "1")
     lp, _ = _init()
     seeds = torch.arange(1)
     T = max(512, 256 * WORLD)
@@ -180,14 +177,12 @@ def test_fused_mp_with_gelu_and_residual_matches_nccl(mp_mode, monkeypatch):
     assert _rel(upd(fused), upd(nccl)) < 0.25
 
 
-@queued
 @pytest.mark.parametrize("method", ["ddp", "fsdp", "mp"])
-def test_fused_adam_matches_unfused_adam(method, monkeypatch):
+def test_fused_adam_matches_unfused_adam(method):
     """Adam inside the fused kernel's owner reduction (moments sharded by tile owner; MP: fused collectives + the native
     Adam kernel on the shard-local dW) vs the unfused trainer (bf16 all-reduce / reduce-scatter, then b200_adam_bf16).  Adam's first step moves every weight by ~lr regardless of the
     gradient scale, so the two must agree closely; two steps exercise the stored moments."""
     from distributed_llm_code_samples_b200.parallel import api
-    monkeypatch.setenv("B200_FUSED_ADAM", "1")
     lp, _ = _init()
     seeds = torch.arange(2 if method == "mp" else 2 * WORLD)      # two optimizer steps either way (MP: every rank sees every seed)
     fn = {"ddp": api.train_ddp, "fsdp": api.train_fsdp, "mp": api.train_tp}[method]
@@ -199,7 +194,6 @@ def test_fused_adam_matches_unfused_adam(method, monkeypatch):
     assert _rel(upd(fused), upd(unfused)) < 0.25
 
 
-@queued
 @pytest.mark.parametrize("method,extra", [("ddp", {"optimizer": "adam"}), ("fsdp", {"bias": True}), ("mp", {"residual": True})])
 def test_unfused_trainers_on_native_collectives_match_nccl(method, extra):
     """--comm native: the plain trainers (so Adam / bias / residual work) with every collective on the peer-memory
@@ -267,7 +261,6 @@ def _vmm_worker(rank, world, dev, out):
     out[rank] = (2.0 if mc_ok else 1.0) if ok else 0.0
 
 
-@queued
 def test_vmm_multicast_all_reduce():
     """EXPERIMENTAL runtime (csrc/vmm.cu): cuMem blocks shared by fd, used as a peer table, and - where the box has
     NVLS - an in-switch all-reduce (multimem.ld_reduce / multimem.st) on the multicast mapping."""
@@ -309,7 +302,6 @@ def _stress_worker(rank, world, dev, out):
     sw.close()
 
 
-@queued
 def test_barrier_and_flag_protocol_stress():
     from distributed_llm_code_samples_b200.parallel.launcher import launch
     out = torch.zeros(WORLD).share_memory_()

@@ -122,7 +122,10 @@ def bench(dev, which: str) -> None:
     y = torch.empty(T, D, dtype=torch.bfloat16, device=dev)
     dw1 = torch.empty(F, D, dtype=torch.bfloat16, device=dev)
     dw2 = torch.empty(D, F, dtype=torch.bfloat16, device=dev)
+    mask = torch.zeros(T, F // 8, dtype=torch.uint8, device=dev)
     cases = [
+        ("G1m h=relu(x@W1^T) TN + sign bitmask (the step's default)", lambda: nv.gemm(x, 0, w1, 0, h, T, F, D, nv.EPI_RELU_MASK, out2=mask), lambda: torch.relu(x @ w1.T), 2 * T * F * D),
+        ("G5m da=dy@W2 NN + relu_bwd from bitmask (the step's default)", lambda: nv.gemm(dy, 0, w2, 1, h, T, F, D, nv.EPI_RELU_BWD_MASK, aux=mask), lambda: (dy @ w2).masked_fill_(a <= 0, 0), 2 * T * F * D),
         ("G1 h=relu(x@W1^T) TN", lambda: nv.gemm(x, 0, w1, 0, h, T, F, D, nv.EPI_RELU), lambda: torch.relu(x @ w1.T), 2 * T * F * D),
         ("G2 y=a@W2^T TN", lambda: nv.gemm(a, 0, w2, 0, y, T, D, F), lambda: a @ w2.T, 2 * T * F * D),
         ("G5 da=dy@W2 NN +relu_bwd", lambda: nv.gemm(dy, 0, w2, 1, h, T, F, D, nv.EPI_RELU_BWD, aux=a), lambda: (dy @ w2).masked_fill_(a <= 0, 0), 2 * T * F * D),
@@ -138,7 +141,7 @@ def bench(dev, which: str) -> None:
                "ours_tflops": round(flops / tm / 1e9, 1), "torch_tflops": round(flops / tr / 1e9, 1)}
         recs.append(rec)
         print(json.dumps(rec))
-    with open(os.path.join(OUT, f"gemm_bench_{which}.jsonl"), "w") as f:
+    with open(os.path.join(OUT, f"gemm_bench_{which}{os.environ.get('GEMM_BENCH_TAG', '')}.jsonl"), "w") as f:
         for r in recs:
             f.write(json.dumps(r) + "\n")
 

@@ -7,7 +7,7 @@ Same command line as the reference (``train_ffns.py:343-351``):
 
 ``M``: 0 = all methods, 1 = one GPU, 2 = DDP, 3 = FSDP, 4 = MP/TP (``:5-6``).  Extra flags select what the
 reference hard-codes: ``--ffn_dim --dtype --activation --residual --bias --optimizer --lr --world_size --backend
---device --impl --comm --recompute --mp_mode --save_path --load_path --profile --cuda_graph --data``.
+--device --impl --comm --recompute --mp_mode --fsdp_gather --mp_input --save_path --load_path --profile --cuda_graph --data``.
 """
 from __future__ import annotations
 
@@ -48,6 +48,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--comm', default='auto', choices=['auto', 'fused', 'native', 'nccl'])
     p.add_argument('--recompute', action='store_true')
     p.add_argument('--mp_mode', default='ar', choices=['ar', 'sp', 'spf'])
+    p.add_argument('--fsdp_gather', default='dma', choices=['dma', 'fused'], help='fused FSDP: copy-engine prefetch, or all-gather inside the consuming GEMMs')
+    p.add_argument('--mp_input', default='full', choices=['full', 'sharded'])
     p.add_argument('--master_port', type=int, default=29500)
     p.add_argument('--save_path', default=None)
     p.add_argument('--load_path', default=None)
