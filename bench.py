@@ -43,13 +43,19 @@ def parse_args():
     ap.add_argument("--recompute", action="store_true", help="reference-style activation recompute in backward")
     ap.add_argument("--mp_mode", default="ar", choices=["ar", "sp", "spf"],
                     help="MP form: ar = the reference's all-reduce form (default, the benchmarked one); sp / spf = sequence-parallel variants")
+    ap.add_argument("--fsdp_gather", default="dma", choices=["dma", "fused"])
+    ap.add_argument("--mp_input", default="full", choices=["full", "sharded"])
+    ap.add_argument("--also", default="auto",
+                    help="extra strategies measured in the same process and reported under `also` (comma list of fsdp, mp, "
+                         "ddp_recompute; auto = fsdp,mp when --method ddp; none)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--pool", type=int, default=3, help="distinct synthetic batches cycled through")
     return ap.parse_args()
 
 
-def shape_defaults(args):
-    if args.method == "mp":     # BASELINE.json config 4: Llama-70B FFN shape, TP
+def shape_defaults(args, method=None):
+    method = method or args.method
+    if method == "mp":          # BASELINE.json config 4: Llama-70B FFN shape, TP
         d, f, l = 8192, 28672, 16
     else:                       # configs 2/3: DDP / FSDP stack
         d, f, l = 4096, 16384, 32
@@ -104,23 +110,49 @@ def emit(rec):
     print(json.dumps(rec), flush=True)
 
 
+# ------------------------------------------------------------------------------------------------ shared
+def base_config(method, world, d, f, l, args, global_batch):
+    """The `config` block: IDENTICAL keys and values in both arms (what differs per arm goes to `impl_detail`)."""
+    par = {"single": "single", "ddp": f"dp{world}", "fsdp": f"fsdp{world}", "mp": f"tp{world}"}[method]
+    return {"model": f"ffn_stack_d{d}_f{f}_l{l}_relu", "global_batch": global_batch, "seq_len": args.seq_len,
+            "batch_size_per_rank": args.batch_size, "parallelism": par,
+            "l2": "per-step inputs (>= 256 MiB) and weights (>= 8 GiB) far exceed the 126 MB L2; batches cycle through a pool",
+            "init": "variance-preserving scale (2/(D*F))^(1/4), same in both arms", "dloss_scale": DLOSS_SCALE}
+
+
+def record(impl, method, world, args, value, ms, clocks, e2e, launches, config, detail):
+    return {"metric": f"ffn_stack_{method}_tokens_per_sec", "value": value, "unit": "tokens/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak" if method in ("ddp", "fsdp") else "strong", "vs_baseline": PUBLISHED_BASELINE,
+            "dtype": "bf16", "data": "synthetic", "impl": impl, "config": config, "impl_detail": detail,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches}
+
+
+def also_methods(args):
+    if args.also == "none":
+        return []
+    if args.also != "auto":
+        return [m for m in args.also.split(",") if m]
+    return ["fsdp", "mp"] if args.method == "ddp" else []
+
+
 # ------------------------------------------------------------------------------------------------ ours
-def run_ours(args):
+def ours_one(args, method, recompute):
+    """One strategy of this framework: device-timed K steps, then the end-to-end loop.  Returns the record (rank 0's is
+    the one printed).  Everything the run allocated is released before returning."""
+    import gc
     from distributed_llm_code_samples_b200.config import TrainConfig
-    from distributed_llm_code_samples_b200.engine import Engine
+    from distributed_llm_code_samples_b200.engine import Engine, init_params_on_device
     from distributed_llm_code_samples_b200.ops import native as nv
     from distributed_llm_code_samples_b200.utils.clocks import ClockSampler
 
     rank, world, local = rank_world()
-    d, f, l = shape_defaults(args)
-    method = args.method if world > 1 or args.method == "single" else args.method
+    d, f, l = shape_defaults(args, method)
     cfg = TrainConfig(num_steps=args.steps, batch_size=args.batch_size, seq_len=args.seq_len, layers=l, model_size=d,
                       ffn_dim=f, dtype="bf16", device="cuda", backend="nccl", impl=args.ops, comm=args.comm,
-                      recompute=args.recompute, mp_mode=args.mp_mode)
-    from distributed_llm_code_samples_b200.engine import init_params_on_device
-    _, _, local0 = rank_world()
-    torch.cuda.set_device(local0)
-    params0 = init_params_on_device(cfg, torch.device("cuda", local0), seed=1234, scale=init_scale(d, f))
+                      recompute=recompute, mp_mode=args.mp_mode, fsdp_gather=args.fsdp_gather, mp_input=args.mp_input)
+    torch.cuda.set_device(local)
+    params0 = init_params_on_device(cfg, torch.device("cuda", local), seed=1234, scale=init_scale(d, f))
     eng = Engine(cfg, method=method, layers_params=params0)
     del params0
     dev = eng.device
@@ -164,51 +196,65 @@ def run_ours(args):
                "ms_per_step": wall_ms / args.steps, "h2d_bytes_per_step": eng.h2d_bytes // args.steps,
                "d2h_bytes_per_step": eng.d2h_bytes // args.steps, "last_metric": metrics[-1] if metrics else None}
 
+    detail = {"activations": "recompute" if recompute else "kept",
+              "gemms_per_block_step": 7 if recompute else 6,
+              "comm": getattr(eng.trainer, "comm_name", "nccl" if world > 1 else "none"), "ops": args.ops,
+              "torch_fallback_ops": getattr(eng.ops, "fallbacks", None),
+              "peak_mem_gib": round(torch.cuda.max_memory_allocated(dev) / 2 ** 30, 2)}
+    rec = record("ours", method, world, args, value, ms, clocks, e2e, launches,
+                 base_config(method if world > 1 else "single", world, d, f, l, args, eng.tokens_per_step_global), detail)
+    eng.close()
+    del eng, dev_pool, host_pool
+    gc.collect()
+    torch.cuda.empty_cache()
+    torch.cuda.reset_peak_memory_stats()
+    return rec
+
+
+def run_ours(args):
+    rank, world, _ = rank_world()
+    rec = ours_one(args, args.method, args.recompute)
+    also = {}
+    for m in also_methods(args):
+        if world == 1 and m == "fsdp" and args.method == "ddp":
+            # a world of one: FSDP and DDP are the same single-device loop on the same shape - not run twice
+            also[m] = {"same_run_as": "ddp", "value": rec["value"], "unit": rec["unit"], "ms_per_step": rec["ms_per_step"],
+                       "e2e": rec["e2e"], "clocks": rec["clocks"], "gpu_launches": rec["gpu_launches"], "config": rec["config"]}
+            continue
+        if m == "ddp_recompute":
+            also[m] = ours_one(args, "ddp", True)
+        else:
+            also[m] = ours_one(args, m, args.recompute)
+    if also:
+        rec["also"] = also
     if rank == 0:
-        par = {"single": "single", "ddp": f"dp{world}", "fsdp": f"fsdp{world}", "mp": f"tp{world}"}[method]
-        fallbacks = getattr(eng.ops, "fallbacks", None)
-        emit({"metric": f"ffn_stack_{method}_tokens_per_sec", "value": value, "unit": "tokens/s", "n_gpus": world,
-              "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-              "scaling": "weak" if method in ("ddp", "fsdp") else "strong", "vs_baseline": PUBLISHED_BASELINE,
-              "dtype": "bf16", "data": "synthetic", "impl": "ours",
-              "config": {"model": f"ffn_stack_d{d}_f{f}_l{l}_relu", "global_batch": eng.tokens_per_step_global,
-                         "seq_len": args.seq_len, "batch_size_per_rank": args.batch_size, "parallelism": par,
-                         "l2": "inputs (256 MiB/step) and weights (8 GiB) far exceed the 126 MB L2; batches cycle through a pool",
-                         "init": "variance-preserving scale (2/(D*F))^(1/4), same in both arms", "dloss_scale": DLOSS_SCALE,
-                         "activations": "recompute" if args.recompute else "kept", "comm": getattr(eng.trainer, "comm_name", "nccl" if world > 1 else "none"),
-                         "ops": args.ops, "torch_fallback_ops": fallbacks},
-              "clocks": clocks, "e2e": e2e, "gpu_launches": launches})
+        emit(rec)
 
 
 # ------------------------------------------------------------------------------------------------ reference
-def run_reference(args):
+def load_reference():
     ref_dir = os.path.join(ROOT, "baseline", "_ref")
     if not os.path.exists(os.path.join(ref_dir, "train_ffns.py")):
-        emit({"impl": "reference", "unavailable": "baseline/_ref/train_ffns.py missing (reference not installed)"})
-        return
-    rank, world, local = rank_world()
+        return None, "baseline/_ref/train_ffns.py missing (reference not installed)"
     if not torch.cuda.is_available():
-        emit({"impl": "reference", "unavailable": "no CUDA device"})
-        return
-    import torch.distributed as dist
+        return None, "no CUDA device"
     sys.path.insert(0, ref_dir)
     real_count = torch.cuda.device_count
     if real_count() == 1:       # the module refuses to import with exactly one visible GPU (train_ffns.py:26-27)
         torch.cuda.device_count = lambda: 2
     import train_ffns as ref    # UNMODIFIED reference module
     torch.cuda.device_count = real_count
-    ref.nGPUs = world           # it derives the world size from device_count at import (:25)
-    from distributed_llm_code_samples_b200.utils.clocks import ClockSampler
+    return ref, None
 
-    d, f, l = shape_defaults(args)
-    method = args.method
+
+def reference_one(args, ref, method):
+    """One strategy of the unmodified reference (its own per-rank function, its own H2D, its own collectives)."""
+    import gc
+    from distributed_llm_code_samples_b200.utils.clocks import ClockSampler
+    rank, world, local = rank_world()
+    d, f, l = shape_defaults(args, method)
     tokens = args.batch_size * args.seq_len
     dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("MASTER_PORT", "29500")
-        dist.init_process_group("nccl", rank=rank, world_size=world)
 
     g = torch.Generator(device=dev)
     g.manual_seed(1234)
@@ -228,6 +274,7 @@ def run_reference(args):
     if world == 1:
         fn = ref.train_1gpu
     state = {"params": params}
+    del params
 
     host_pool = make_host_pool(args.pool, tokens, d, 1000 * (rank if method in ("ddp", "fsdp") else 0))
     dev_pool = [(x.to(dev), dy.to(dev)) for x, dy in host_pool]
@@ -269,18 +316,47 @@ def run_reference(args):
         e2e = {"value": per_step_tokens * args.steps / (wall_ms * 1e-3), "unit": "tokens/s", "ms_per_step": wall_ms / args.steps,
                "h2d_bytes_per_step": 2 * tokens * d * 2, "d2h_bytes_per_step": int(peek.numel() * 4 / max(args.steps, 1))}
 
+    detail = {"activations": "recompute", "gemms_per_block_step": 7,
+              "comm": "NCCL via torch.distributed" if world > 1 else "none", "ops": "cuBLAS + ATen (torch)",
+              "note": "unmodified baseline/_ref/train_ffns.py per-rank function; mock_data yields the bf16 benchmark batches",
+              "final_param_finite": bool(torch.isfinite(state["params"][-1][0].float()).all().item()),
+              "peak_mem_gib": round(torch.cuda.max_memory_allocated(dev) / 2 ** 30, 2)}
+    rec = record("reference", method, world, args, value, ms, clocks, e2e, 0,
+                 base_config(method if world > 1 else "single", world, d, f, l, args, per_step_tokens), detail)
+    del state, dev_pool, host_pool
+    gc.collect()
+    torch.cuda.empty_cache()
+    torch.cuda.reset_peak_memory_stats()
+    return rec
+
+
+def run_reference(args):
+    ref, why = load_reference()
+    if ref is None:
+        emit({"impl": "reference", "unavailable": why})
+        return
+    import torch.distributed as dist
+    rank, world, local = rank_world()
+    ref.nGPUs = world           # it derives the world size from device_count at import (:25)
+    torch.cuda.set_device(torch.device("cuda", local))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        dist.init_process_group("nccl", rank=rank, world_size=world)
+    rec = reference_one(args, ref, args.method)
+    also = {}
+    for m in also_methods(args):
+        if m == "ddp_recompute":
+            continue                                  # the reference always recomputes (:63)
+        if world == 1 and m == "fsdp" and args.method == "ddp":
+            also[m] = {"same_run_as": "ddp", "value": rec["value"], "unit": rec["unit"], "ms_per_step": rec["ms_per_step"],
+                       "e2e": rec["e2e"], "clocks": rec["clocks"], "gpu_launches": 0, "config": rec["config"]}
+            continue
+        also[m] = reference_one(args, ref, m)
+    if also:
+        rec["also"] = also
     if rank == 0:
-        par = {"single": "single", "ddp": f"dp{world}", "fsdp": f"fsdp{world}", "mp": f"tp{world}"}[method if world > 1 else "single"]
-        emit({"metric": f"ffn_stack_{method}_tokens_per_sec", "value": value, "unit": "tokens/s", "n_gpus": world,
-              "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-              "scaling": "weak" if method in ("ddp", "fsdp") else "strong", "vs_baseline": PUBLISHED_BASELINE,
-              "dtype": "bf16", "data": "synthetic", "impl": "reference",
-              "config": {"model": f"ffn_stack_d{d}_f{f}_l{l}_relu", "global_batch": per_step_tokens, "seq_len": args.seq_len,
-                         "batch_size_per_rank": args.batch_size, "parallelism": par,
-                         "init": "variance-preserving scale (2/(D*F))^(1/4), same in both arms", "dloss_scale": DLOSS_SCALE,
-                         "note": "unmodified baseline/_ref/train_ffns.py per-rank function; mock_data yields the bf16 benchmark batches",
-                         "final_param_finite": bool(torch.isfinite(state["params"][-1][0].float()).all().item())},
-              "clocks": clocks, "e2e": e2e, "gpu_launches": 0})
+        emit(rec)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

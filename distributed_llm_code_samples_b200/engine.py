@@ -116,3 +116,19 @@ class Engine:
 
     def full_params(self) -> List[Params]:
         return self.trainer.full_params()
+
+    def close(self) -> None:
+        """Release the trainer and, with it, the symmetric memory of the fused paths (collective under > 1 rank), so that
+        another ``Engine`` can be built in the same process (bench.py measures DDP, FSDP and MP back to back)."""
+        import gc
+        self.trainer = None
+        self.comm = None
+        self._graphs = {}
+        gc.collect()
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        if self.device.type == "cuda":
+            from .parallel.symm import release_world
+            release_world()                    # no-op when no symmetric world was created
+        if self.device.type == "cuda":
+            torch.cuda.empty_cache()

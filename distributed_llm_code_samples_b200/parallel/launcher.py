@@ -8,8 +8,10 @@ tensors the parent allocated rather than CUDA-IPC views of parent-owned device m
 """
 from __future__ import annotations
 
+import multiprocessing.connection as mpc
 import os
 import socket
+import time
 import traceback
 from datetime import timedelta
 from typing import Any, Callable, Sequence
@@ -17,6 +19,9 @@ from typing import Any, Callable, Sequence
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
+
+
+PEER_GRACE_S = 5.0     # after the first failed rank, how long the others may keep running before they are terminated
 
 
 def free_port() -> int:
@@ -89,23 +94,45 @@ def launch(world: int, fn: Callable, args: Sequence[Any], backend: str = "auto",
         p = ctx.Process(target=_entry, args=(rank, world, backend, port, device, fn, tuple(args), errq))
         p.start()
         procs.append(p)
-    failed = []
-    for rank, p in enumerate(procs):
-        p.join(join_timeout_s)
-        if p.is_alive():
-            p.terminate()
-            failed.append((rank, "timeout"))
-        elif p.exitcode != 0:
-            failed.append((rank, f"exit code {p.exitcode}"))
-    if failed:
-        for p in procs:                     # do not leave peers blocked in a collective
-            if p.is_alive():
-                p.terminate()
-        tb = ""
+    # Wait on ALL ranks at once: a rank that dies while its peers are blocked in a collective must fail the launch now,
+    # not after the peers' own (NCCL / flag) timeouts.  The error queue is drained while waiting so that a child with a
+    # large traceback never blocks in put().
+    pending = {p.sentinel: (rank, p) for rank, p in enumerate(procs)}
+    deadline = time.monotonic() + join_timeout_s
+    failed, tbs = [], []
+
+    def drain() -> None:
         while not errq.empty():
             r, t = errq.get()
-            tb += f"\n--- rank {r} ---\n{t}"
-        raise RuntimeError(f"ranks failed: {failed}{tb}")
+            tbs.append(f"\n--- rank {r} ---\n{t}")
+
+    grace_until = None
+    while pending:
+        ready = mpc.wait(list(pending), timeout=0.5)
+        drain()
+        for s_ in ready:
+            rank, p = pending.pop(s_)
+            p.join()
+            if p.exitcode != 0:
+                failed.append((rank, f"exit code {p.exitcode}"))
+        now = time.monotonic()
+        if failed and grace_until is None:
+            grace_until = now + PEER_GRACE_S          # let the peers report their own tracebacks, briefly
+        if (grace_until is not None and now > grace_until) or now > deadline:
+            break
+    if pending:
+        for rank, p in pending.values():              # do not leave peers blocked in a collective
+            if now > deadline and not failed:
+                failed.append((rank, "timeout"))
+            if p.is_alive():
+                p.terminate()
+        for rank, p in pending.values():
+            p.join(10)
+            if p.is_alive():
+                p.kill()
+    drain()
+    if failed:
+        raise RuntimeError(f"ranks failed: {sorted(failed)}{''.join(tbs)}")
 
 
 def under_torchrun() -> bool:

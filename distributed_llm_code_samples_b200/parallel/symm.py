@@ -149,14 +149,22 @@ class SymmComm:
     """The strategies' collective interface on the native peer-memory kernels (bf16 payloads).
 
     Operands that already live in symmetric memory are used in place; others are staged through a symmetric
-    bounce buffer (one local copy in, one out)."""
+    bounce buffer (one local copy in, one out).
+
+    Two independent lanes: blocking calls run on the caller's current stream, ``async_op=True`` calls on ``self.side``.
+    Each lane has its OWN flag block, epoch counter and half of the staging buffer, so a caller may mix the two forms
+    freely (kernels of different lanes can overtake each other on the device without ever seeing each other's flags or
+    staging bytes).  Within a lane the order is the stream's.  All blocking calls must be issued on the same stream."""
 
     name = "b200-p2p"
 
     def __init__(self, sw: SymmWorld, staging_bytes: int = 64 << 20, group: Optional[dist.ProcessGroup] = None):
         self.sw, self.rank, self.world, self.group = sw, sw.rank, sw.world, group
-        self.chan = CollChannel(sw)
-        self.staging = sw.alloc(staging_bytes)
+        self.chans = (CollChannel(sw), CollChannel(sw))          # [0] blocking lane, [1] async (side-stream) lane
+        self.chan = self.chans[0]
+        half = (staging_bytes + 255) // 256 * 256
+        self.staging = sw.alloc(2 * half)
+        self._stage_half = half
         self.side = torch.cuda.Stream(device=sw.device)
         self.lib = nv.load()
 
@@ -182,9 +190,13 @@ class SymmComm:
                 return b
         return None
 
+    def _lane(self, async_op: bool):
+        """(channel, staging offset) of the lane a call runs in."""
+        return (self.chans[1], self._stage_half) if async_op else (self.chans[0], 0)
+
     def _stage_check(self, nbytes: int) -> None:
-        if nbytes > self.staging.nbytes:
-            raise ValueError(f"operand of {nbytes} bytes exceeds the symmetric staging buffer ({self.staging.nbytes}); "
+        if nbytes > self._stage_half:
+            raise ValueError(f"operand of {nbytes} bytes exceeds the symmetric staging buffer ({self._stage_half}); "
                              "allocate it with SymmWorld.alloc or raise staging_bytes")
 
     # ---- collectives ----------------------------------------------------------------------------------------
@@ -199,18 +211,19 @@ class SymmComm:
         fn = self.lib.b200_all_reduce_bf16 if es == 2 else self.lib.b200_all_reduce_f32
         nbytes = (t.numel() * es + 15) // 16 * 16
         buf = self._find(t)
-        e = self.chan.next_epoch()
+        chan, soff = self._lane(async_op)
+        e = chan.next_epoch()
         if buf is not None and (t.numel() * es) % 16 == 0:
             off = buf.offset_of(t)
-            return self._run(lambda s: nv._check(fn(buf.peers_c, off, nbytes, self.chan.flags.peers_c, self.rank, self.world, e, 0, s),
+            return self._run(lambda s: nv._check(fn(buf.peers_c, off, nbytes, chan.flags.peers_c, self.rank, self.world, e, 0, s),
                                                  "b200_all_reduce"), async_op)
         self._stage_check(nbytes)
-        st = self.staging.tensor(0, (nbytes // es,), t.dtype)
+        st = self.staging.tensor(soff, (nbytes // es,), t.dtype)
 
         def go(s):
             st[t.numel():].zero_()                                   # the padding lanes are summed too
             st[: t.numel()].copy_(t.reshape(-1))
-            nv._check(fn(self.staging.peers_c, 0, nbytes, self.chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_all_reduce")
+            nv._check(fn(self.staging.peers_c, soff, nbytes, chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_all_reduce")
             t.reshape(-1).copy_(st[: t.numel()])
         return self._run(go, async_op)
 
@@ -218,18 +231,19 @@ class SymmComm:
         assert out.is_contiguous() and shard.is_contiguous()
         sb = shard.numel() * shard.element_size()
         assert sb % 16 == 0, "shard size must be a multiple of 16 bytes"
-        e = self.chan.next_epoch()
+        chan, soff = self._lane(async_op)
+        e = chan.next_epoch()
         buf = self._find(shard)
         if buf is not None:
             off = buf.offset_of(shard)
-            return self._run(lambda s: nv._check(self.lib.b200_all_gather_into(out.data_ptr(), buf.peers_c, off, sb, self.chan.flags.peers_c,
+            return self._run(lambda s: nv._check(self.lib.b200_all_gather_into(out.data_ptr(), buf.peers_c, off, sb, chan.flags.peers_c,
                                                                               self.rank, self.world, e, 0, s), "b200_all_gather_into"), async_op)
         self._stage_check(sb)
-        st = self.staging.tensor(0, (sb,), torch.uint8)
+        st = self.staging.tensor(soff, (sb,), torch.uint8)
 
         def go(s):
             st.copy_(shard.reshape(-1).view(torch.uint8))
-            nv._check(self.lib.b200_all_gather_into(out.data_ptr(), self.staging.peers_c, 0, sb, self.chan.flags.peers_c,
+            nv._check(self.lib.b200_all_gather_into(out.data_ptr(), self.staging.peers_c, soff, sb, chan.flags.peers_c,
                                                     self.rank, self.world, e, 0, s), "b200_all_gather_into")
         return self._run(go, async_op)
 
@@ -239,7 +253,8 @@ class SymmComm:
         rs = self.lib.b200_reduce_scatter_bf16 if es == 2 else self.lib.b200_reduce_scatter_f32
         nbytes = full.numel() * es
         assert nbytes % (16 * self.world) == 0, "reduce_scatter needs bytes % (16*world) == 0"
-        e = self.chan.next_epoch()
+        chan, soff = self._lane(async_op)
+        e = chan.next_epoch()
         buf = self._find(full)
         sl = nbytes // self.world
 
@@ -247,15 +262,15 @@ class SymmComm:
             off = buf.offset_of(full)
 
             def go(s):
-                nv._check(rs(buf.peers_c, off, nbytes, self.chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_reduce_scatter")
+                nv._check(rs(buf.peers_c, off, nbytes, chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_reduce_scatter")
                 out.reshape(-1).copy_(full.reshape(-1)[self.rank * (sl // es): (self.rank + 1) * (sl // es)])
             return self._run(go, async_op)
         self._stage_check(nbytes)
-        st = self.staging.tensor(0, (nbytes // es,), full.dtype)
+        st = self.staging.tensor(soff, (nbytes // es,), full.dtype)
 
         def go2(s):
             st.copy_(full.reshape(-1))
-            nv._check(rs(self.staging.peers_c, 0, nbytes, self.chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_reduce_scatter")
+            nv._check(rs(self.staging.peers_c, soff, nbytes, chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_reduce_scatter")
             out.reshape(-1).copy_(st[self.rank * (sl // es): (self.rank + 1) * (sl // es)])
         return self._run(go2, async_op)
 
@@ -274,3 +289,12 @@ def get_symm_world(comm, device: torch.device) -> SymmWorld:
     if _WORLD is None:
         _WORLD = SymmWorld(comm.rank, comm.world, device, getattr(comm, "group", None))
     return _WORLD
+
+
+def release_world() -> None:
+    """Free every symmetric block of the process-wide world (collective: every rank calls it).  Tensors carved out of
+    the blocks must already be unreachable.  The next ``get_symm_world`` starts a fresh world."""
+    global _WORLD
+    if _WORLD is not None:
+        _WORLD.close()
+        _WORLD = None

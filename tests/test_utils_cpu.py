@@ -58,3 +58,23 @@ def test_benchmark_shapes_take_the_fused_paths_at_every_world_size():
             assert 0 < inbox <= 2 << 30, (method, world, inbox)
             grid = 148
             assert (cap + grid - 1) // grid <= 64, "owned tiles per CTA fit the done-counter scratch"
+
+
+def _crashing_rank(rank, world, dev):
+    import time
+    if rank == 1:
+        raise ValueError("boom from rank 1")
+    time.sleep(120)          # rank 0 'hangs in a collective'
+
+
+def test_launcher_fails_fast_when_a_peer_crashes():
+    """A crashed rank must fail the launch within seconds even though its peer is still blocked (the old
+    in-order join waited on rank 0 for up to an hour)."""
+    import time
+    import pytest
+    from distributed_llm_code_samples_b200.parallel.launcher import launch
+    t0 = time.monotonic()
+    with pytest.raises(RuntimeError) as ei:
+        launch(2, _crashing_rank, (), backend="gloo", device="cpu")
+    assert time.monotonic() - t0 < 60
+    assert "boom from rank 1" in str(ei.value) and "(1, 'exit code 1')" in str(ei.value)
