@@ -59,17 +59,115 @@ __global__ void __launch_bounds__(EW_THREADS) sgd_kernel(__nv_bfloat16* p, const
 }
 
 // ------------------------------------------------------------------ Adam
+// 8 elements per thread: one 16-byte load/store of the bf16 parameter, 16- or 32-byte loads of the gradient, two float4
+// each for the fp32 moments (26 bytes of traffic per element, all in full 32-byte sectors).
+__device__ __forceinline__ float adam_one(float w, float gr, float& m, float& v, float lr, float b1, float b2, float eps, float bc1, float bc2) {
+    m = b1 * m + (1.0f - b1) * gr;
+    v = b2 * v + (1.0f - b2) * gr * gr;
+    return w - lr * ((m / bc1) / (sqrtf(v / bc2) + eps));
+}
 __global__ void __launch_bounds__(EW_THREADS) adam_kernel(__nv_bfloat16* p, const void* g, float* m, float* v, long long n, float lr,
                                                           float b1, float b2, float eps, float bc1, float bc2, int grad_f32) {
+    const long long n8 = n / 8;
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint4* pv = reinterpret_cast<uint4*>(p);
+    float4* mv = reinterpret_cast<float4*>(m);
+    float4* vv = reinterpret_cast<float4*>(v);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+        float w[8], gr[8];
+        unpack8(pv[i], w);
+        load_grad8(g, i, grad_f32 != 0, gr);
+        const float4 m0 = mv[2 * i], m1 = mv[2 * i + 1], v0 = vv[2 * i], v1 = vv[2 * i + 1];
+        float mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+        float vs[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) w[j] = adam_one(w[j], gr[j], mm[j], vs[j], lr, b1, b2, eps, bc1, bc2);
+        mv[2 * i] = make_float4(mm[0], mm[1], mm[2], mm[3]); mv[2 * i + 1] = make_float4(mm[4], mm[5], mm[6], mm[7]);
+        vv[2 * i] = make_float4(vs[0], vs[1], vs[2], vs[3]); vv[2 * i + 1] = make_float4(vs[4], vs[5], vs[6], vs[7]);
+        pv[i] = pack8(w);
+    }
+    for (long long i = n8 * 8 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {   // scalar tail
         const float gr = grad_f32 ? reinterpret_cast<const float*>(g)[i] : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(g)[i]);
-        const float mi = b1 * m[i] + (1.0f - b1) * gr;
-        const float vi = b2 * v[i] + (1.0f - b2) * gr * gr;
+        float mi = m[i], vi = v[i];
+        p[i] = __float2bfloat16_rn(adam_one(__bfloat162float(p[i]), gr, mi, vi, lr, b1, b2, eps, bc1, bc2));
         m[i] = mi;
         v[i] = vi;
-        const float upd = (mi / bc1) / (sqrtf(vi / bc2) + eps);
-        p[i] = __float2bfloat16_rn(__bfloat162float(p[i]) - lr * upd);
+    }
+}
+
+// ------------------------------------------------------------------ fp32 parameters (biases are kept in fp32)
+// OPT 0: p -= lr * g     OPT 1: Adam.  Scalar accesses: these vectors are a few thousand elements.
+template <int OPT>
+__global__ void __launch_bounds__(EW_THREADS) opt_f32_kernel(float* p, const float* g, float* m, float* v, long long n, float lr,
+                                                             float b1, float b2, float eps, float bc1, float bc2) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        if constexpr (OPT == 0) {
+            p[i] -= lr * g[i];
+        } else {
+            float mi = m[i], vi = v[i];
+            p[i] = adam_one(p[i], g[i], mi, vi, lr, b1, b2, eps, bc1, bc2);
+            m[i] = mi;
+            v[i] = vi;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ column sums (bias gradient: db = sum_t dy[t, :])
+// Stage 1: CTA (cb, rc) sums rows [rc * rows_per_chunk, ...) of columns [cb * 256, +256): thread = (8-column group, row
+// lane); 16-byte loads, whole 512-byte row segments per warp-pair.  Stage 2: one thread per column adds the chunk
+// partials in a fixed order (deterministic).  HBM-bound: reads the matrix once.
+constexpr int CS_COLS = 256, CS_ROWLANES = EW_THREADS / (CS_COLS / 8);   // 32 column groups x 8 row lanes
+__global__ void __launch_bounds__(EW_THREADS) colsum_partial_kernel(float* partial, const __nv_bfloat16* x, long long ld, int T, int N,
+                                                                    int rows_per_chunk) {
+    __shared__ float sh[CS_ROWLANES][CS_COLS + 8];
+    const int cg = threadIdx.x & 31, rl = threadIdx.x >> 5;
+    const int col = blockIdx.x * CS_COLS + cg * 8;
+    const int r0 = blockIdx.y * rows_per_chunk, r1 = min(T, r0 + rows_per_chunk);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (col < N) {
+        for (int r = r0 + rl; r < r1; r += CS_ROWLANES) {
+            float f[8];
+            unpack8(ld_nc_u4(x + (long long)r * ld + col), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sh[rl][cg * 8 + j] = acc[j];
+    __syncthreads();
+    const int c = threadIdx.x;                                        // 256 threads = 256 columns
+    if (blockIdx.x * CS_COLS + c < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < CS_ROWLANES; ++k) t += sh[k][c];
+        partial[(long long)blockIdx.y * N + blockIdx.x * CS_COLS + c] = t;
+    }
+}
+__global__ void __launch_bounds__(EW_THREADS) colsum_final_kernel(float* out, const float* partial, int N, int chunks, int accumulate) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= N) return;
+    float t = accumulate ? out[c] : 0.f;
+    for (int k = 0; k < chunks; ++k) t += partial[(long long)k * N + c];
+    out[c] = t;
+}
+
+// ------------------------------------------------------------------ out[t, :] = bias (+ residual[t, :])
+// Pre-fills the output of a fused row-parallel GEMM + all-reduce whose in-place mode then adds the cross-rank sum.
+__global__ void __launch_bounds__(EW_THREADS) bias_rows_kernel(__nv_bfloat16* out, long long ldo, const __nv_bfloat16* res, long long ldr,
+                                                               const float* bias, int T, int N) {
+    const int n8 = N / 8;
+    const long long total = (long long)T * n8;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const int t = (int)(i / n8), c = (int)(i % n8) * 8;
+        float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (res != nullptr) unpack8(*reinterpret_cast<const uint4*>(res + (long long)t * ldr + c), f);
+        if (bias != nullptr) {
+            const float4 b0 = *reinterpret_cast<const float4*>(bias + c), b1 = *reinterpret_cast<const float4*>(bias + c + 4);
+            f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w; f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+        }
+        *reinterpret_cast<uint4*>(out + (long long)t * ldo + c) = pack8(f);
     }
 }
 
@@ -255,9 +353,66 @@ extern "C" int b200_adam_bf16(void* param, const void* grad, float* m, float* v,
                               float eps, int step, int grad_f32, void* stream) {
     if (n <= 0) return 0;
     if (param == nullptr || grad == nullptr || m == nullptr || v == nullptr || step < 1) { set_last_error("adam: bad arguments"); return B200_ERR_ARG; }
+    if (int rc = check_ptr16(param, "adam param")) return rc;
+    if (int rc = check_ptr16(grad, "adam grad")) return rc;
+    if (int rc = check_ptr16(m, "adam m")) return rc;
+    if (int rc = check_ptr16(v, "adam v")) return rc;
     const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
-    adam_kernel<<<ew_grid(n), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(param), grad, m, v, n, lr, beta1, beta2, eps, bc1, bc2, grad_f32);
+    adam_kernel<<<ew_grid(n / 8 + 1), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(param), grad, m, v, n, lr, beta1, beta2, eps, bc1, bc2, grad_f32);
     return check_cuda(cudaGetLastError(), "adam launch");
+}
+
+extern "C" int b200_sgd_f32(float* param, const float* grad, long long n, float lr, void* stream) {
+    if (n <= 0) return 0;
+    if (param == nullptr || grad == nullptr) { set_last_error("sgd_f32: null pointer"); return B200_ERR_ARG; }
+    opt_f32_kernel<0><<<ew_grid(n), EW_THREADS, 0, ST(stream)>>>(param, grad, nullptr, nullptr, n, lr, 0.f, 0.f, 0.f, 1.f, 1.f);
+    return check_cuda(cudaGetLastError(), "sgd_f32 launch");
+}
+
+extern "C" int b200_adam_f32(float* param, const float* grad, float* m, float* v, long long n, float lr, float beta1, float beta2,
+                             float eps, int step, void* stream) {
+    if (n <= 0) return 0;
+    if (param == nullptr || grad == nullptr || m == nullptr || v == nullptr || step < 1) { set_last_error("adam_f32: bad arguments"); return B200_ERR_ARG; }
+    const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
+    opt_f32_kernel<1><<<ew_grid(n), EW_THREADS, 0, ST(stream)>>>(param, grad, m, v, n, lr, beta1, beta2, eps, bc1, bc2);
+    return check_cuda(cudaGetLastError(), "adam_f32 launch");
+}
+
+// chunks of rows such that the first stage launches about 4 CTAs per SM
+static int colsum_chunks(int T, int N) {
+    const int col_blocks = (N + CS_COLS - 1) / CS_COLS;
+    int chunks = (num_sms() * 4 + col_blocks - 1) / col_blocks;
+    const int max_chunks = (T + 63) / 64;                             // at least 64 rows per chunk
+    if (chunks > max_chunks) chunks = max_chunks;
+    return chunks < 1 ? 1 : chunks;
+}
+extern "C" long long b200_colsum_scratch_bytes(int T, int N) { return (long long)colsum_chunks(T, N) * N * 4; }
+
+extern "C" int b200_colsum_bf16(float* out, const void* x, long long ld, int T, int N, int accumulate, void* scratch,
+                                long long scratch_bytes, void* stream) {
+    if (T <= 0 || N <= 0) return 0;
+    if (out == nullptr || scratch == nullptr) { set_last_error("colsum: null out/scratch"); return B200_ERR_ARG; }
+    if (int rc = check_ptr16(x, "colsum x")) return rc;
+    if (N % 8 || ld % 8 || ld < N) { set_last_error("colsum: N and ld must be multiples of 8 and ld >= N"); return B200_ERR_ARG; }
+    if (scratch_bytes < b200_colsum_scratch_bytes(T, N)) { set_last_error("colsum: scratch must hold %lld bytes", b200_colsum_scratch_bytes(T, N)); return B200_ERR_ARG; }
+    const int chunks = colsum_chunks(T, N);
+    const int rows_per_chunk = (T + chunks - 1) / chunks;
+    dim3 grid((N + CS_COLS - 1) / CS_COLS, chunks);
+    colsum_partial_kernel<<<grid, EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<float*>(scratch), reinterpret_cast<const __nv_bfloat16*>(x), ld, T, N, rows_per_chunk);
+    if (int rc = check_cuda(cudaGetLastError(), "colsum partial launch")) return rc;
+    colsum_final_kernel<<<(N + EW_THREADS - 1) / EW_THREADS, EW_THREADS, 0, ST(stream)>>>(out, reinterpret_cast<const float*>(scratch), N, chunks, accumulate);
+    return check_cuda(cudaGetLastError(), "colsum final launch");
+}
+
+extern "C" int b200_bias_rows_bf16(void* out, long long ldo, const void* residual, long long ldr, const float* bias, int T, int N, void* stream) {
+    if (T <= 0 || N <= 0) return 0;
+    if (int rc = check_ptr16(out, "bias_rows out")) return rc;
+    if (residual != nullptr) { if (int rc = check_ptr16(residual, "bias_rows residual")) return rc; }
+    if (bias != nullptr) { if (int rc = check_ptr16(bias, "bias_rows bias")) return rc; }
+    if (N % 8 || ldo % 8 || (residual != nullptr && ldr % 8)) { set_last_error("bias_rows: N and pitches must be multiples of 8"); return B200_ERR_ARG; }
+    bias_rows_kernel<<<ew_grid((long long)T * (N / 8)), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(out), ldo,
+        reinterpret_cast<const __nv_bfloat16*>(residual), ldr, bias, T, N);
+    return check_cuda(cudaGetLastError(), "bias_rows launch");
 }
 
 extern "C" int b200_relu_bf16(void* out, const void* x, long long n, void* stream) {

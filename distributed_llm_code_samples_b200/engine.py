@@ -37,7 +37,7 @@ def init_params_on_device(cfg: TrainConfig, device: torch.device, seed: int = 12
         w2 = (scale * torch.randn((cfg.model_size, cfg.ffn_dim), generator=g, device=device)).to(dtype)
         lp = [w1, w2]
         if cfg.bias:
-            lp += [torch.zeros(cfg.ffn_dim, dtype=dtype, device=device), torch.zeros(cfg.model_size, dtype=dtype, device=device)]
+            lp += [torch.zeros(cfg.ffn_dim, dtype=torch.float32, device=device), torch.zeros(cfg.model_size, dtype=torch.float32, device=device)]
         out.append(lp)
     return out
 

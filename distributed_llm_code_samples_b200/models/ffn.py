@@ -33,7 +33,7 @@ def init_linear_layer(m: int, n: int, gen: Optional[torch.Generator], scale: flo
 def init_tlayer_ffn(emb_dim: int, ffn_dim: int, gen: Optional[torch.Generator], bias: bool = False) -> Params:
     p = [init_linear_layer(emb_dim, ffn_dim, gen), init_linear_layer(ffn_dim, emb_dim, gen)]
     if bias:
-        p += [torch.zeros(ffn_dim), torch.zeros(emb_dim)]
+        p += [torch.zeros(ffn_dim), torch.zeros(emb_dim)]          # fp32, and kept fp32 on every path
     return p
 
 
@@ -137,7 +137,8 @@ def tlayer_ffn_bkwd(ops, dy: torch.Tensor, p: Params, saved: Saved, opts: BlockO
 
     The input-gradient GEMM of each linear is issued BEFORE its weight-gradient GEMM so that, when
     ``update_lr`` is given, the weight can be updated in place inside the dW GEMM's epilogue (``W -= lr dW``,
-    one kernel, no gradient tensor) - the returned grads are then ``None``.  ``need_dx=False`` skips the
+    one kernel, no gradient tensor) - the returned weight grads are then ``None`` (with bias: ``(None, None, db1, db2)``,
+    without: ``None``).  Biases are fp32 whatever the weights' dtype, and so are their gradients.  ``need_dx=False`` skips the
     layer-0 input gradient the reference computes and discards (``:88``).
     """
     with block_range("ffn_bwd"):
@@ -153,7 +154,7 @@ def _tlayer_ffn_bkwd(ops, dy, p, saved, opts, need_dx, update_lr):
     aux = (pre if pre is not None else a) if opts.activation == "relu" else pre
     dh = ops.grad_input(dy, p[1], act=opts.activation, aux=aux)            # da then activation backward (:66-67)
     has_bias = len(p) == 4
-    fused = update_lr is not None and not has_bias
+    fused = update_lr is not None            # weights updated in the dW GEMM's epilogue; bias gradients are still returned
     if fused:
         ops.grad_weight_sgd_(p[1], dy, a, update_lr)
         dW2 = None
@@ -164,12 +165,12 @@ def _tlayer_ffn_bkwd(ops, dy, p, saved, opts, need_dx, update_lr):
         dx = ops.grad_input(dh, p[0], add=dy if opts.residual else None)   # (:68)
     if fused:
         ops.grad_weight_sgd_(p[0], dh, x, update_lr)
-        return dx, None
-    dW1 = ops.grad_weight(dh, x)                                           # (:68)
-    grads: LayerGrads = (dW1, dW2)
+        dW1 = None
+    else:
+        dW1 = ops.grad_weight(dh, x)                                       # (:68)
     if has_bias:
-        grads = (dW1, dW2, ops.grad_bias(dh), ops.grad_bias(dy))
-    return dx, grads
+        return dx, (dW1, dW2, ops.grad_bias(dh), ops.grad_bias(dy))
+    return dx, (None if fused else (dW1, dW2))
 
 
 # ------------------------------------------------------------------------------------------- stack fwd / bwd

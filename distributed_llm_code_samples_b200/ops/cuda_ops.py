@@ -34,6 +34,13 @@ class CudaOps(TorchOps):
                 return False
         return True
 
+    @staticmethod
+    def _bias32(bias: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        """The epilogues take an fp32 bias vector; biases are stored fp32, so this is normally the tensor itself."""
+        if bias is None or (bias.dtype == torch.float32 and bias.is_contiguous()):
+            return bias
+        return bias.float().contiguous()
+
     def _fb(self):
         self.fallbacks += 1
         return super()
@@ -45,7 +52,7 @@ class CudaOps(TorchOps):
         if not self._ok(x, W) or N % 8:
             return self._fb().linear_act(x, W, act, bias)
         a = torch.empty(T, N, dtype=torch.bfloat16, device=x.device)
-        b32 = None if bias is None else bias.float().contiguous()
+        b32 = self._bias32(bias)
         if act == "relu":
             if self.relu_mask and N % 128 == 0:
                 # also emit the packed sign mask (1 bit/element): the backward reads 1/16 of the bytes of `a`
@@ -64,7 +71,7 @@ class CudaOps(TorchOps):
         if not self._ok(a, W, residual) or N % 8:
             return self._fb().linear(a, W, bias, residual)
         y = torch.empty(T, N, dtype=torch.bfloat16, device=a.device) if out is None else out
-        b32 = None if bias is None else bias.float().contiguous()
+        b32 = self._bias32(bias)
         if residual is not None:
             nv.gemm(a, nv.MAJOR_K, W, nv.MAJOR_K, y, T, N, K, nv.EPI_ADD, aux=residual, bias=b32, max_ctas=self.max_ctas)
         else:
@@ -112,8 +119,17 @@ class CudaOps(TorchOps):
             return self._fb().grad_weight_sgd_(W, dy, x, lr)
         nv.gemm(dy, nv.MAJOR_MN, x, nv.MAJOR_MN, W, M, N, T, nv.EPI_SGD, alpha=lr, max_ctas=self.max_ctas)
 
+    def grad_bias(self, dy: torch.Tensor) -> torch.Tensor:
+        """``db = dy.sum(0)`` in fp32: the native two-stage column sum (reads ``dy`` once)."""
+        if self._ok(dy) and dy.shape[1] % 8 == 0:
+            return nv.colsum(dy)
+        return self._fb().grad_bias(dy)
+
     # ---- optimizer ---------------------------------------------------------------------------------------
     def sgd_(self, p, g, lr) -> None:
+        if p.is_cuda and p.dtype == torch.float32 and g.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous():
+            nv.sgd_f32_(p, g, lr)           # fp32 parameters: the biases
+            return
         if p.is_cuda and p.dtype == torch.bfloat16 and p.is_contiguous() and g.is_contiguous() \
                 and g.dtype in (torch.bfloat16, torch.float32) and p.data_ptr() % 16 == 0 and g.data_ptr() % 16 == 0:
             nv.sgd_(p, g, lr)
@@ -121,6 +137,9 @@ class CudaOps(TorchOps):
             self._fb().sgd_(p, g, lr)
 
     def adam_(self, p, g, m, v, lr, beta1, beta2, eps, step) -> None:
+        if p.is_cuda and p.dtype == torch.float32 and g.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous():
+            nv.adam_f32_(p, g, m, v, lr, beta1, beta2, eps, step)
+            return
         if p.is_cuda and p.dtype == torch.bfloat16 and p.is_contiguous() and g.is_contiguous() \
                 and g.dtype in (torch.bfloat16, torch.float32):
             nv.adam_(p, g, m, v, lr, beta1, beta2, eps, step)

@@ -127,6 +127,11 @@ def _optional_declare(lib) -> None:
         "b200_gather_gemm_bf16": ([pp, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp], i),
         "b200_debug_gather_chunk": ([i, i, i, i, ll, C.POINTER(ll)], i),
         "b200_fused_config": ([i, i], i),
+        "b200_sgd_f32": ([vp, vp, ll, f, vp], i),
+        "b200_adam_f32": ([vp, vp, vp, vp, ll, f, f, f, f, i, vp], i),
+        "b200_colsum_scratch_bytes": ([i, i], ll),
+        "b200_colsum_bf16": ([vp, vp, ll, i, i, i, vp, ll, vp], i),
+        "b200_bias_rows_bf16": ([vp, ll, vp, ll, vp, i, i, vp], i),
         "b200_emu_table_bytes": ([], ll),
         "b200_emu_gemm_allreduce_bf16": ([i, pp, ll, i, pp, ll, i, i, i, i, pp, ll, pp, pp, i, i, u, i, i, i, f,
                                          pp, pp, f, f, f, f, i, f, i, vp, vp], i),
@@ -203,6 +208,55 @@ def adam_(param: torch.Tensor, grad: torch.Tensor, m: torch.Tensor, v: torch.Ten
                                  float(lr), float(beta1), float(beta2), float(eps), int(step),
                                  int(grad.dtype == torch.float32), _stream()), "b200_adam_bf16")
     launch_count += 1
+
+
+def sgd_f32_(param: torch.Tensor, grad: torch.Tensor, lr: float) -> None:
+    global launch_count
+    assert param.dtype == torch.float32 and grad.dtype == torch.float32 and param.is_contiguous() and grad.is_contiguous()
+    _check(load().b200_sgd_f32(param.data_ptr(), grad.data_ptr(), param.numel(), float(lr), _stream()), "b200_sgd_f32")
+    launch_count += 1
+
+
+def adam_f32_(param: torch.Tensor, grad: torch.Tensor, m: torch.Tensor, v: torch.Tensor, lr: float, beta1: float, beta2: float,
+              eps: float, step: int) -> None:
+    global launch_count
+    assert param.dtype == torch.float32 and grad.dtype == torch.float32 and m.dtype == torch.float32 and v.dtype == torch.float32
+    _check(load().b200_adam_f32(param.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), param.numel(), float(lr),
+                                float(beta1), float(beta2), float(eps), int(step), _stream()), "b200_adam_f32")
+    launch_count += 1
+
+
+_colsum_scratch: dict = {}
+
+
+def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
+    """``out[n] (+)= sum_t x[t, n]`` (fp32) for a bf16 ``[T, N]`` matrix - the bias gradient."""
+    global launch_count
+    assert x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
+    T, N = x.shape
+    lib = load()
+    need = int(lib.b200_colsum_scratch_bytes(T, N))
+    key = x.device.index or 0
+    sc = _colsum_scratch.get(key)
+    if sc is None or sc.numel() < need:
+        sc = _colsum_scratch[key] = torch.empty(max(need, 1 << 20), dtype=torch.uint8, device=x.device)
+    if out is None:
+        out = torch.empty(N, dtype=torch.float32, device=x.device)
+        accumulate = False
+    _check(lib.b200_colsum_bf16(out.data_ptr(), x.data_ptr(), x.stride(0), T, N, int(accumulate), sc.data_ptr(), sc.numel(), _stream()),
+           "b200_colsum_bf16")
+    launch_count += 2
+    return out
+
+
+def bias_rows_(out: torch.Tensor, bias: Optional[torch.Tensor], residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``out[t, :] = bias (+ residual[t, :])`` (bf16 out / residual, fp32 bias)."""
+    global launch_count
+    T, N = out.shape
+    _check(load().b200_bias_rows_bf16(out.data_ptr(), out.stride(0), _ptr(residual), residual.stride(0) if residual is not None else 0,
+                                      _ptr(bias), T, N, _stream()), "b200_bias_rows_bf16")
+    launch_count += 1
+    return out
 
 
 def relu(x: torch.Tensor) -> torch.Tensor:

@@ -52,7 +52,7 @@ def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Seque
     if method == "fsdp":
         shards = [[fsdp_shard(p, r, n) for p in lp] for lp in layers_params]
         if cfg.comm in ("auto", "fused") and _fused_available(ops, comm, cfg, "fsdp"):
-            if cfg.fsdp_gather == "fused" and cfg.tokens % 8 == 0:
+            if cfg.fsdp_gather == "fused" and cfg.tokens % 8 == 0 and not cfg.bias:   # (transposed activations: a per-row bias has no epilogue yet)
                 # parameter all-gather inside the consuming GEMMs, forward and backward
                 from .fused_fsdp_t import FusedFSDPGatherTrainer
                 return FusedFSDPGatherTrainer(ops, comm, cfg, place(shards, device, dtype), device)
@@ -69,12 +69,12 @@ def build_trainer(method: str, ops, comm, cfg: TrainConfig, layers_params: Seque
 
 
 def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
-    """The peer-memory fused kernels need the native ops, bf16, >1 rank, SGD, no bias and TMA-legal shapes
-    (FSDP additionally needs every row shard to be a whole number of 128-row tiles)."""
+    """The peer-memory fused kernels need the native ops, bf16, >1 rank and TMA-legal shapes (FSDP additionally needs
+    every row shard to be a whole number of 128-row tiles).  SGD or Adam, ReLU or GELU, with or without bias / residual."""
     # Adam: inside the kernel for DDP / FSDP (the tile owner applies it and owns the moments); MP: fused collectives + the
     # native Adam kernel on the shard-local dW.
     ok = (getattr(ops, "name", "") == "native" and comm.world > 1 and cfg.dtype in ("bf16", "bfloat16")
-          and not cfg.bias and cfg.model_size % 8 == 0 and cfg.ffn_dim % 8 == 0)
+          and cfg.model_size % 8 == 0 and cfg.ffn_dim % 8 == 0)
     if method == "fsdp":
         ok = ok and cfg.model_size % (128 * comm.world) == 0 and cfg.ffn_dim % (128 * comm.world) == 0
     if method == "mp":
@@ -86,7 +86,7 @@ def _fused_available(ops, comm, cfg: TrainConfig, method: str = "ddp") -> bool:
             ok = ok and cfg.model_size % 64 == 0
     if not ok:
         if cfg.comm == "fused":
-            raise RuntimeError("comm=fused needs impl=native, bf16, no bias, world>1, dims % 8 == 0 "
+            raise RuntimeError("comm=fused needs impl=native, bf16, world>1, dims % 8 == 0 "
                                "(FSDP: dims % (128*world) == 0; MP sp forms: tokens % (128*world) == 0)")
         return False
     try:

@@ -27,7 +27,9 @@ class Optimizer:
     def begin_step(self) -> None:
         self.t += 1
 
-    def update(self, key: int, p: torch.Tensor, g: torch.Tensor) -> None:
+    def update(self, key: int, p: torch.Tensor, g: Optional[torch.Tensor]) -> None:
+        if g is None:                      # already applied inside the GEMM that produced it
+            return
         if self.kind == "sgd":
             self.ops.sgd_(p, g, self.lr)
             return
@@ -69,4 +71,6 @@ def tp_shard(p: torch.Tensor, index_in_layer: int, rank: int, world: int) -> tor
 
 def place(layers_params: Sequence[Params], device: torch.device, dtype: torch.dtype) -> List[Params]:
     # copy=True: on CPU the inputs are the parent's shared-memory tensors; every rank needs a PRIVATE replica
-    return [[p.to(device=device, dtype=dtype, copy=True).contiguous() for p in lp] for lp in layers_params]
+    # biases (index 2, 3) stay fp32: the GEMM epilogues take fp32 bias vectors and the bias gradients are fp32 sums
+    return [[p.to(device=device, dtype=dtype if j < 2 else torch.float32, copy=True).contiguous() for j, p in enumerate(lp)]
+            for lp in layers_params]

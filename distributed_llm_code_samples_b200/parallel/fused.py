@@ -104,7 +104,7 @@ class GatherChannel:
 
     def gemm(self, a_peers, B: torch.Tensor, b_major: int, out: torch.Tensor, M: int, N: int, K: int, epilogue: int,
              aux: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None, max_ctas: int = 0,
-             a_major: int = nv.MAJOR_K) -> torch.Tensor:
+             a_major: int = nv.MAJOR_K, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
         """``out = epilogue(A_full @ B^T)``; ``a_peers[q]`` = rank q's buffer holding its row shard of A: ``[M, K]`` sharded
         along M (``a_major`` K) or ``[K, M]`` sharded along K (``a_major`` MN)."""
         rows = M if a_major == nv.MAJOR_K else K
@@ -114,10 +114,55 @@ class GatherChannel:
         rc = nv.load().b200_gather_gemm_bf16(
             a_peers, a_major, B.data_ptr(), B.stride(0), b_major, out.data_ptr(), out.stride(0), M, N, K, epilogue,
             nv._ptr(aux), aux.stride(0) if aux is not None else 0, nv._ptr(out2), out2.stride(0) if out2 is not None else 0,
-            None, 1.0, self.started.peers_c, self.ready.data_ptr(), sw.rank, sw.world, self.seq, int(max_ctas), nv._stream())
+            nv._ptr(bias), 1.0, self.started.peers_c, self.ready.data_ptr(), sw.rank, sw.world, self.seq, int(max_ctas), nv._stream())
         nv._check(rc, "b200_gather_gemm_bf16")
         nv.launch_count += 1
         return out
+
+
+class _ReplicatedBiases:
+    """Biases of a data-parallel stack under the fused trainers: replicated fp32 vectors (a few KiB per layer) in ONE
+    contiguous tensor, their gradients (native column sums of ``dh`` / ``dy``) in one symmetric fp32 buffer, so a step
+    costs one native all-reduce and one optimizer kernel for all layers together.  The reference has no bias
+    (``train_ffns.py:35``); this is the north-star block's."""
+
+    def __init__(self, sw: SymmWorld, cfg: TrainConfig, biases: List[Tuple[torch.Tensor, torch.Tensor]], device: torch.device):
+        F, D, L = cfg.ffn_dim, cfg.model_size, len(biases)
+        self.sw, self.L = sw, L
+        self.n = L * (F + D)
+        self.values = torch.empty(self.n, dtype=torch.float32, device=device)
+        self.gbuf = sw.alloc(self.n * 4 + 256)
+        self.grads, self.goff = self.gbuf.carve((self.n,), torch.float32)
+        self.coll = CollChannel(sw)
+        self.b1, self.b2, self.g1, self.g2 = [], [], [], []
+        for l, (b1, b2) in enumerate(biases):
+            o = l * (F + D)
+            self.b1.append(self.values[o:o + F]); self.b2.append(self.values[o + F:o + F + D])
+            self.g1.append(self.grads[o:o + F]); self.g2.append(self.grads[o + F:o + F + D])
+            self.b1[l].copy_(b1.to(device=device, dtype=torch.float32))
+            self.b2[l].copy_(b2.to(device=device, dtype=torch.float32))
+        self.adam = cfg.optimizer == "adam"
+        self.lr = cfg.lr * cfg.grad_scale
+        if self.adam:
+            self.m, self.v = torch.zeros_like(self.values), torch.zeros_like(self.values)
+
+    def accumulate(self, l: int, dh: torch.Tensor, dy: torch.Tensor) -> None:
+        """This rank's bias gradients of layer ``l``: db1 = dh.sum(0), db2 = dy.sum(0) (native column sums)."""
+        nv.colsum(dh, out=self.g1[l])
+        nv.colsum(dy, out=self.g2[l])
+
+    def reduce_and_update(self, step: int) -> None:
+        """SUM over ranks (train_ffns.py:165 semantics) on the native peer-memory all-reduce, then one optimizer kernel."""
+        sw = self.sw
+        if sw.world > 1:
+            nbytes = (self.n * 4 + 15) // 16 * 16
+            nv._check(nv.load().b200_all_reduce_f32(self.gbuf.peers_c, self.goff, nbytes, self.coll.flags.peers_c, sw.rank, sw.world,
+                                                    self.coll.next_epoch(), 0, nv._stream()), "b200_all_reduce_f32 (bias gradients)")
+            nv.launch_count += 1
+        if self.adam:
+            nv.adam_f32_(self.values, self.grads, self.m, self.v, self.lr, 0.9, 0.999, 1e-8, step)
+        else:
+            nv.sgd_f32_(self.values, self.grads, self.lr)
 
 
 # =================================================================================================== DDP
@@ -140,6 +185,11 @@ class FusedDDPTrainer:
             w2.copy_(lp[1].to(device=device, dtype=torch.bfloat16))
             self.params.append([w1, w2])
             self.offsets.append((o1, o2))
+        self.biases: Optional[_ReplicatedBiases] = None
+        if len(layers_params[0]) == 4:
+            self.biases = _ReplicatedBiases(self.sw, cfg, [(lp[2], lp[3]) for lp in layers_params], device)
+            for l, p in enumerate(self.params):
+                p += [self.biases.b1[l], self.biases.b2[l]]
         self.peer_tabs = [(self.wbuf.peers_at(o1), self.wbuf.peers_at(o2)) for o1, o2 in self.offsets]
         shapes = [(F, D), (D, F)]
         self.chan = FusedChannel(self.sw, _owned_cap(shapes, comm.world, OWN_INTERLEAVED), max(_tiles(*s) for s in shapes))
@@ -167,18 +217,22 @@ class FusedDDPTrainer:
         d = dloss_dx
         T = x.shape[0]
         for i in reversed(range(len(self.params))):
-            W1, W2 = self.params[i]
+            W1, W2 = self.params[i][:2]
             s = acts[i]
             a, pre = s.a, s.pre
             if a is None:
-                a, pre = ops.linear_act(s.x, W1, self.opts.activation)
+                a, pre = ops.linear_act(s.x, W1, self.opts.activation, self.params[i][2] if self.biases else None)
             dh = ops.grad_input(d, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
+            if self.biases:
+                self.biases.accumulate(i, dh, d)
             # dW2 = d^T a  summed over ranks, W2 -= lr * dW2, new W2 stored to every replica - one kernel
             self._update(i, 1, d, a, D, F, T)
             dn = ops.grad_input(dh, W1, add=d if self.opts.residual else None) if i > 0 else None
             self._update(i, 0, dh, s.x, F, D, T)
             acts[i] = None
             d = dn
+        if self.biases:
+            self.biases.reduce_and_update(self.t)
         return y
 
     def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor]]) -> None:
@@ -212,9 +266,23 @@ class FusedFSDPTrainer:
             w2.copy_(lp[1])
             self.shards.append([w1, w2])
             self.shard_off.append((o1, o2))
+        # biases: replicated (they are tiny), exposed to the driver as dim-0 shards like every other parameter (:265-266)
+        self.biases: Optional[_ReplicatedBiases] = None
+        if len(shards[0]) == 4:
+            fullb = []
+            for lp in shards:
+                pair = []
+                for b in lp[2:]:
+                    fb = torch.empty(b.numel() * n, dtype=torch.float32, device=device)
+                    comm.all_gather_into(fb, b.to(device=device, dtype=torch.float32).contiguous())
+                    pair.append(fb)
+                fullb.append(tuple(pair))
+            self.biases = _ReplicatedBiases(self.sw, cfg, fullb, device)
+            for l, sh in enumerate(self.shards):
+                sh += [self.biases.b1[l].chunk(n)[self.rank], self.biases.b2[l].chunk(n)[self.rank]]
         self.full = [[torch.empty(F, D, dtype=torch.bfloat16, device=device), torch.empty(D, F, dtype=torch.bfloat16, device=device)]
                      for _ in range(2)]
-        self.local_out = [(C.c_void_p * n)(*[w.data_ptr() if r == self.rank else 0 for r in range(n)]) for lp in self.shards for w in lp]
+        self.local_out = [(C.c_void_p * n)(*[w.data_ptr() if r == self.rank else 0 for r in range(n)]) for lp in self.shards for w in lp[:2]]
         shapes = [(F, D), (D, F)]
         self.chan = FusedChannel(self.sw, _owned_cap(shapes, n, OWN_ROW_SHARDED), max(_tiles(*s) for s in shapes))
         self.coll = CollChannel(self.sw)
@@ -267,10 +335,11 @@ class FusedFSDPTrainer:
         y = x
         self._start_gather(0)
         params = None
+        bias = self.biases
         for l in range(L):
             params = self._finish_gather(l)
             self._start_gather(l + 1)
-            y, s = tlayer_ffn_fwd(ops, params, y, self.opts)
+            y, s = tlayer_ffn_fwd(ops, params + [bias.b1[l], bias.b2[l]] if bias else params, y, self.opts)
             acts.append(s)
         self._start_gather(L - 2)
         d = dloss_dx
@@ -282,13 +351,17 @@ class FusedFSDPTrainer:
             s = acts[i]
             a, pre = s.a, s.pre
             if a is None:
-                a, pre = ops.linear_act(s.x, W1, self.opts.activation)
+                a, pre = ops.linear_act(s.x, W1, self.opts.activation, bias.b1[i] if bias else None)
             dh = ops.grad_input(d, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
+            if bias:
+                bias.accumulate(i, dh, d)
             self._update(i, 1, d, a, D, F, T)
             dn = ops.grad_input(dh, W1, add=d if self.opts.residual else None) if i > 0 else None
             self._update(i, 0, dh, s.x, F, D, T)
             acts[i] = None
             d = dn
+        if bias:
+            bias.reduce_and_update(self.t)
         return y
 
     def run(self, batches: Iterable[Tuple[torch.Tensor, torch.Tensor]]) -> None:
@@ -307,6 +380,8 @@ class FusedFSDPTrainer:
                 nv._check(lib.b200_all_gather_into(full.data_ptr(), self.sbuf.peers_c, self.shard_off[l][k], sh.numel() * 2,
                                                    self.coll.flags.peers_c, self.rank, self.world, e, 0, nv._stream()), "b200_all_gather_into")
                 fl.append(full)
+            if self.biases:
+                fl += [self.biases.b1[l].clone(), self.biases.b2[l].clone()]
             out.append(fl)
         return out
 
@@ -329,8 +404,12 @@ class FusedMPTrainer:
         # Residual: the output buffer is pre-filled with the residual and the kernel runs its in-place update mode with
         # alpha = -1 (out = out + sum over ranks), i.e. the DDP / FSDP code path of the same kernel.
         self.residual = cfg.residual
-        # dW is shard-local under MP (:311-312): SGD rides in the dW GEMM's epilogue; Adam = dW GEMM + the native Adam kernel
-        self.opt = Optimizer(ops, cfg) if cfg.optimizer == "adam" else None
+        # dW is shard-local under MP (:311-312): SGD rides in the dW GEMM's epilogue; Adam = dW GEMM + the native Adam kernel.
+        # Biases (fp32): b1 follows W1's row shard, b2 is replicated and enters the reduced output exactly once - the
+        # output buffer is pre-filled with it (and the residual) before the kernel's in-place mode adds the cross-rank sum.
+        self.opt = Optimizer(ops, cfg)
+        self.adam = cfg.optimizer == "adam"
+        self.has_bias = len(shards[0]) == 4
         self.sp = cfg.mp_mode == "sp"
         self.spf = cfg.mp_mode == "spf"
         if self.sp:
@@ -347,10 +426,29 @@ class FusedMPTrainer:
 
     def update_local(self, W: torch.Tensor, dy: torch.Tensor, x: torch.Tensor) -> None:
         """``W -= update(dy^T @ x)`` on this rank's shard; no communication."""
-        if self.opt is None:
+        if not self.adam:
             self.ops.grad_weight_sgd_(W, dy, x, self.lr)
         else:
             self.opt.update(W.data_ptr(), W, self.ops.grad_weight(dy, x))
+
+    def update_bias(self, layer: int, dh: torch.Tensor, dy: torch.Tensor) -> None:
+        """b1 shard -= update(dh.sum(0)) (local, like dW1); b2 -= update(dy.sum(0)) (every rank computes the same sum)."""
+        if not self.has_bias:
+            return
+        b1, b2 = self.shards[layer][2], self.shards[layer][3]
+        self.opt.update(b1.data_ptr(), b1, nv.colsum(dh))
+        self.opt.update(b2.data_ptr(), b2, nv.colsum(dy))
+
+    def _b(self, layer: int, j: int) -> Optional[torch.Tensor]:
+        return self.shards[layer][2 + j] if self.has_bias else None
+
+    def _prefill(self, out: torch.Tensor, layer: Optional[int], residual: Optional[torch.Tensor]) -> bool:
+        """out = b2 (+ residual) where either exists; returns whether the kernel must ADD its sum to `out`."""
+        b2 = self._b(layer, 1) if layer is not None else None
+        if b2 is None and residual is None:
+            return False
+        nv.bias_rows_(out, b2, residual)
+        return True
 
     def _ensure_buffers(self, T: int) -> None:
         if self.T == T:
@@ -418,35 +516,35 @@ class FusedMPTrainer:
         Fs = self.shards[0][0].shape[0]
         saved = []
         y = x
-        for l, (W1, W2) in enumerate(self.shards):
-            a, pre = ops.linear_act(y, W1, self.opts.activation)
+        for l, sh in enumerate(self.shards):
+            W1, W2 = sh[0], sh[1]
+            a, pre = ops.linear_act(y, W1, self.opts.activation, self._b(l, 0))
             saved.append((y, None if self.opts.recompute else a, None if self.opts.recompute else pre))
-            # y_l = sum over ranks of a_r @ W2_r^T, delivered to every rank - one kernel (:302-303)
-            if self.residual:
-                self.y[l].copy_(y)
+            # y_l = sum over ranks of a_r @ W2_r^T (+ b2 + x), delivered to every rank - one kernel (:302-303)
+            if self._prefill(self.y[l], l, y if self.residual else None):
                 self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SGD, True, -1.0)
             else:
                 self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
             y = self.y[l]
         d = dloss_dx
         for i in reversed(range(self.L)):
-            W1, W2 = self.shards[i]
+            W1, W2 = self.shards[i][0], self.shards[i][1]
             xin, a, pre = saved[i]
             if a is None:
-                a, pre = ops.linear_act(xin, W1, self.opts.activation)
+                a, pre = ops.linear_act(xin, W1, self.opts.activation, self._b(i, 0))
             dh = ops.grad_input(d, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
             self.update_local(W2, d, a)                                   # shard-local, no communication (:311-312)
             dn = None
             if i > 0:
                 slot = i % 2
-                # dx = sum over ranks of dh_r @ W1_r, delivered to every rank - one kernel (:308-309)
-                if self.residual:
-                    self.dx[slot].copy_(d)
+                # dx = sum over ranks of dh_r @ W1_r (+ d), delivered to every rank - one kernel (:308-309)
+                if self._prefill(self.dx[slot], None, d if self.residual else None):
                     self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SGD, True, -1.0)
                 else:
                     self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
                 dn = self.dx[slot]
             self.update_local(W1, dh, xin)
+            self.update_bias(i, dh, d)
             saved[i] = None
             d = dn
         return y
@@ -470,13 +568,13 @@ class FusedMPTrainer:
         saved = []
         cur_off = self.xs0_off
         cur_shard = self.xs0
-        for l, (W1, W2) in enumerate(self.shards):
+        for l, sh in enumerate(self.shards):
+            W1, W2 = sh[0], sh[1]
             xfull = self._gather_tokens(cur_off, T, D)                    # all-gather -> column-parallel GEMM
-            a, pre = ops.linear_act(xfull, W1, self.opts.activation)
+            a, pre = ops.linear_act(xfull, W1, self.opts.activation, self._b(l, 0))
             saved.append((cur_off, None if self.opts.recompute else a, None if self.opts.recompute else pre))
             # row-parallel GEMM -> reduce-scatter over token shards, one kernel: I keep rows [r*Ts, (r+1)*Ts)
-            if self.residual:
-                self.ys[l].copy_(cur_shard)
+            if self._prefill(self.ys[l], l, cur_shard if self.residual else None):
                 self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.local_tab(self.ys[l]), D, r * Ts, OWN_ROW_SHARDED, FOP_SGD, False, -1.0)
             else:
                 self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.local_tab(self.ys[l]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
@@ -486,29 +584,30 @@ class FusedMPTrainer:
         self.dxs[d_slot].copy_(dloss_dx[r * Ts:(r + 1) * Ts])
         d_off, d_shard = self.dxs_off[d_slot], self.dxs[d_slot]
         for i in reversed(range(self.L)):
-            W1, W2 = self.shards[i]
+            W1, W2 = self.shards[i][0], self.shards[i][1]
             x_off, a, pre = saved[i]
             dfull = self._gather_tokens(d_off, T, D)
             xfull = self._gather_tokens(x_off, T, D)
             if a is None:
-                a, pre = ops.linear_act(xfull, W1, self.opts.activation)
+                a, pre = ops.linear_act(xfull, W1, self.opts.activation, self._b(i, 0))
             dh = ops.grad_input(dfull, W2, act=self.opts.activation, aux=(pre if pre is not None else a) if self.opts.activation == "relu" else pre)
             self.update_local(W2, dfull, a)
             if i > 0:
                 slot = i % 2
-                if self.residual:
-                    self.dxs[slot].copy_(d_shard)
+                if self._prefill(self.dxs[slot], None, d_shard if self.residual else None):
                     self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.local_tab(self.dxs[slot]), D, r * Ts, OWN_ROW_SHARDED, FOP_SGD, False, -1.0)
                 else:
                     self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.local_tab(self.dxs[slot]), D, r * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
                 d_off, d_shard = self.dxs_off[slot], self.dxs[slot]
             self.update_local(W1, dh, xfull)
+            self.update_bias(i, dh, dfull)
             saved[i] = None
         return self._gather_tokens(self.ys_off[self.L - 1], T, D)
 
     # ---- sequence-parallel form, gathers fused into the column-parallel GEMMs ------------------------------------
     # The schedule itself is `spf_step` (below the class); these are its three primitives on the native kernels.
-    def ag_gemm(self, buf: torch.Tensor, W: torch.Tensor, b_major: int, kind: str, aux: Optional[torch.Tensor] = None):
+    def ag_gemm(self, buf: torch.Tensor, W: torch.Tensor, b_major: int, kind: str, aux: Optional[torch.Tensor] = None,
+                bias: Optional[torch.Tensor] = None):
         """``out = epilogue(all_gather(buf) @ W^T)`` in one kernel; ``buf`` (a full-size symmetric ``[T, D]`` buffer whose
         own token rows are final) is complete on return.  Returns ``(out, saved_for_backward)``."""
         T, D = buf.shape
@@ -517,14 +616,14 @@ class FusedMPTrainer:
         peers = self.abuf.peers_at(self.abuf.offset_of(buf))
         if kind == "relu" and N % 128 == 0:
             mask = torch.empty(T, N // 8, dtype=torch.uint8, device=self.device)
-            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_RELU_MASK, out2=mask)
+            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_RELU_MASK, out2=mask, bias=bias)
             return out, mask
         if kind == "relu":
-            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_RELU)
+            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_RELU, bias=bias)
             return out, out
         if kind == "gelu":
             pre = torch.empty_like(out)
-            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_GELU, out2=pre)
+            self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_GELU, out2=pre, bias=bias)
             return out, pre
         if kind == "relu_bwd":
             self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_RELU_BWD_MASK if aux.dtype == torch.uint8 else nv.EPI_RELU_BWD, aux=aux)
@@ -534,15 +633,16 @@ class FusedMPTrainer:
             return out, None
         raise ValueError(kind)
 
-    def rs_gemm(self, A: torch.Tensor, W: torch.Tensor, b_major: int, dst: torch.Tensor, residual: Optional[torch.Tensor] = None) -> None:
-        """``dst[own token rows] = sum over ranks of A @ W^T (+ residual[own token rows])`` - row-parallel GEMM +
+    def rs_gemm(self, A: torch.Tensor, W: torch.Tensor, b_major: int, dst: torch.Tensor, residual: Optional[torch.Tensor] = None,
+                bias: Optional[torch.Tensor] = None) -> None:
+        """``dst[own token rows] = sum over ranks of A @ W^T (+ bias + residual[own token rows])`` - row-parallel GEMM +
         reduce-scatter in one kernel."""
         T, D = dst.shape
         Ts = T // self.world
         rows = slice(self.rank * Ts, (self.rank + 1) * Ts)
         own = dst[rows]
-        if residual is not None:
-            own.copy_(residual[rows])
+        if residual is not None or bias is not None:
+            nv.bias_rows_(own, bias, residual[rows] if residual is not None else None)
             self.chan.gemm(A, nv.MAJOR_K, W, b_major, T, D, A.shape[1], self.local_tab(own), D, self.rank * Ts, OWN_ROW_SHARDED, FOP_SGD, False, -1.0)
         else:
             self.chan.gemm(A, nv.MAJOR_K, W, b_major, T, D, A.shape[1], self.local_tab(own), D, self.rank * Ts, OWN_ROW_SHARDED, FOP_SUM, False)
@@ -558,8 +658,7 @@ class FusedMPTrainer:
 
     def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         self._ensure_buffers(x.shape[0])
-        if self.opt is not None:
-            self.opt.begin_step()
+        self.opt.begin_step()
         if self.spf:
             return spf_step(self, x, dloss_dx)
         return self._step_sp(x, dloss_dx) if self.sp else self._step_ar(x, dloss_dx)
@@ -593,16 +692,18 @@ def spf_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
     act = t.opts.activation
     t.X[0][own].copy_(x[own])
     saved = []
-    for l, (W1, W2) in enumerate(t.shards):
-        a, aux = t.ag_gemm(t.X[l], W1, nv.MAJOR_K, act)                   # completes X[l] as a side effect
-        t.rs_gemm(a, W2, nv.MAJOR_K, t.X[l + 1], t.X[l] if t.opts.residual else None)   # my token rows of the next layer's input
+    bias = lambda l, j: t.shards[l][2 + j] if len(t.shards[l]) == 4 else None
+    for l, sh in enumerate(t.shards):
+        W1, W2 = sh[0], sh[1]
+        a, aux = t.ag_gemm(t.X[l], W1, nv.MAJOR_K, act, bias=bias(l, 0))   # completes X[l] as a side effect
+        t.rs_gemm(a, W2, nv.MAJOR_K, t.X[l + 1], t.X[l] if t.opts.residual else None, bias=bias(l, 1))   # my token rows of the next layer's input
         saved.append(None if t.opts.recompute else (a, aux))
     cur = 0
     t.DX[cur][own].copy_(dloss_dx[own])
     for i in reversed(range(t.L)):
-        W1, W2 = t.shards[i]
+        W1, W2 = t.shards[i][0], t.shards[i][1]
         if saved[i] is None:                                              # X[i] is complete since the forward pass
-            a, pre = t.ops.linear_act(t.X[i], W1, act)
+            a, pre = t.ops.linear_act(t.X[i], W1, act, bias(i, 0))
             aux = (pre if pre is not None else a) if act == "relu" else pre
         else:
             a, aux = saved[i]
@@ -611,6 +712,7 @@ def spf_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         if i > 0:
             t.rs_gemm(dh, W1, nv.MAJOR_MN, t.DX[1 - cur], t.DX[cur] if t.opts.residual else None)
         t.update_local(W1, dh, t.X[i])
+        t.update_bias(i, dh, t.DX[cur])
         saved[i] = None
         cur = 1 - cur
     return t.gather_out(t.X[t.L])

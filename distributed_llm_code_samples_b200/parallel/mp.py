@@ -32,8 +32,7 @@ class MPTrainer:
         self.residual = cfg.residual
         self.opt = Optimizer(ops, cfg)
         self.world, self.rank = comm.world, comm.rank
-        has_bias = len(shards[0]) == 4
-        self.fused = bool(getattr(ops, "fused_update", False)) and cfg.optimizer == "sgd" and not has_bias
+        self.fused = bool(getattr(ops, "fused_update", False)) and cfg.optimizer == "sgd"
         self.sp = cfg.mp_mode in ("sp", "spf")      # spf is a fused-kernel variant of sp: same math on this path
 
     def _params_for_fwd(self, p: Params) -> Params:

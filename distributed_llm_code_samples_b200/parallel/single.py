@@ -18,8 +18,7 @@ class SingleTrainer:
         self.ops, self.cfg, self.params = ops, cfg, params
         self.opts = block_opts(cfg)
         self.opt = Optimizer(ops, cfg)
-        has_bias = len(params[0]) == 4
-        self.fused = bool(getattr(ops, "fused_update", False)) and cfg.optimizer == "sgd" and not has_bias
+        self.fused = bool(getattr(ops, "fused_update", False)) and cfg.optimizer == "sgd"
 
     def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         self.opt.begin_step()
@@ -27,9 +26,12 @@ class SingleTrainer:
         if self.fused:
             d = dloss_dx
             for i in reversed(range(len(self.params))):
-                d, _ = tlayer_ffn_bkwd(self.ops, d, self.params[i], acts[i], self.opts, need_dx=i > 0,
+                d, g = tlayer_ffn_bkwd(self.ops, d, self.params[i], acts[i], self.opts, need_dx=i > 0,
                                        update_lr=self.opt.lr)
                 acts[i] = None      # release this block's activations as soon as they are consumed
+                if g is not None:   # bias gradients (the weights were updated in the dW GEMMs' epilogues)
+                    for j, (p, gj) in enumerate(zip(self.params[i], g)):
+                        self.opt.update(i * 4 + j, p, gj)
             return y
         grads, _ = tlayers_ffn_bkwd(self.ops, dloss_dx, self.params, acts, self.opts)
         for i in range(len(self.params)):

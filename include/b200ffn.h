@@ -67,6 +67,20 @@ int b200_sgd_bf16(void* param, const void* grad, long long n, float lr, int grad
 /* Adam on bf16 params with fp32 moments (extension; the reference only has SGD). step is 1-based. */
 int b200_adam_bf16(void* param, const void* grad, float* m, float* v, long long n, float lr, float beta1,
                    float beta2, float eps, int step, int grad_f32, void* stream);
+/* fp32 parameters (biases stay fp32 whatever the weights' dtype): p -= lr * g, and Adam. */
+int b200_sgd_f32(float* param, const float* grad, long long n, float lr, void* stream);
+int b200_adam_f32(float* param, const float* grad, float* m, float* v, long long n, float lr, float beta1, float beta2,
+                  float eps, int step, void* stream);
+/* Bias gradient: out[n] (+)= sum_t x[t, n] over a bf16 [T, N] matrix of row pitch ld (elements).  Deterministic two-stage
+ * sum; `scratch`: b200_colsum_scratch_bytes(T, N) bytes of device memory.  accumulate != 0 adds to out.  The reference
+ * has no bias (train_ffns.py:35 "no bias as simplification"); this is the north-star extension's db = dy.sum(0). */
+long long b200_colsum_scratch_bytes(int T, int N);
+int b200_colsum_bf16(float* out, const void* x, long long ld, int T, int N, int accumulate, void* scratch,
+                     long long scratch_bytes, void* stream);
+/* out[t, :] = bias (+ residual[t, :]): pre-fills the output of a fused row-parallel GEMM + all-reduce / reduce-scatter whose
+ * in-place mode (op 1, alpha = -1) then adds the cross-rank sum - how bias and residual reach the fused MP kernels.
+ * bias (fp32 [N]) and residual (bf16) may each be NULL. */
+int b200_bias_rows_bf16(void* out, long long ldo, const void* residual, long long ldr, const float* bias, int T, int N, void* stream);
 /* out = relu(x) (:47-48) and dy = dy * (x > 0) in place (:50-52), standalone (unfused) forms. */
 int b200_relu_bf16(void* out, const void* x, long long n, void* stream);
 int b200_relu_bwd_bf16(void* dy, const void* x, long long n, void* stream);

@@ -214,3 +214,60 @@ def test_adam(cuda_device):
         opt.step()
         nv.adam_(p, g, m, v, 1e-2, 0.9, 0.999, 1e-8, step)
     assert (p.float() - pr.detach()).abs().max().item() < 6e-2   # three bf16 roundings at |p|~3
+
+
+@pytest.mark.parametrize("n", [4096, 1000003])
+def test_adam_vectorised_matches_fp32_reference(cuda_device, n):
+    """8-wide Adam (16-byte parameter / moment accesses) + scalar tail vs the same formula in fp32 torch, both gradient
+    dtypes; the moments must match to fp32 round-off."""
+    for gdt in (torch.bfloat16, torch.float32):
+        p = _rand((n,), cuda_device, seed=21)
+        g = _rand((n,), cuda_device, seed=22).to(gdt)
+        m, v = torch.zeros(n, device=cuda_device), torch.zeros(n, device=cuda_device)
+        pr, mr, vr = p.float().clone(), torch.zeros(n, device=cuda_device), torch.zeros(n, device=cuda_device)
+        for step in (1, 2):
+            nv.adam_(p, g, m, v, 1e-2, 0.9, 0.999, 1e-8, step)
+            mr = 0.9 * mr + 0.1 * g.float()
+            vr = 0.999 * vr + 0.001 * g.float() ** 2
+            pr = (pr - 1e-2 * (mr / (1 - 0.9 ** step)) / ((vr / (1 - 0.999 ** step)).sqrt() + 1e-8)).to(torch.bfloat16).float()
+            assert (m - mr).abs().max().item() < 1e-5 and (v - vr).abs().max().item() < 1e-5
+            assert (p.float() - pr).abs().max().item() <= 2 ** -6      # one bf16 ulp at |p| < 4
+            pr = p.float().clone()
+
+
+def test_fp32_param_optimizers_and_bias_kernels(cuda_device):
+    """fp32 SGD / Adam (the biases), the column-sum bias gradient (two-stage, deterministic) and the bias/residual row fill."""
+    n = 5000
+    p, g = torch.randn(n, device=cuda_device), torch.randn(n, device=cuda_device)
+    p0 = p.clone()
+    nv.sgd_f32_(p, g, 0.1)
+    assert torch.allclose(p, p0 - 0.1 * g, atol=1e-6)
+    m, v = torch.zeros(n, device=cuda_device), torch.zeros(n, device=cuda_device)
+    pr = torch.nn.Parameter(p.clone())
+    opt = torch.optim.Adam([pr], lr=1e-2)
+    for step in (1, 2, 3):
+        pr.grad = g.clone()
+        opt.step()
+        nv.adam_f32_(p, g, m, v, 1e-2, 0.9, 0.999, 1e-8, step)
+    assert torch.allclose(p, pr.detach(), atol=1e-5)
+    for T, N in [(16384, 4096), (1000, 264), (77, 8), (4096, 16384)]:
+        x = _rand((T, N), cuda_device, seed=23)
+        ref = x.double().sum(0)
+        out = nv.colsum(x)
+        out2 = nv.colsum(x)
+        assert torch.equal(out, out2), "column sum must be deterministic"
+        assert (out.double() - ref).abs().max().item() <= 1e-3 * max(1.0, ref.abs().max().item()), (T, N)
+        acc = out.clone()
+        nv.colsum(x, out=acc, accumulate=True)
+        assert torch.allclose(acc, 2 * out, rtol=1e-6, atol=1e-4)
+    xs = _rand((512, 1024), cuda_device, seed=24)[:, 256:512]             # strided view
+    assert (nv.colsum(xs).double() - xs.double().sum(0)).abs().max().item() < 1e-2
+    T, N = 300, 512
+    res, bias = _rand((T, N), cuda_device, seed=25), torch.randn(N, device=cuda_device)
+    out = torch.empty(T, N, dtype=torch.bfloat16, device=cuda_device)
+    nv.bias_rows_(out, bias, res)
+    assert torch.equal(out, (res.float() + bias).to(torch.bfloat16))
+    nv.bias_rows_(out, bias, None)
+    assert torch.equal(out, bias.to(torch.bfloat16).expand(T, N))
+    nv.bias_rows_(out, None, res)
+    assert torch.equal(out, res)

@@ -194,6 +194,32 @@ def test_fused_adam_matches_unfused_adam(method):
     assert _rel(upd(fused), upd(unfused)) < 0.25
 
 
+@pytest.mark.parametrize("method,mp_mode", [("ddp", "ar"), ("fsdp", "ar"), ("mp", "ar"), ("mp", "sp"), ("mp", "spf")])
+@pytest.mark.parametrize("optimizer", ["sgd", "adam"])
+def test_fused_north_star_block_matches_nccl(method, mp_mode, optimizer):
+    """BASELINE.json's block - Linear -> GELU -> Linear + residual, with biases, SGD or Adam - on the FUSED trainers (bias
+    in the GEMM epilogues / pre-filled outputs, bias gradients = native column sums + the native fp32 all-reduce) against
+    the unfused trainers on NCCL.  Two optimizer steps; weights and biases compared."""
+    from distributed_llm_code_samples_b200.models import ffn
+    from distributed_llm_code_samples_b200.parallel import api
+    g = torch.Generator().manual_seed(44)
+    lp = [[p.to(torch.bfloat16).float() if j < 2 else p.normal_(0, 0.05, generator=g) for j, p in enumerate(l)]
+          for l in ffn.init_stack(3, DM, 4 * DM, g, bias=True)]
+    seeds = torch.arange(2 if method == "mp" else 2 * WORLD)
+    T = max(512, 256 * WORLD)
+    fn = {"ddp": api.train_ddp, "fsdp": api.train_fsdp, "mp": api.train_tp}[method]
+    kw = dict(activation="gelu", residual=True, bias=True, optimizer=optimizer, mp_mode=mp_mode, lr=1e-3)
+    fused = fn(lp, seeds, T, DM, _cfg(comm="fused", **kw))
+    nccl = fn(lp, seeds, T, DM, _cfg(comm="nccl", **kw))
+    upd = lambda res: [[p.float() - q for p, q in zip(a, b)] for a, b in zip(res, lp)]
+    uf, un = upd(fused), upd(nccl)
+    assert all(torch.isfinite(p).all() for l in fused for p in l)
+    for j in range(4):                                            # W1, W2, b1, b2 separately: a dead bias path must not hide
+        a, b = [[l[j]] for l in uf], [[l[j]] for l in un]
+        assert max(u[0].abs().max().item() for u in a) > 0, f"param {j} did not move"
+        assert _rel(a, b) < 0.25, (j, _rel(a, b))
+
+
 @pytest.mark.parametrize("method,extra", [("ddp", {"optimizer": "adam"}), ("fsdp", {"bias": True}), ("mp", {"residual": True})])
 def test_unfused_trainers_on_native_collectives_match_nccl(method, extra):
     """--comm native: the plain trainers (so Adam / bias / residual work) with every collective on the peer-memory

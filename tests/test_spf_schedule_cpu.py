@@ -39,10 +39,17 @@ class _GlooSpf:
             if q != self.rank:
                 buf[q * Ts:(q + 1) * Ts] = p
 
-    def ag_gemm(self, buf, W, b_major, kind, aux=None):
+    def update_bias(self, layer, dh, dy):
+        if len(self.shards[layer]) == 4:
+            self.shards[layer][2].sub_(self.lr * dh.sum(0))
+            self.shards[layer][3].sub_(self.lr * dy.sum(0))
+
+    def ag_gemm(self, buf, W, b_major, kind, aux=None, bias=None):
         self._gather_rows(buf)
         assert torch.isfinite(buf).all()
         h = buf @ (W.t() if b_major == nv.MAJOR_K else W)
+        if bias is not None:
+            h = h + bias
         if kind == "relu":
             a = torch.where(h <= 0, torch.zeros_like(h), h)
             return a, a
@@ -56,9 +63,11 @@ class _GlooSpf:
             return h * g, None
         raise ValueError(kind)
 
-    def rs_gemm(self, A, W, b_major, dst, residual=None):
+    def rs_gemm(self, A, W, b_major, dst, residual=None, bias=None):
         full = A @ (W.t() if b_major == nv.MAJOR_K else W)
         dist.all_reduce(full)
+        if bias is not None:
+            full = full + bias
         Ts = dst.shape[0] // self.world
         rows = slice(self.rank * Ts, (self.rank + 1) * Ts)
         res = residual[rows].clone() if residual is not None else 0.0     # (residual may alias dst's buffer family)
@@ -83,13 +92,22 @@ def _worker(rank, world, dev, lp, seeds, cfg_dict, out):
     for i, l in enumerate(shards):
         out[i][0].chunk(world, dim=0)[rank].copy_(l[0])
         out[i][1].chunk(world, dim=1)[rank].copy_(l[1])
+        if len(l) == 4:
+            out[i][2].chunk(world, dim=0)[rank].copy_(l[2])
+            if rank == 0:
+                out[i][3].copy_(l[3])
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("act,recompute,residual", [("relu", False, False), ("gelu", False, True), ("relu", True, True)])
-def test_spf_schedule_equals_single_device(act, recompute, residual):
+@pytest.mark.parametrize("act,recompute,residual,bias", [("relu", False, False, False), ("gelu", False, True, False),
+                                                         ("relu", True, True, False), ("gelu", False, True, True)])
+def test_spf_schedule_equals_single_device(act, recompute, residual, bias):
     g = torch.Generator().manual_seed(17)
-    lp = ffn.init_stack(L, D, FF, g)
+    lp = ffn.init_stack(L, D, FF, g, bias=bias)
+    if bias:
+        for l in lp:                  # non-zero biases so that a dropped or doubled bias shows
+            l[2].normal_(0, 0.1, generator=g)
+            l[3].normal_(0, 0.1, generator=g)
     seeds = torch.tensor([5, 9, 13])
     cfg = TrainConfig(model_size=D, ffn_dim=FF, layers=L, device="cpu", backend="gloo", world_size=2, impl="torch", lr=0.05,
                       activation=act, recompute=recompute, residual=residual, mp_mode="spf")
