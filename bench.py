@@ -45,6 +45,7 @@ def parse_args():
                     help="MP form: ar = the reference's all-reduce form (default, the benchmarked one); sp / spf = sequence-parallel variants")
     ap.add_argument("--fsdp_gather", default="dma", choices=["dma", "fused"])
     ap.add_argument("--mp_input", default="full", choices=["full", "sharded"])
+    ap.add_argument("--nvls", default="auto", choices=["auto", "off"])
     ap.add_argument("--also", default="auto",
                     help="extra strategies measured in the same process and reported under `also` (comma list of fsdp, mp, "
                          "ddp_recompute; auto = fsdp,mp when --method ddp; none)")
@@ -128,6 +129,40 @@ def record(impl, method, world, args, value, ms, clocks, e2e, launches, config, 
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches}
 
 
+def also_in_child(args, impl, method, idx, recompute=False):
+    """Measure one more strategy in a FRESH process per rank (same launcher environment, its own rendezvous port), so that
+    it starts from the same clean CUDA context / allocator state as a stand-alone `bench.py --method ...` run: measured in
+    round 2, FSDP's end-to-end loop ran 13 % slower when it followed another engine in the same process.  Every rank spawns
+    its child at the same point; rank 0 returns the child's JSON record."""
+    import subprocess
+    rank, world, _ = rank_world()
+    env = dict(os.environ)
+    if world > 1:
+        env["MASTER_PORT"] = str(int(os.environ.get("MASTER_PORT", "29500")) + 101 + idx)
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", impl, "--method", method, "--also", "none", "--gpus", str(args.gpus),
+           "--steps", str(args.steps), "--warmup", str(args.warmup), "--batch_size", str(args.batch_size), "--seq_len", str(args.seq_len),
+           "--comm", args.comm, "--ops", args.ops, "--mp_mode", args.mp_mode, "--fsdp_gather", args.fsdp_gather,
+           "--mp_input", args.mp_input, "--nvls", args.nvls, "--pool", str(args.pool)]
+    if recompute:
+        cmd.append("--recompute")
+    if args.no_e2e:
+        cmd.append("--no-e2e")
+    try:
+        p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=1500)
+        out, err, rc = p.stdout, p.stderr, p.returncode
+    except subprocess.TimeoutExpired as e:
+        out, err, rc = (e.stdout or ""), "timeout", -1
+    if rank != 0:
+        return None
+    for line in reversed(out.splitlines()):
+        if line.startswith("{"):
+            try:
+                return json.loads(line)
+            except json.JSONDecodeError:
+                pass
+    return {"error": f"child rc={rc}", "stderr_tail": err[-600:]}
+
+
 def also_methods(args):
     if args.also == "none":
         return []
@@ -150,7 +185,7 @@ def ours_one(args, method, recompute):
     d, f, l = shape_defaults(args, method)
     cfg = TrainConfig(num_steps=args.steps, batch_size=args.batch_size, seq_len=args.seq_len, layers=l, model_size=d,
                       ffn_dim=f, dtype="bf16", device="cuda", backend="nccl", impl=args.ops, comm=args.comm,
-                      recompute=recompute, mp_mode=args.mp_mode, fsdp_gather=args.fsdp_gather, mp_input=args.mp_input)
+                      recompute=recompute, mp_mode=args.mp_mode, fsdp_gather=args.fsdp_gather, mp_input=args.mp_input, nvls=args.nvls)
     torch.cuda.set_device(local)
     params0 = init_params_on_device(cfg, torch.device("cuda", local), seed=1234, scale=init_scale(d, f))
     eng = Engine(cfg, method=method, layers_params=params0)
@@ -221,10 +256,8 @@ def run_ours(args):
             also[m] = {"same_run_as": "ddp", "value": rec["value"], "unit": rec["unit"], "ms_per_step": rec["ms_per_step"],
                        "e2e": rec["e2e"], "clocks": rec["clocks"], "gpu_launches": rec["gpu_launches"], "config": rec["config"]}
             continue
-        if m == "ddp_recompute":
-            also[m] = ours_one(args, "ddp", True)
-        else:
-            also[m] = ours_one(args, m, args.recompute)
+        k = len(also)
+        also[m] = also_in_child(args, "ours", "ddp", k, True) if m == "ddp_recompute" else also_in_child(args, "ours", m, k, args.recompute)
     if also:
         rec["also"] = also
     if rank == 0:
@@ -352,7 +385,7 @@ def run_reference(args):
             also[m] = {"same_run_as": "ddp", "value": rec["value"], "unit": rec["unit"], "ms_per_step": rec["ms_per_step"],
                        "e2e": rec["e2e"], "clocks": rec["clocks"], "gpu_launches": 0, "config": rec["config"]}
             continue
-        also[m] = reference_one(args, ref, m)
+        also[m] = also_in_child(args, "reference", m, len(also) + 10)
     if also:
         rec["also"] = also
     if rank == 0:

@@ -17,7 +17,7 @@
 namespace b200 {
 
 constexpr int COLL_THREADS = 256;   // small footprint: must be able to co-reside with a 320-thread GEMM CTA on every SM
-constexpr int COLL_MAX_BLOCKS = 64;
+constexpr int COLL_MAX_BLOCKS = COLL_FLAG_BLOCKS;   // one 256-thread CTA per SM at most (they co-reside with GEMM CTAs)
 
 __global__ void __launch_bounds__(32) barrier_kernel(PeerTable flags, int rank, int world, uint32_t value, unsigned int* err) {
     block_barrier(flags, rank, world, value, err);

@@ -56,11 +56,16 @@ struct FusedParams {
     int owned_cap;
     int owned_count;                 // tiles this rank owns in this call
     int ready_base;                  // word offset of the ready flags inside the flag block
+    // NVLS form (FusedEpiT<.., NVLS = 1>): partials stay LOCAL, the owner sums them inside the NVSwitch.
+    __nv_bfloat16* part_local;       // this rank's partial tiles [2 parities][part_cap][TILE_ELEMS], a multicast-bound block
+    const __nv_bfloat16* part_mc;    // the same block through its multicast address (multimem.ld_reduce sums all ranks' copies)
+    __nv_bfloat16* out_mc;           // the output through its multicast address (multimem.st stores into every replica)
+    int part_cap;
 };
 
 // Adam variant (OPT = 1): the owner of a tile also owns its optimizer state - fp32 moments in a compact per-owned-tile
 // layout [owned slot][128][256], i.e. 1/world of the state per rank (ZeRO-1 for DDP, the natural layout for FSDP).
-// Formula as b200_adam_bf16 (elementwise.cu).  Written after round 1's GPU budget was spent: not yet run on hardware.
+// Formula as b200_adam_bf16 (elementwise.cu).  Validated in round 2 (tests/test_emu_gpu.py::test_emu_dw_adam; 2 GPUs: test_fused_adam_matches_unfused_adam).
 struct FusedAdamParams : FusedParams {
     float* adam_m;
     float* adam_v;
@@ -88,6 +93,19 @@ __host__ __device__ __forceinline__ void owned_tile_coords(const FusedParams& p,
 }
 __host__ __device__ __forceinline__ size_t inbox_slot(const FusedParams& p, int k_local, int src) {
     return ((size_t)(p.parity * p.owned_cap + k_local) * p.world + src) * TILE_ELEMS;
+}
+__host__ __device__ __forceinline__ size_t part_slot(const FusedParams& p, int lin_tile) {
+    return ((size_t)p.parity * p.part_cap + lin_tile) * TILE_ELEMS;
+}
+// sum over every rank's copy of 8 bf16 (fp32 accumulation inside the switch), and a store into every rank's copy
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st_bf16x8(void* mc, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 __device__ __forceinline__ void epi_group_sync() {       // the 8 epilogue warps only (named barrier 1)
     asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
@@ -118,8 +136,14 @@ __device__ __forceinline__ void side_group_sync(int threads) {   // the side war
 //     been handed back to the MMA warp: the system-scope fence (microseconds over NVLink) no longer sits between the two
 //     halves' TMEM drains, i.e. on the path that gates the next tile's first MMAs.
 //   * Completion is counted with the barrier instead of shared-memory atomics.
-template <int SIDE_WARPS, int PAD, int OPT = 0>
+//   * NVLS = 1 (link-bound all-reduce / reduce-scatter of activations, SUM or in-place add): every rank stores its partial
+//     tile LOCALLY into a multicast-bound buffer and only sends the arrival flag; the owner's side warps read the tile
+//     through the multicast address (multimem.ld_reduce: the NVSwitch pulls the `world` copies and returns their fp32-
+//     accumulated sum) and, in broadcast mode, write the result with multimem.st (the switch replicates it).  Per GPU and
+//     direction ~1.1x the activation bytes cross NVLink instead of the ~1.75x of push + broadcast.
+template <int SIDE_WARPS, int PAD, int OPT = 0, int NVLS = 0>
 struct FusedEpiT {
+    static_assert(!(NVLS == 1 && OPT == 1), "the NVLS form serves activations (SUM / in-place add), not optimizer updates");
     using Params = std::conditional_t<OPT == 1, FusedAdamParams, FusedParams>;
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
     static constexpr int EXTRA_WARPS = SIDE_WARPS;   // side warps reduce/broadcast owned tiles under the MMAs
@@ -143,7 +167,9 @@ struct FusedEpiT {
     // ---- push this warp's 32 rows x 128 columns of the accumulator into the owner's inbox ------------------
     static __device__ __forceinline__ void process_tile(const Params& p, const GemmCore& g, const EpiCtx& ctx, uint32_t taddr, State& st) {
         st.owner = owner_of(p, g, ctx.m_blk, ctx.n_blk, st.k_local);
-        __nv_bfloat16* dst_tile = reinterpret_cast<__nv_bfloat16*>(p.inbox[st.owner]) + inbox_slot(p, st.k_local, p.rank);
+        __nv_bfloat16* dst_tile;
+        if constexpr (NVLS == 1) dst_tile = p.part_local + part_slot(p, ctx.m_blk * g.tiles_n + ctx.n_blk);   // local store; the switch fetches it
+        else dst_tile = reinterpret_cast<__nv_bfloat16*>(p.inbox[st.owner]) + inbox_slot(p, st.k_local, p.rank);
         const int lane = ctx.lane;
         uint4* stage = reinterpret_cast<uint4*>(ctx.stage);
 #pragma unroll 1
@@ -270,11 +296,40 @@ struct FusedEpiT {
     // in flight per lane instead of one.
     static __device__ __forceinline__ void reduce_rows(const Params& p, const GemmCore& g, int k_local, int swarp, int lane) {
         constexpr int ROWS = BM / EXTRA_WARPS;
+        static_assert(ROWS % 8 == 0, "the NVLS path batches 8 rows");
         int m_blk, n_blk;
         owned_tile_coords(p, g, k_local, m_blk, n_blk);
         const __nv_bfloat16* inb = reinterpret_cast<const __nv_bfloat16*>(p.inbox[p.rank]);
         const int col = n_blk * BN + lane * 8;                       // 32 lanes x 8 columns = one 256-wide row
         if (col >= g.N) return;
+        if constexpr (NVLS == 1) {
+            // 8 rows (8 in-switch reductions) in flight per lane: a multimem.ld_reduce is a round trip through the switch
+            constexpr int NB = 8;
+            const __nv_bfloat16* src = p.part_mc + part_slot(p, m_blk * g.tiles_n + n_blk) + lane * 8;
+#pragma unroll 1
+            for (int r0 = 0; r0 < ROWS; r0 += NB) {
+                uint4 v[NB];
+#pragma unroll
+                for (int rr = 0; rr < NB; ++rr) v[rr] = multimem_ld_reduce_bf16x8(src + (size_t)(swarp * ROWS + r0 + rr) * BN);
+#pragma unroll
+                for (int rr = 0; rr < NB; ++rr) {
+                    const int grow = m_blk * BM + swarp * ROWS + r0 + rr;
+                    if (grow >= g.M) continue;
+                    const size_t off = (size_t)(grow - p.out_row_offset) * p.ldo + col;
+                    uint4 o = v[rr];
+                    if (p.op == FOP_SGD) {                           // in-place form: out = out - alpha * sum (residual / bias pre-filled)
+                        const uint4 ww = *reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.out[p.rank]) + off);
+                        o.x = pack_bf16x2(bf16_lo(ww.x) - p.alpha * bf16_lo(o.x), bf16_hi(ww.x) - p.alpha * bf16_hi(o.x));
+                        o.y = pack_bf16x2(bf16_lo(ww.y) - p.alpha * bf16_lo(o.y), bf16_hi(ww.y) - p.alpha * bf16_hi(o.y));
+                        o.z = pack_bf16x2(bf16_lo(ww.z) - p.alpha * bf16_lo(o.z), bf16_hi(ww.z) - p.alpha * bf16_hi(o.z));
+                        o.w = pack_bf16x2(bf16_lo(ww.w) - p.alpha * bf16_lo(o.w), bf16_hi(ww.w) - p.alpha * bf16_hi(o.w));
+                    }
+                    if (p.broadcast) multimem_st_bf16x8(p.out_mc + off, o);
+                    else st_u4(reinterpret_cast<__nv_bfloat16*>(p.out[p.rank]) + off, o);
+                }
+            }
+            return;
+        }
         constexpr int RB = OPT == 1 ? 1 : 2;                         // Adam keeps 16 more floats live per row
 #pragma unroll 1
         for (int r0 = 0; r0 < ROWS; r0 += RB) {
@@ -418,6 +473,9 @@ struct FusedCall {
     float alpha;
     int max_ctas;
     const AdamArgs* adam;
+    void* part_local = nullptr;      // NVLS form: all three set (see FusedParams)
+    const void* part_mc = nullptr;
+    void* out_mc = nullptr;
 };
 
 // Runtime choice of the kernel variant (b200_fused_config): side warps 2 (384 threads, 168 registers) or 4 (448 threads,
@@ -442,7 +500,12 @@ extern "C" int b200_fused_config(int side_warps, int overlap) {
 
 static int fused_build(const FusedCall& c, FusedParams* out, int* grid_out) {
     if (c.world < 1 || c.world > MAX_WORLD_F || c.rank < 0 || c.rank >= c.world) { set_last_error("gemm_allreduce: bad rank/world"); return B200_ERR_ARG; }
-    if (c.out_peers == nullptr || c.inbox_peers == nullptr || c.flag_peers == nullptr) { set_last_error("gemm_allreduce: null peer table"); return B200_ERR_ARG; }
+    const bool nvls = c.part_mc != nullptr;
+    if (c.out_peers == nullptr || (!nvls && c.inbox_peers == nullptr) || c.flag_peers == nullptr) { set_last_error("gemm_allreduce: null peer table"); return B200_ERR_ARG; }
+    if (nvls && (c.part_local == nullptr || (c.broadcast && c.out_mc == nullptr) || c.adam != nullptr || c.world < 2 ||
+                 (reinterpret_cast<uintptr_t>(c.part_local) & 15) || (reinterpret_cast<uintptr_t>(c.part_mc) & 15) || (reinterpret_cast<uintptr_t>(c.out_mc) & 15))) {
+        set_last_error("gemm_allreduce_nvls: needs 16-byte aligned part_local / part_mc (and out_mc when broadcasting), world >= 2, no Adam"); return B200_ERR_ARG;
+    }
     if (c.seq == 0) { set_last_error("gemm_allreduce: seq must start at 1"); return B200_ERR_ARG; }
     if (c.ldo % 8 || c.ldo < c.N) { set_last_error("gemm_allreduce: ldo must be >= N and a multiple of 8"); return B200_ERR_ARG; }
     const int tm = (c.M + BM - 1) / BM, tn = (c.N + BN - 1) / BN;
@@ -461,12 +524,18 @@ static int fused_build(const FusedCall& c, FusedParams* out, int* grid_out) {
     if (p.owned_count > c.owned_cap || b200_fused_owned_tiles(c.M, c.N, c.world, c.owner_mode) > c.owned_cap) { set_last_error("gemm_allreduce: inbox too small (%d owned tiles, capacity %d)", p.owned_count, c.owned_cap); return B200_ERR_ARG; }
     if (c.broadcast && tm * tn > c.ready_cap) { set_last_error("gemm_allreduce: ready-flag capacity %d < %d tiles", c.ready_cap, tm * tn); return B200_ERR_ARG; }
     p.ready_base = c.owned_cap * MAX_WORLD_F;
+    p.part_local = reinterpret_cast<__nv_bfloat16*>(c.part_local);
+    p.part_mc = reinterpret_cast<const __nv_bfloat16*>(c.part_mc);
+    p.out_mc = reinterpret_cast<__nv_bfloat16*>(c.out_mc);
+    p.part_cap = c.ready_cap;
+    if (nvls && tm * tn > c.ready_cap) { set_last_error("gemm_allreduce_nvls: partial-tile capacity %d < %d tiles", c.ready_cap, tm * tn); return B200_ERR_ARG; }
     for (int i = 0; i < c.world; ++i) {
-        p.inbox[i] = c.inbox_peers[i];
+        p.inbox[i] = nvls ? nullptr : c.inbox_peers[i];
         p.flags[i] = reinterpret_cast<uint32_t*>(c.flag_peers[i]);
-        p.out[i] = (c.broadcast || i == c.rank) ? c.out_peers[i] : nullptr;
-        if (p.inbox[i] == nullptr || p.flags[i] == nullptr || ((c.broadcast || i == c.rank) && p.out[i] == nullptr)) { set_last_error("gemm_allreduce: null peer pointer for rank %d", i); return B200_ERR_ARG; }
-        if ((reinterpret_cast<uintptr_t>(p.inbox[i]) & 15) || ((c.broadcast || i == c.rank) && (reinterpret_cast<uintptr_t>(p.out[i]) & 15))) { set_last_error("gemm_allreduce: peer pointers must be 16-byte aligned"); return B200_ERR_ARG; }
+        const bool need_out = (c.broadcast && !nvls) || i == c.rank;       // NVLS broadcasts through out_mc; only its own copy is read
+        p.out[i] = need_out ? c.out_peers[i] : nullptr;
+        if ((!nvls && p.inbox[i] == nullptr) || p.flags[i] == nullptr || (need_out && p.out[i] == nullptr)) { set_last_error("gemm_allreduce: null peer pointer for rank %d", i); return B200_ERR_ARG; }
+        if ((reinterpret_cast<uintptr_t>(p.inbox[i]) & 15) || (need_out && (reinterpret_cast<uintptr_t>(p.out[i]) & 15))) { set_last_error("gemm_allreduce: peer pointers must be 16-byte aligned"); return B200_ERR_ARG; }
     }
     // every rank must use the same grid: owned tile k is reduced by CTA k %% grid on its owner
     int grid_cap = c.max_ctas > 0 ? c.max_ctas : num_sms();
@@ -519,8 +588,26 @@ static int fused_entry(const FusedCall& c, void* stream) {
         if (g_side_warps == 2) return launch_gemm<FusedEpiT<2, 0, 1>>(o, ap, c.max_ctas, st, rot, c.world, overlap);
         return launch_gemm<FusedEpiT<4, 32, 1>>(o, ap, c.max_ctas, st, rot, c.world, overlap);
     }
+    if (c.part_mc != nullptr) return launch_gemm<FusedEpiT<4, 32, 0, 1>>(o, p, c.max_ctas, st, rot, c.world, overlap);
     if (g_side_warps == 2) return launch_gemm<FusedEpiT<2, 0>>(o, p, c.max_ctas, st, rot, c.world, overlap);
     return launch_gemm<FusedEpiT<4, 32>>(o, p, c.max_ctas, st, rot, c.world, overlap);
+}
+
+// NVLS form of b200_gemm_allreduce_bf16 (op SUM or the in-place add; no optimizer update): partial tiles stay in this
+// rank's `part_local` ([2][ready_cap][128*256] bf16 = b200_fused_partial_bytes(ready_cap)), a block that every rank has
+// bound to ONE multicast object whose address is `part_mc`; `out_mc` is the multicast address of the output (needed when
+// broadcast != 0; out_peers[rank] is still the local copy).  Needs NVLS (b200_vmm_query).
+extern "C" long long b200_fused_partial_bytes(int ready_cap) { return 2ll * ready_cap * TILE_ELEMS * 2; }
+extern "C" int b200_gemm_allreduce_nvls_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
+                                             int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
+                                             void* part_local, const void* part_mc, void* out_mc, void* const* flag_peers,
+                                             int owned_cap, int ready_cap, int rank, int world, unsigned int seq, int owner_mode,
+                                             int op, int broadcast, float alpha, int max_ctas, void* stream) {
+    FusedCall c{A, lda, a_major, B, ldb, b_major, M, N, K, out_peers, ldo, out_row_offset, nullptr, flag_peers, owned_cap, ready_cap,
+                rank, world, seq, owner_mode, op, broadcast, alpha, max_ctas, nullptr};
+    c.part_local = part_local; c.part_mc = part_mc; c.out_mc = out_mc;
+    if (part_mc == nullptr) { set_last_error("gemm_allreduce_nvls: part_mc is null"); return B200_ERR_ARG; }
+    return fused_entry(c, stream);
 }
 
 extern "C" int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,

@@ -23,8 +23,8 @@
 // A operand (activations are kept transposed, [features, tokens], so that every forward GEMM is W * act^T) -
 // parallel/fused_fsdp_t.py.
 //
-// STATUS: written after round 1's GPU budget was spent - compiles for sm_100a, host-side maps are tested on the CPU,
-// never run on hardware.  Opt-in (TrainConfig.mp_mode = "spf"; B200_FSDP_FUSED_GATHER=1).
+// STATUS: validated on B200 in round 2 - single-GPU multi-rank emulation (tests/test_emu_gpu.py, 2/4/8 ranks, both forms) and
+// 2 GPUs (tests/test_multigpu.py: mp_spf, FSDP in-kernel gather).  Selected with TrainConfig.mp_mode = "spf" / fsdp_gather = "fused".
 #include "gemm_kernel.cuh"
 #include "peer_sync.cuh"
 #include "../include/b200ffn.h"

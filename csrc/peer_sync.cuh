@@ -9,6 +9,7 @@
 namespace b200 {
 
 constexpr int MAX_WORLD = 8;
+constexpr int COLL_FLAG_BLOCKS = 148;   // barrier slots per flag block = the largest grid a collective kernel may use
 
 struct PeerTable {
     void* p[MAX_WORLD];

@@ -326,56 +326,130 @@ extern "C" int b200_mc_attach(unsigned long long mc, int step, unsigned long lon
     return map_handle(a, (CUmemGenericAllocationHandle)mc, (size_t)bytes, 0, dev, ptr_out);
 }
 
-// ---- NVLS all-reduce (in-switch reduction) -------------------------------------------------------------------
-// Two-shot on the multicast address: rank r asks the switch for the SUM over all replicas of its slice
-// (multimem.ld_reduce, fp32 accumulation of bf16x2) and stores the result back through the multicast address so it
-// lands in every replica (multimem.st).  Per GPU and direction that is ~1x the message instead of the ~2x of the
-// peer-pointer two-shot in comm.cu.  Same flag protocol (values 3*epoch+k, one barrier slot per block).
+// ---- NVLS collectives (in-switch reduction / replication) ----------------------------------------------------------
+// On the multicast address of a block every rank has bound:
+//   all-reduce, two-shot   rank r asks the switch for the SUM over all replicas of slice r (multimem.ld_reduce, fp32
+//                          accumulation: SASS LDGMC...HPADD) and stores it through the multicast address into every
+//                          replica (multimem.st).  ~1x the message per GPU and direction (peer-pointer two-shot: ~2x).
+//   all-reduce, one-shot   latency-bound sizes: every rank reduces the WHOLE vector through the switch and stores its own
+//                          copy; no second phase.
+//   reduce-scatter         first half of the two-shot form, result stored locally into slice r.
+//   all-gather             rank r multimem.st's its slice: the switch replicates it into every copy.
+// Same flag protocol as comm.cu (values 3*epoch+k, one barrier slot per block, identical index->block maps everywhere).
 namespace b200 {
 
 constexpr int NVLS_THREADS = 256;
-constexpr int NVLS_MAX_BLOCKS = 64;
+constexpr int NVLS_MAX_BLOCKS = COLL_FLAG_BLOCKS;
+constexpr int NVLS_UNROLL = 4;                       // in-switch reductions in flight per thread (each is a switch round trip)
 
-__global__ void __launch_bounds__(NVLS_THREADS) nvls_all_reduce_bf16_kernel(uint4* mc, long long V, PeerTable flags, int rank, int world,
-                                                                            uint32_t epoch, unsigned int* err) {
+template <bool F32>
+__device__ __forceinline__ uint4 mm_ld_reduce(const uint4* p) {
+    uint4 v;
+    if constexpr (F32)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    else
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mm_st(uint4* p, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// MODE 0 two-shot all-reduce, 1 one-shot all-reduce, 2 reduce-scatter, 3 all-gather.  `mc` / `local`: the operand through
+// the multicast address / this rank's own copy.
+template <int MODE, bool F32>
+__global__ void __launch_bounds__(NVLS_THREADS) nvls_coll_kernel(uint4* mc, uint4* local, long long V, PeerTable flags, int rank, int world,
+                                                                 uint32_t epoch, unsigned int* err) {
     const long long tstride = (long long)gridDim.x * blockDim.x;
     const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long lo = V * rank / world, hi = V * (rank + 1) / world;
+    long long lo = 0, hi = V;
+    if (MODE != 1) { lo = V * rank / world; hi = V * (rank + 1) / world; }
     block_barrier(flags, rank, world, 3 * epoch + 1, err, 0x800);          // every replica holds its input
-    for (long long i = lo + t0; i < hi; i += tstride) {
-        uint32_t a, b, c, d;
-        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
-                     : "=r"(a), "=r"(b), "=r"(c), "=r"(d)
-                     : "l"(mc + i)
-                     : "memory");
-        asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc + i), "r"(a), "r"(b), "r"(c), "r"(d)
-                     : "memory");
+    if (MODE == 1) {                                                       // <= NVLS_UNROLL vectors per thread (launcher's contract)
+        uint4 v[NVLS_UNROLL];
+#pragma unroll
+        for (int u = 0; u < NVLS_UNROLL; ++u) {
+            const long long i = t0 + u * tstride;
+            if (i < V) v[u] = mm_ld_reduce<F32>(mc + i);
+        }
+        block_barrier(flags, rank, world, 3 * epoch + 2, err, 0x800);      // everyone has read everything: safe to overwrite
+#pragma unroll
+        for (int u = 0; u < NVLS_UNROLL; ++u) {
+            const long long i = t0 + u * tstride;
+            if (i < V) st_u4(local + i, v[u]);
+        }
+        return;
     }
-    block_barrier(flags, rank, world, 3 * epoch + 3, err, 0x800);          // every slice has been written to every replica
+    for (long long i = lo + t0; i < hi; i += tstride * NVLS_UNROLL) {
+        uint4 v[NVLS_UNROLL];
+#pragma unroll
+        for (int u = 0; u < NVLS_UNROLL; ++u) {
+            const long long idx = i + u * tstride;
+            if (idx < hi) v[u] = MODE == 3 ? ld_cv_u4(local + idx) : mm_ld_reduce<F32>(mc + idx);
+        }
+#pragma unroll
+        for (int u = 0; u < NVLS_UNROLL; ++u) {
+            const long long idx = i + u * tstride;
+            if (idx < hi) {
+                if (MODE == 2) st_u4(local + idx, v[u]);
+                else mm_st(mc + idx, v[u]);
+            }
+        }
+    }
+    block_barrier(flags, rank, world, 3 * epoch + 3, err, 0x800);          // every slice has landed in every replica / been read
 }
 
 }  // namespace b200
 
-// In-place all-reduce (SUM, bf16) of the `bytes` at the start of a multicast-bound block.  `mc_ptr` is the pointer
-// returned by b200_mc_attach(step 2); `flag_peers` is an ordinary peer table of b200_coll_flag_bytes() flag blocks.
-extern "C" int b200_all_reduce_nvls_bf16(void* mc_ptr, long long bytes, void* const* flag_peers, int rank, int world,
-                                         unsigned int epoch, int blocks, void* stream) {
-    if (mc_ptr == nullptr || flag_peers == nullptr || bytes <= 0 || (bytes % 16) || world < 2 || world > 8 || rank < 0 || rank >= world) {
-        set_last_error("all_reduce_nvls: bad arguments");
+static int nvls_launch(int mode, bool allow_one_shot, bool f32, void* mc_ptr, void* local_ptr, long long bytes, void* const* flag_peers, int rank, int world,
+                       unsigned int epoch, int blocks, void* stream, const char* what) {
+    if (mc_ptr == nullptr || local_ptr == nullptr || flag_peers == nullptr || bytes <= 0 || (bytes % 16) || world < 2 || world > 8 || rank < 0 || rank >= world) {
+        set_last_error("%s: bad arguments", what);
         return B200_ERR_ARG;
     }
     PeerTable flags{};
     for (int i = 0; i < world; ++i) {
-        if (flag_peers[i] == nullptr) { set_last_error("all_reduce_nvls: null flag pointer for rank %d", i); return B200_ERR_ARG; }
+        if (flag_peers[i] == nullptr) { set_last_error("%s: null flag pointer for rank %d", what, i); return B200_ERR_ARG; }
         flags.p[i] = flag_peers[i];
     }
     const long long V = bytes / 16;
-    if (blocks <= 0) {
-        const long long want = (V / world + NVLS_THREADS * 4 - 1) / (NVLS_THREADS * 4);
+    if (mode == 0 && allow_one_shot && V <= (long long)NVLS_UNROLL * NVLS_THREADS * 32) mode = 1;     // <= 512 KiB: one-shot
+    if (mode == 1) {
+        blocks = (int)((V + NVLS_THREADS * NVLS_UNROLL - 1) / (NVLS_THREADS * NVLS_UNROLL));
+    } else if (blocks <= 0) {
+        const long long want = (V / world + NVLS_THREADS * NVLS_UNROLL - 1) / (NVLS_THREADS * NVLS_UNROLL);
         blocks = (int)(want < 1 ? 1 : (want > NVLS_MAX_BLOCKS ? NVLS_MAX_BLOCKS : want));
     }
     if (blocks > NVLS_MAX_BLOCKS) blocks = NVLS_MAX_BLOCKS;
-    nvls_all_reduce_bf16_kernel<<<blocks, NVLS_THREADS, 0, reinterpret_cast<cudaStream_t>(stream)>>>(reinterpret_cast<uint4*>(mc_ptr), V, flags, rank, world,
-                                                                                                    epoch, device_error_slot());
-    return check_cuda(cudaGetLastError(), "all_reduce_nvls launch");
+    if (blocks < 1) blocks = 1;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    uint4* mc = reinterpret_cast<uint4*>(mc_ptr);
+    uint4* lc = reinterpret_cast<uint4*>(local_ptr);
+    unsigned int* err = device_error_slot();
+#define B200_NVLS(MODE_)                                                                                                      \
+    do {                                                                                                                      \
+        if (f32) nvls_coll_kernel<MODE_, true><<<blocks, NVLS_THREADS, 0, st>>>(mc, lc, V, flags, rank, world, epoch, err);     \
+        else nvls_coll_kernel<MODE_, false><<<blocks, NVLS_THREADS, 0, st>>>(mc, lc, V, flags, rank, world, epoch, err);        \
+    } while (0)
+    switch (mode) {
+        case 0: B200_NVLS(0); break;
+        case 1: B200_NVLS(1); break;
+        case 2: B200_NVLS(2); break;
+        default: B200_NVLS(3); break;
+    }
+#undef B200_NVLS
+    return check_cuda(cudaGetLastError(), what);
+}
+
+// In-place collectives on `bytes` at `mc_ptr` (multicast address, from b200_mc_attach step 2) / `local_ptr` (this rank's
+// own mapping of the same bytes); `flag_peers`: an ordinary peer table of b200_coll_flag_bytes() flag blocks.
+extern "C" int b200_all_reduce_nvls_bf16(void* mc_ptr, long long bytes, void* const* flag_peers, int rank, int world,
+                                         unsigned int epoch, int blocks, void* stream) {
+    // (round-1 signature: no local pointer - always the two-shot form, which needs none)
+    return nvls_launch(0, false, false, mc_ptr, mc_ptr, bytes, flag_peers, rank, world, epoch, blocks, stream, "all_reduce_nvls");
+}
+extern "C" int b200_nvls_collective(int op, int f32, void* mc_ptr, void* local_ptr, long long bytes, void* const* flag_peers, int rank,
+                                    int world, unsigned int epoch, int blocks, void* stream) {
+    if (op < 0 || op > 2) { set_last_error("nvls_collective: op must be 0 (all-reduce), 1 (reduce-scatter) or 2 (all-gather)"); return B200_ERR_ARG; }
+    return nvls_launch(op == 0 ? 0 : op + 1, true, f32 != 0, mc_ptr, local_ptr, bytes, flag_peers, rank, world, epoch, blocks, stream, "nvls_collective");
 }

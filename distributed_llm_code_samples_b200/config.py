@@ -56,6 +56,7 @@ class TrainConfig:
                                            # fused = inside the consuming GEMMs, forward and backward (parallel/fused_fsdp_t.py)
     mp_input: str = "full"                 # Engine.train under MP all-reduce form: full = every rank stages the whole batch (:294, :324);
                                            # sharded = 1/world over PCIe + NVLink all-gather (ShardedPrefetcher)
+    nvls: str = "auto"                     # fused MP all-reduce: auto = sum inside the NVSwitch where the box has NVLS; off = peer pushes
     master_port: int = 29500               # train_ffns.py:124
     save_path: Optional[str] = None
     load_path: Optional[str] = None
@@ -76,6 +77,8 @@ class TrainConfig:
             raise ValueError("mp_mode must be ar, sp or spf")
         if self.fsdp_gather not in ("dma", "fused"):
             raise ValueError("fsdp_gather must be dma or fused")
+        if self.nvls not in ("auto", "off"):
+            raise ValueError("nvls must be auto or off")
         if self.mp_input not in ("full", "sharded"):
             raise ValueError("mp_input must be full or sharded")
         parse_dtype(self.dtype)

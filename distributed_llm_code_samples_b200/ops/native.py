@@ -127,6 +127,9 @@ def _optional_declare(lib) -> None:
         "b200_gather_gemm_bf16": ([pp, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp], i),
         "b200_debug_gather_chunk": ([i, i, i, i, ll, C.POINTER(ll)], i),
         "b200_fused_config": ([i, i], i),
+        "b200_fused_partial_bytes": ([i], ll),
+        "b200_nvls_collective": ([i, i, vp, vp, ll, pp, i, i, u, i, vp], i),
+        "b200_gemm_allreduce_nvls_bf16": ([vp, ll, i, vp, ll, i, i, i, i, pp, ll, i, vp, vp, vp, pp, i, i, i, i, u, i, i, i, f, i, vp], i),
         "b200_sgd_f32": ([vp, vp, ll, f, vp], i),
         "b200_adam_f32": ([vp, vp, vp, vp, ll, f, f, f, f, i, vp], i),
         "b200_colsum_scratch_bytes": ([i, i], ll),

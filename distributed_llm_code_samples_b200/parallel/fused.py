@@ -8,7 +8,7 @@ collectives (``csrc/comm.cu``) - no NCCL on the data path.
   one-warp barrier kernels) straight into the contiguous buffer the GEMM reads (``:203-209``, ``:236-249``).
 * ``FusedMPTrainer``   row-parallel GEMM -> all-reduce of the partial activations inside the kernel
   (``:302-303``, ``:308-309``), or (``mp_mode="sp"``) -> reduce-scatter over token shards + native all-gather, or
-  (``mp_mode="spf"``, not yet run on hardware) the all-gather fused into the column-parallel GEMM as well.
+  (``mp_mode="spf"``) the all-gather fused into the column-parallel GEMM as well.
 """
 from __future__ import annotations
 
@@ -42,18 +42,38 @@ def _tiles(M: int, N: int) -> int:
 class FusedChannel:
     """Inbox + flags + call counter for one stream of fused GEMM+collective calls."""
 
-    def __init__(self, sw: SymmWorld, owned_cap: int, ready_cap: int):
+    def __init__(self, sw: SymmWorld, owned_cap: int, ready_cap: int, nvls: bool = False):
+        """``nvls=True`` (activations of the MP paths, where the box has NVLS): partial tiles stay in a local, multicast-
+        bound buffer and the owner sums them inside the NVSwitch, instead of every rank pushing into the owner's inbox."""
         lib = nv.load()
         self.sw, self.owned_cap, self.ready_cap = sw, owned_cap, ready_cap
-        self.inbox = sw.alloc(int(lib.b200_fused_inbox_bytes(owned_cap, sw.world)))
+        self.part = None
+        if nvls and sw.multicast_supported():
+            self.part = sw.alloc(int(lib.b200_fused_partial_bytes(ready_cap)), multicast=True)
+            self.inbox = None
+        else:
+            self.inbox = sw.alloc(int(lib.b200_fused_inbox_bytes(owned_cap, sw.world)))
         self.flags = sw.alloc(int(lib.b200_fused_flag_bytes(owned_cap, ready_cap)))
         self.seq = 0
 
+    @property
+    def nvls(self) -> bool:
+        return self.part is not None
+
     def gemm(self, A: torch.Tensor, a_major: int, B: torch.Tensor, b_major: int, M: int, N: int, K: int,
              out_peers, ldo: int, out_row_offset: int, owner_mode: int, op: int, broadcast: bool, alpha: float = 1.0,
-             max_ctas: int = 0) -> None:
+             max_ctas: int = 0, out_mc: Optional[int] = None) -> None:
         self.seq += 1
         sw = self.sw
+        if self.part is not None:
+            assert not broadcast or out_mc, "the NVLS form broadcasts through the output's multicast address"
+            rc = nv.load().b200_gemm_allreduce_nvls_bf16(
+                A.data_ptr(), A.stride(0), a_major, B.data_ptr(), B.stride(0), b_major, M, N, K, out_peers, ldo,
+                out_row_offset, self.part.ptr, self.part.mc_ptr, out_mc, self.flags.peers_c, self.owned_cap, self.ready_cap,
+                sw.rank, sw.world, self.seq, owner_mode, op, int(broadcast), float(alpha), int(max_ctas), nv._stream())
+            nv._check(rc, "b200_gemm_allreduce_nvls_bf16")
+            nv.launch_count += 1
+            return
         rc = nv.load().b200_gemm_allreduce_bf16(
             A.data_ptr(), A.stride(0), a_major, B.data_ptr(), B.stride(0), b_major, M, N, K, out_peers, ldo,
             out_row_offset, self.inbox.peers_c, self.flags.peers_c, self.owned_cap, self.ready_cap, sw.rank, sw.world,
@@ -71,7 +91,7 @@ class FusedChannel:
     def gemm_adam(self, A: torch.Tensor, a_major: int, B: torch.Tensor, b_major: int, M: int, N: int, K: int,
                   out_peers, ldo: int, out_row_offset: int, owner_mode: int, broadcast: bool, state, lr: float, step: int,
                   beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, grad_scale: float = 1.0, max_ctas: int = 0) -> None:
-        """As ``gemm`` with FOP_SGD, but the owner applies Adam (NOT YET RUN ON HARDWARE)."""
+        """As ``gemm`` with FOP_SGD, but the owner applies Adam (moments sharded by tile owner)."""
         self.seq += 1
         sw = self.sw
         m, v = state
@@ -92,7 +112,7 @@ def _owned_cap(shapes, world: int, owner_mode: int) -> int:
 class GatherChannel:
     """Flags + call counter for one stream of all-gather -> GEMM calls (``csrc/gather_gemm.cu``).
 
-    NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent)."""
+    Validated on B200 in round 2 (2 GPUs and the single-GPU multi-rank emulation, ``tests/test_emu_gpu.py``)."""
 
     def __init__(self, sw: SymmWorld, max_rows: int):
         lib = nv.load()
@@ -494,18 +514,23 @@ class FusedMPTrainer:
             self.chan = FusedChannel(self.sw, _owned_cap([(T, D)], n, OWN_ROW_SHARDED), _tiles(T, D))
             self.coll = CollChannel(self.sw)
         else:
-            self.abuf = self.sw.alloc((self.L + 2) * T * D * 2 + 8192)
-            self.y, self.y_tab = [], []
+            nvls = self.cfg.nvls != "off"
+            self.abuf = self.sw.alloc((self.L + 2) * T * D * 2 + 8192, multicast=nvls)
+            self.y, self.y_tab, self.y_mc = [], [], []
             for _ in range(self.L):
                 t, o = self.abuf.carve((T, D), torch.bfloat16)
                 self.y.append(t)
                 self.y_tab.append(self.abuf.peers_at(o))
-            self.dx, self.dx_tab = [], []
+                self.y_mc.append(self.abuf.mc_at(o))
+            self.dx, self.dx_tab, self.dx_mc = [], [], []
             for _ in range(2):
                 t, o = self.abuf.carve((T, D), torch.bfloat16)
                 self.dx.append(t)
                 self.dx_tab.append(self.abuf.peers_at(o))
-            self.chan = FusedChannel(self.sw, _owned_cap([(T, D)], n, OWN_INTERLEAVED), _tiles(T, D))
+                self.dx_mc.append(self.abuf.mc_at(o))
+            self.chan = FusedChannel(self.sw, _owned_cap([(T, D)], n, OWN_INTERLEAVED), _tiles(T, D), nvls=nvls and self.abuf.mc_ptr is not None)
+            if self.chan.nvls:
+                self.comm_name = "fused: row-parallel GEMM + all-reduce in one kernel, summed in the NVSwitch (multimem.ld_reduce / multimem.st)"
         self.T = T
         self.sw.host_barrier()
 
@@ -522,9 +547,9 @@ class FusedMPTrainer:
             saved.append((y, None if self.opts.recompute else a, None if self.opts.recompute else pre))
             # y_l = sum over ranks of a_r @ W2_r^T (+ b2 + x), delivered to every rank - one kernel (:302-303)
             if self._prefill(self.y[l], l, y if self.residual else None):
-                self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SGD, True, -1.0)
+                self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SGD, True, -1.0, out_mc=self.y_mc[l])
             else:
-                self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
+                self.chan.gemm(a, nv.MAJOR_K, W2, nv.MAJOR_K, T, D, Fs, self.y_tab[l], D, 0, OWN_INTERLEAVED, FOP_SUM, True, out_mc=self.y_mc[l])
             y = self.y[l]
         d = dloss_dx
         for i in reversed(range(self.L)):
@@ -539,9 +564,9 @@ class FusedMPTrainer:
                 slot = i % 2
                 # dx = sum over ranks of dh_r @ W1_r (+ d), delivered to every rank - one kernel (:308-309)
                 if self._prefill(self.dx[slot], None, d if self.residual else None):
-                    self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SGD, True, -1.0)
+                    self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SGD, True, -1.0, out_mc=self.dx_mc[slot])
                 else:
-                    self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SUM, True)
+                    self.chan.gemm(dh, nv.MAJOR_K, W1, nv.MAJOR_MN, T, D, Fs, self.dx_tab[slot], D, 0, OWN_INTERLEAVED, FOP_SUM, True, out_mc=self.dx_mc[slot])
                 dn = self.dx[slot]
             self.update_local(W1, dh, xin)
             self.update_bias(i, dh, d)

@@ -18,7 +18,7 @@ layers' weights are still complete from the forward pass and are used as they ar
 layer's, ``:244``).  No copy-engine prefetch is left in this trainer.  The schedule is ``fsdp_t_step`` below, written
 against three primitives so that it is checked on CPU (``tests/test_fsdp_t_schedule_cpu.py``).
 
-NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent); opt-in with ``B200_FSDP_FUSED_GATHER=1``.
+Validated on B200 in round 2 (2 GPUs, ``profiles/tests/r2_call1_2gpu``); selected with ``TrainConfig.fsdp_gather = "fused"`` (``--fsdp_gather fused``).
 """
 from __future__ import annotations
 

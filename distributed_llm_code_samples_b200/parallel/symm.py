@@ -54,6 +54,7 @@ class SymmBuffer:
         else:
             self.peer_ptrs = [self.ptr]
         self.peers_c = (C.c_void_p * world.world)(*self.peer_ptrs)
+        self.mc_ptr: Optional[int] = None          # (VmmBuffer blocks have one where the box does NVLS)
         self._base = torch.as_tensor(_CudaArray(self.ptr, nbytes), device=world.device)
         self._cursor = 0
 
@@ -76,6 +77,9 @@ class SymmBuffer:
     def peers_at(self, offset_bytes: int):
         """ctypes array of every rank's pointer to ``offset_bytes`` inside this block."""
         return (C.c_void_p * self.world.world)(*[p + offset_bytes for p in self.peer_ptrs])
+
+    def mc_at(self, offset_bytes: int) -> Optional[int]:
+        return None
 
     def offset_of(self, t: torch.Tensor) -> int:
         off = t.data_ptr() - self.ptr
@@ -102,12 +106,31 @@ class SymmWorld:
     def __init__(self, rank: int, world: int, device: torch.device, group: Optional[dist.ProcessGroup] = None):
         self.rank, self.world, self.device, self.group = rank, world, device, group
         self.buffers: List[SymmBuffer] = []
+        self._mc_ok: Optional[bool] = None
+        self._vmm_count = 0
         torch.cuda.set_device(device)
 
-    def alloc(self, nbytes: int) -> SymmBuffer:
-        """Collective: every rank must call with the same size in the same order."""
+    def multicast_supported(self) -> bool:
+        """NVLS on this box: POSIX-fd shareable cuMem blocks + multicast objects, and more than one rank to bind."""
+        if self._mc_ok is None:
+            from . import vmm
+            fd_ok, mc_ok = vmm.supported() if self.world > 1 else (False, False)
+            ok = torch.tensor([int(fd_ok and mc_ok)], device=self.device)
+            if self.world > 1:
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)     # all ranks or none
+            self._mc_ok = bool(ok.item())
+        return self._mc_ok
+
+    def alloc(self, nbytes: int, multicast: bool = False):
+        """Collective: every rank must call with the same size in the same order.  ``multicast=True`` (where the box has
+        NVLS) returns a cuMem VMM block bound to a multicast object (``.mc_ptr``), else a cudaMalloc + CUDA-IPC block."""
         nbytes = (nbytes + 255) // 256 * 256
-        b = SymmBuffer(self, nbytes)
+        if multicast and self.multicast_supported():
+            from .vmm import VmmBuffer
+            self._vmm_count += 1
+            b = VmmBuffer(self.rank, self.world, self.device, nbytes, multicast=True, group=self.group, tag=f"sw{self._vmm_count}_")
+        else:
+            b = SymmBuffer(self, nbytes)
         self.buffers.append(b)
         return b
 
@@ -163,7 +186,7 @@ class SymmComm:
         self.chans = (CollChannel(sw), CollChannel(sw))          # [0] blocking lane, [1] async (side-stream) lane
         self.chan = self.chans[0]
         half = (staging_bytes + 255) // 256 * 256
-        self.staging = sw.alloc(2 * half)
+        self.staging = sw.alloc(2 * half, multicast=True)       # NVLS-capable where the box has it (else a plain IPC block)
         self._stage_half = half
         self.side = torch.cuda.Stream(device=sw.device)
         self.lib = nv.load()
@@ -194,6 +217,16 @@ class SymmComm:
         """(channel, staging offset) of the lane a call runs in."""
         return (self.chans[1], self._stage_half) if async_op else (self.chans[0], 0)
 
+    def _reduce(self, op: int, buf, off: int, nbytes: int, f32: bool, chan: "CollChannel", e: int, s, fallback) -> None:
+        """All-reduce (op 0) / reduce-scatter (op 1) of ``nbytes`` at ``off`` of symmetric block ``buf``: inside the
+        NVSwitch when the block is multicast-bound (multimem.ld_reduce / multimem.st), else on the peer-pointer kernels."""
+        if getattr(buf, "mc_ptr", None):
+            nv._check(self.lib.b200_nvls_collective(op, int(f32), buf.mc_ptr + off, buf.ptr + off, nbytes, chan.flags.peers_c,
+                                                    self.rank, self.world, e, 0, s), "b200_nvls_collective")
+        else:
+            nv._check(fallback(buf.peers_c, off, nbytes, chan.flags.peers_c, self.rank, self.world, e, 0, s),
+                      "b200_all_reduce" if op == 0 else "b200_reduce_scatter")
+
     def _stage_check(self, nbytes: int) -> None:
         if nbytes > self._stage_half:
             raise ValueError(f"operand of {nbytes} bytes exceeds the symmetric staging buffer ({self._stage_half}); "
@@ -215,15 +248,14 @@ class SymmComm:
         e = chan.next_epoch()
         if buf is not None and (t.numel() * es) % 16 == 0:
             off = buf.offset_of(t)
-            return self._run(lambda s: nv._check(fn(buf.peers_c, off, nbytes, chan.flags.peers_c, self.rank, self.world, e, 0, s),
-                                                 "b200_all_reduce"), async_op)
+            return self._run(lambda s: self._reduce(0, buf, off, nbytes, es == 4, chan, e, s, fn), async_op)
         self._stage_check(nbytes)
         st = self.staging.tensor(soff, (nbytes // es,), t.dtype)
 
         def go(s):
             st[t.numel():].zero_()                                   # the padding lanes are summed too
             st[: t.numel()].copy_(t.reshape(-1))
-            nv._check(fn(self.staging.peers_c, soff, nbytes, chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_all_reduce")
+            self._reduce(0, self.staging, soff, nbytes, es == 4, chan, e, s, fn)
             t.reshape(-1).copy_(st[: t.numel()])
         return self._run(go, async_op)
 
@@ -262,7 +294,7 @@ class SymmComm:
             off = buf.offset_of(full)
 
             def go(s):
-                nv._check(rs(buf.peers_c, off, nbytes, chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_reduce_scatter")
+                self._reduce(1, buf, off, nbytes, es == 4, chan, e, s, rs)
                 out.reshape(-1).copy_(full.reshape(-1)[self.rank * (sl // es): (self.rank + 1) * (sl // es)])
             return self._run(go, async_op)
         self._stage_check(nbytes)
@@ -270,7 +302,7 @@ class SymmComm:
 
         def go2(s):
             st.copy_(full.reshape(-1))
-            nv._check(rs(self.staging.peers_c, soff, nbytes, chan.flags.peers_c, self.rank, self.world, e, 0, s), "b200_reduce_scatter")
+            self._reduce(1, self.staging, soff, nbytes, es == 4, chan, e, s, rs)
             out.reshape(-1).copy_(st[self.rank * (sl // es): (self.rank + 1) * (sl // es)])
         return self._run(go2, async_op)
 

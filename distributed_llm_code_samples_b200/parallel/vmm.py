@@ -2,8 +2,9 @@
 
 Same peer-table contract as ``symm.SymmBuffer`` (CUDA IPC), plus ``mc_ptr``: a multicast address on which
 ``multimem.ld_reduce`` / ``multimem.st`` reduce and broadcast inside the NVSwitch.  File descriptors travel between the
-ranks of the node over unix datagram sockets (``SCM_RIGHTS``).  Round 1 status: host side unit-tested on CPU
-(``tests/test_vmm_cpu.py``); device side compiled, GPU test queued (``tests/test_multigpu.py::test_vmm_multicast_all_reduce``).
+ranks of the node over unix datagram sockets (``SCM_RIGHTS``).  Validated on B200 in round 2 (``profiles/tests/``):
+``tests/test_multigpu.py::test_vmm_multicast_all_reduce``; ``SymmWorld.alloc(..., multicast=True)`` hands these blocks to
+the fused MP trainer, whose all-reduce then sums inside the switch.
 """
 from __future__ import annotations
 
@@ -42,7 +43,8 @@ class VmmBuffer:
         if gran <= 0:
             raise nv.NativeError("VMM allocation granularity query failed: " + lib.b200_last_error().decode())
         self.nbytes = (nbytes + gran - 1) // gran * gran
-        tag = f"{tag}{os.getpid() if world == 1 else ''}"
+        # unique per job on this host: ranks of one job share MASTER_PORT; a world of one uses its pid
+        tag = f"{tag}{os.environ.get('MASTER_PORT', '') if world > 1 else os.getpid()}"
         ptr, handle, fd = C.c_void_p(), C.c_ulonglong(), C.c_int()
         nv._check(lib.b200_vmm_alloc(self.nbytes, C.byref(ptr), C.byref(handle), C.byref(fd)), "b200_vmm_alloc")
         self.ptr, self.handle = ptr.value, handle.value
@@ -105,11 +107,53 @@ class VmmBuffer:
         except OSError:
             pass
 
-    def tensor(self, offset_bytes: int, shape, dtype: torch.dtype) -> torch.Tensor:
         from .symm import _CudaArray
-        base = torch.as_tensor(_CudaArray(self.ptr, self.nbytes), device=self.device)
+        self._base = torch.as_tensor(_CudaArray(self.ptr, self.nbytes), device=self.device)
+        self._cursor = 0
+        self._base.zero_()                                 # cuMemCreate memory is not zeroed; flags and counters rely on it
+        torch.cuda.synchronize(device)
+        if world > 1:
+            dist.barrier(group=group)
+
+    # ---- the SymmBuffer interface (parallel/symm.py) ---------------------------------------------------------------
+    def tensor(self, offset_bytes: int, shape, dtype: torch.dtype) -> torch.Tensor:
         n = 1
         for s in shape:
             n *= s
         nb = n * torch.empty((), dtype=dtype).element_size()
-        return base[offset_bytes: offset_bytes + nb].view(dtype).view(*shape)
+        assert offset_bytes % 16 == 0 and offset_bytes + nb <= self.nbytes, (offset_bytes, nb, self.nbytes)
+        return self._base[offset_bytes: offset_bytes + nb].view(dtype).view(*shape)
+
+    def carve(self, shape, dtype: torch.dtype, align: int = 256):
+        off = (self._cursor + align - 1) // align * align
+        t = self.tensor(off, shape, dtype)
+        self._cursor = off + t.numel() * t.element_size()
+        return t, off
+
+    def peers_at(self, offset_bytes: int):
+        return (C.c_void_p * self.world)(*[p + offset_bytes for p in self.peer_ptrs])
+
+    def mc_at(self, offset_bytes: int) -> Optional[int]:
+        """The multicast address of ``offset_bytes`` inside the block (None without NVLS)."""
+        return None if self.mc_ptr is None else self.mc_ptr + offset_bytes
+
+    def offset_of(self, t: torch.Tensor) -> int:
+        off = t.data_ptr() - self.ptr
+        assert 0 <= off < self.nbytes, "tensor is not inside this symmetric block"
+        return off
+
+    def contains(self, t: torch.Tensor) -> bool:
+        return self.ptr <= t.data_ptr() < self.ptr + self.nbytes
+
+    def close(self) -> None:
+        """Unmap the peers' blocks and free mine.  (The multicast object and its mapping are left to process exit: every
+        rank would have to unbind before anyone releases, and nothing here reuses the address range.)"""
+        lib = nv.load()
+        self._base = None
+        for q in range(self.world):
+            if q != self.rank and self.peer_ptrs[q]:
+                lib.b200_vmm_free(C.c_void_p(self.peer_ptrs[q]), self.nbytes, C.c_ulonglong(self.peer_handles[q]))
+                self.peer_ptrs[q] = 0
+        if self.ptr and self.mc_ptr is None:
+            lib.b200_vmm_free(C.c_void_p(self.ptr), self.nbytes, C.c_ulonglong(self.handle))
+        self.ptr = 0

@@ -133,7 +133,7 @@ class ShardedPrefetcher:
     round 1's measurements, where MP's end-to-end rate was 15 % below its device-timed rate in both arms).
     Every rank must iterate the same batches.  The reference copies the full batch on every rank (``train_ffns.py:294``).
 
-    NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent); opt-in with ``B200_MP_SHARDED_INPUT=1``."""
+    Selected with ``TrainConfig.mp_input = "sharded"`` (``--mp_input sharded``)."""
 
     def __init__(self, batches: Iterator[Tuple[torch.Tensor, torch.Tensor]], device: torch.device, sw, rank: int, world: int):
         from ..parallel.symm import CollChannel

@@ -7,7 +7,7 @@ torch glue between them all land on the capture stream - and replays it with one
 Scope: one GPU, SGD.  Not capturable: Adam (its step count is a kernel ARGUMENT, frozen at capture), and the
 peer-memory fused kernels (their per-call sequence numbers are kernel arguments too, and they wait on other ranks).
 
-NOT YET RUN ON HARDWARE: written after round 1's GPU budget was spent (tests/test_train_gpu.py, queued).
+Validated on B200 in round 2 (``tests/test_train_gpu.py::test_cuda_graph_replay_matches_eager_steps``).
 
 The reference has no counterpart (eager PyTorch, ``train_ffns.py:101-116``).
 """

@@ -187,8 +187,12 @@ int b200_gemm_allreduce_bf16(const void* A, long long lda, int a_major, const vo
  * `adam_m` / `adam_v`: LOCAL fp32 moments of the tiles this rank owns, compact layout [owned slot][128][256]
  * (b200_fused_adam_state_bytes(owned_cap) bytes each, zeroed by the caller before the first step): every rank holds
  * 1/world of the optimizer state, for DDP as well as FSDP.  `step` >= 1 (bias correction).  No counterpart in the
- * reference (SGD only, train_ffns.py:172).  NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent). */
+ * reference (SGD only, train_ffns.py:172).  */
 long long b200_fused_adam_state_bytes(int owned_cap);
+/* Kernel variant for the fused calls of this process: side_warps 2 (384 threads, 168 registers) or 4 (448 threads, 128
+ * registers; default); overlap -1 = per call, 0 = CTA-pair mainloop, 1 = double-buffered 1-CTA mainloop.  Out-of-range
+ * values leave a setting unchanged.  Returns side_warps * 10 + (overlap + 1).  Every rank must use the same settings. */
+int b200_fused_config(int side_warps, int overlap);
 int b200_gemm_allreduce_adam_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
                                   int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
                                   void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
@@ -213,7 +217,7 @@ int b200_gemm_allreduce_adam_bf16(const void* A, long long lda, int a_major, con
  * The kernel never waits for peers to finish reading a shard: the caller must not overwrite its shard before a later
  * collective that every rank enters after this call (docs/KERNELS.md 2.5).
  * No counterpart in the reference (it all-reduces, train_ffns.py:303,:309); this is the sequence-parallel form
- * SURVEY.md 2.6 plans for C4/C5.  NOT YET RUN ON HARDWARE (written after round 1's GPU budget was spent). */
+ * SURVEY.md 2.6 plans for C4/C5.  */
 long long b200_gather_gemm_ready_bytes(int M);
 int b200_gather_gemm_bf16(void* const* a_peers, int a_major, const void* B, long long ldb, int b_major, void* C, long long ldc,
                           int M, int N, int K, int epilogue, const void* aux, long long ldaux, void* out2, long long ldc2,
@@ -228,9 +232,29 @@ int b200_debug_gather_tile_walk(int M, int N, int rank, int world, int* first_ro
  * storage block, that block's index, kb_rot, num_kb, blocks per shard} */
 int b200_debug_gather_kwalk(int K, int rank, int world, int kb, int* out);
 
-/* ---- EXPERIMENTAL: cuMem VMM blocks + NVLS multicast (csrc/vmm.cu) -----------------------------------------------
- * The runtime the in-switch reductions need; not used by the default training paths.  Host-side fd
- * passing is unit-tested on CPU; the device side has GPU tests queued (tests/test_multigpu.py::test_vmm_*).
+/* ---- several ranks of the fused kernels as slices of ONE cooperative launch on one GPU (tests, ncu) ---------------------
+ * Kernels that spin on one another's flags cannot be separate launches on one device (nothing makes them co-resident),
+ * so CTAs [r * ctas_per_rank, (r + 1) * ctas_per_rank) of a single grid run rank r's kernel body - its own operands, owner
+ * maps, tile walk, flags - against peer tables whose entries are all local memory.  Per-rank inputs are HOST arrays of
+ * `world` device pointers; peer tables as in the real entry points; `table`: b200_emu_table_bytes() bytes of device
+ * scratch; ctas_per_rank even, world * ctas_per_rank <= SM count.  adam_m == NULL selects `op`, else Adam.  No counterpart
+ * in the reference (its multi-rank paths need as many GPUs as ranks). */
+long long b200_emu_table_bytes(void);
+int b200_emu_gemm_allreduce_bf16(int world, const void* const* A, long long lda, int a_major, const void* const* B, long long ldb,
+                                 int b_major, int M, int N, int K, void* const* out_peers, long long ldo,
+                                 void* const* inbox_peers, void* const* flag_peers, int owned_cap, int ready_cap,
+                                 unsigned int seq, int owner_mode, int op, int broadcast, float alpha,
+                                 float* const* adam_m, float* const* adam_v, float lr, float beta1, float beta2, float eps,
+                                 int step, float grad_scale, int ctas_per_rank, void* table, void* stream);
+int b200_emu_gather_gemm_bf16(int world, void* const* a_peers, int a_major, const void* const* B, long long ldb, int b_major,
+                              void* const* C, long long ldc, int M, int N, int K, int epilogue, const void* const* aux,
+                              long long ldaux, void* const* out2, long long ldc2, void* const* started_peers,
+                              void* const* ready, unsigned int seq, int ctas_per_rank, void* table, void* stream);
+
+/* ---- cuMem VMM blocks + NVLS multicast (csrc/vmm.cu) -----------------------------------------------------------
+ * The runtime the in-switch reductions need: symmetric blocks the fused MP trainer allocates with
+ * SymmWorld.alloc(multicast=True) where the box has NVLS.  Host-side fd passing is unit-tested on CPU; the device side
+ * runs in tests/test_multigpu.py::test_vmm_* (B200, 2 GPUs: profiles/tests/).
  * Descriptor passing between the ranks of one node (SCM_RIGHTS over a unix datagram socket): */
 int b200_fd_listen(const char* path);              /* returns the listening socket fd */
 int b200_fd_send(const char* path, int fd, int tag);
@@ -251,6 +275,22 @@ int b200_mc_attach(unsigned long long mc, int step, unsigned long long mem_handl
  * result to every replica.  Counterpart of train_ffns.py:165/:303 on NVLS. */
 int b200_all_reduce_nvls_bf16(void* mc_ptr, long long bytes, void* const* flag_peers, int rank, int world,
                               unsigned int epoch, int blocks, void* stream);
+/* In-place NVLS collectives on `bytes` of a multicast-bound block: op 0 all-reduce (one-shot below 512 KiB, else
+ * two-shot), 1 reduce-scatter (slice `rank` of the local copy holds the sum), 2 all-gather (slice `rank` is the input).
+ * f32 != 0: fp32 payload, else bf16 with fp32 accumulation in the switch.  `mc_ptr` / `local_ptr`: the operand through
+ * the multicast address / this rank's own mapping.  Counterparts of test_nccl.py:16,25,35 on NVLS. */
+int b200_nvls_collective(int op, int f32, void* mc_ptr, void* local_ptr, long long bytes, void* const* flag_peers, int rank,
+                         int world, unsigned int epoch, int blocks, void* stream);
+/* NVLS form of b200_gemm_allreduce_bf16 (op 0 SUM or op 1 with alpha = -1: in-place add; no optimizer): partial tiles
+ * stay in this rank's `part_local` (b200_fused_partial_bytes(ready_cap) bytes of a block every rank bound to one
+ * multicast object, address `part_mc`); the owner sums them in the switch (multimem.ld_reduce, fp32 accumulate) and, with
+ * broadcast != 0, stores the result through `out_mc`, the output's multicast address.  Reference sites: :303, :309. */
+long long b200_fused_partial_bytes(int ready_cap);
+int b200_gemm_allreduce_nvls_bf16(const void* A, long long lda, int a_major, const void* B, long long ldb, int b_major,
+                                  int M, int N, int K, void* const* out_peers, long long ldo, int out_row_offset,
+                                  void* part_local, const void* part_mc, void* out_mc, void* const* flag_peers,
+                                  int owned_cap, int ready_cap, int rank, int world, unsigned int seq, int owner_mode,
+                                  int op, int broadcast, float alpha, int max_ctas, void* stream);
 
 #ifdef __cplusplus
 }

@@ -34,13 +34,17 @@ class _FakeBuffer(symm.SymmBuffer):
         self.peer_ptrs = [self.ptr] * world.world
         self.peers_c = (C.c_void_p * world.world)(*self.peer_ptrs)
         self._opened, self._cursor = [], 0
+        self.mc_ptr = None
 
 
 class _FakeWorld:
     def __init__(self, rank, world):
         self.rank, self.world, self.device, self.group, self.buffers = rank, world, torch.device("cpu"), None, []
 
-    def alloc(self, nbytes):
+    def multicast_supported(self):
+        return False
+
+    def alloc(self, nbytes, multicast=False):
         b = _FakeBuffer(self, (nbytes + 255) // 256 * 256)
         self.buffers.append(b)
         return b

@@ -11,7 +11,8 @@ rank, world, dev = init_from_env("cuda", "nccl")
 sw = SymmWorld(rank, world, dev)
 comm = SymmComm(sw, staging_bytes=1 << 20)
 max_bytes = int(sys.argv[1]) if len(sys.argv) > 1 else (1 << 30)
-buf = sw.alloc(max_bytes + 4096)
+buf = sw.alloc(max_bytes + 4096, multicast=True)        # NVLS where the box has it: all-reduce / reduce-scatter sum in the switch
+p2p = sw.alloc(max_bytes + 4096)                        # plain IPC block: the peer-pointer kernels, for comparison
 
 
 def timeit(fn, iters, warmup=3):
@@ -42,7 +43,11 @@ while size <= max_bytes:
     full = torch.empty(n, dtype=torch.bfloat16, device=dev)
     iters = 50 if nbytes <= (1 << 20) else (10 if nbytes <= (1 << 26) else 4)
     r = {"bytes": nbytes, "world": world}
+    r["nvls"] = bool(getattr(buf, "mc_ptr", None))
     r["ar_native_us"] = timeit(lambda: comm.all_reduce(x), iters) * 1e3
+    xp = p2p.tensor(0, (n,), torch.bfloat16)
+    xp.normal_()
+    r["ar_p2p_us"] = timeit(lambda: comm.all_reduce(xp), iters) * 1e3
     r["ar_nccl_us"] = timeit(lambda: dist.all_reduce(y), iters) * 1e3
     xs = x[rank * (n // world):(rank + 1) * (n // world)]
     r["ag_native_us"] = timeit(lambda: comm.all_gather_into(full, xs), iters) * 1e3

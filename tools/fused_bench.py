@@ -74,6 +74,11 @@ def case_mp(T, D, Fs, name):
     res = {"case": name, "world": world, "M": T, "N": D, "K": Fs}
     res["local_gemm_ms"] = timeit(lambda: nv.gemm(a, 0, w, 0, y2, T, D, Fs))
     res["fused_gemm_allreduce_ms"] = timeit(lambda: ch.gemm(a, 0, w, 0, T, D, Fs, tab, D, 0, 0, 0, True))
+    if sw.multicast_supported():           # the same call with the partial tiles summed inside the NVSwitch
+        ym = sw.alloc(T * D * 2 + 4096, multicast=True)
+        _, offm = ym.carve((T, D), torch.bfloat16)
+        chn = FusedChannel(sw, _owned_cap([(T, D)], world, 0), _tiles(T, D), nvls=True)
+        res["fused_gemm_allreduce_nvls_ms"] = timeit(lambda: chn.gemm(a, 0, w, 0, T, D, Fs, ym.peers_at(offm), D, 0, 0, 0, True, out_mc=ym.mc_at(offm)))
 
     def unfused():
         nv.gemm(a, 0, w, 0, y2, T, D, Fs)
@@ -83,6 +88,10 @@ def case_mp(T, D, Fs, name):
     res["compute_floor_ms"] = 2.0 * T * D * Fs / (PEAK_TF * 1e12) * 1e3
     res["link_floor_allreduce_ms"] = 2.0 * (world - 1) / world * T * D * 2 / (LINK_GBS * 1e9) * 1e3
     res["roofline_frac_fused"] = max(res["compute_floor_ms"], res["link_floor_allreduce_ms"]) / res["fused_gemm_allreduce_ms"]
+    if "fused_gemm_allreduce_nvls_ms" in res:
+        # in-switch reduction: ~ (world-1)/world * S out (the pulls) + S/world (the multicast store) per GPU and direction
+        res["link_floor_nvls_ms"] = T * D * 2 / (LINK_GBS * 1e9) * 1e3
+        res["roofline_frac_fused_nvls"] = max(res["compute_floor_ms"], res["link_floor_nvls_ms"]) / res["fused_gemm_allreduce_nvls_ms"]
     return res
 
 

@@ -50,6 +50,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--mp_mode', default='ar', choices=['ar', 'sp', 'spf'])
     p.add_argument('--fsdp_gather', default='dma', choices=['dma', 'fused'], help='fused FSDP: copy-engine prefetch, or all-gather inside the consuming GEMMs')
     p.add_argument('--mp_input', default='full', choices=['full', 'sharded'])
+    p.add_argument('--nvls', default='auto', choices=['auto', 'off'], help='fused MP all-reduce: sum inside the NVSwitch (multimem) where available')
     p.add_argument('--master_port', type=int, default=29500)
     p.add_argument('--save_path', default=None)
     p.add_argument('--load_path', default=None)
