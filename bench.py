@@ -136,9 +136,12 @@ def also_in_child(args, impl, method, idx, recompute=False):
     its child at the same point; rank 0 returns the child's JSON record."""
     import subprocess
     rank, world, _ = rank_world()
-    env = dict(os.environ)
+    # torchrun tells its workers to use the AGENT's rendezvous store (TORCHELASTIC_USE_AGENT_STORE): a child on another
+    # port would wait for a store nobody serves.  Without those variables rank 0's child hosts its own store.
+    env = {k: v for k, v in os.environ.items() if not k.startswith("TORCHELASTIC_")}
     if world > 1:
         env["MASTER_PORT"] = str(int(os.environ.get("MASTER_PORT", "29500")) + 101 + idx)
+    env["B200_INIT_TIMEOUT_S"] = "180"
     cmd = [sys.executable, os.path.abspath(__file__), "--impl", impl, "--method", method, "--also", "none", "--gpus", str(args.gpus),
            "--steps", str(args.steps), "--warmup", str(args.warmup), "--batch_size", str(args.batch_size), "--seq_len", str(args.seq_len),
            "--comm", args.comm, "--ops", args.ops, "--mp_mode", args.mp_mode, "--fsdp_gather", args.fsdp_gather,
@@ -148,19 +151,35 @@ def also_in_child(args, impl, method, idx, recompute=False):
     if args.no_e2e:
         cmd.append("--no-e2e")
     try:
-        p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=1500)
+        p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
         out, err, rc = p.stdout, p.stderr, p.returncode
     except subprocess.TimeoutExpired as e:
         out, err, rc = (e.stdout or ""), "timeout", -1
-    if rank != 0:
-        return None
-    for line in reversed(out.splitlines()):
-        if line.startswith("{"):
-            try:
-                return json.loads(line)
-            except json.JSONDecodeError:
-                pass
-    return {"error": f"child rc={rc}", "stderr_tail": err[-600:]}
+    if isinstance(out, bytes):
+        out = out.decode(errors="replace")
+    rec = None
+    if rank == 0:
+        for line in reversed(out.splitlines()):
+            if line.startswith("{"):
+                try:
+                    rec = json.loads(line)
+                    break
+                except json.JSONDecodeError:
+                    pass
+        if rec is not None and "value" not in rec:
+            rec = None
+    # every rank must agree on whether the child run counts (a failed child falls back to an in-process measurement)
+    ok = rc == 0 and (rank != 0 or rec is not None)
+    if world > 1:
+        import torch.distributed as dist
+        flag = torch.tensor([1 if ok else 0], device=torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0"))))
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = bool(flag.item())
+    if not ok:
+        if rank == 0:
+            print(f"bench: child run of {impl}/{method} failed (rc={rc}): {str(err)[-300:]} - measuring in-process instead", file=sys.stderr, flush=True)
+        return "fallback"
+    return rec
 
 
 def also_methods(args):
@@ -257,7 +276,9 @@ def run_ours(args):
                        "e2e": rec["e2e"], "clocks": rec["clocks"], "gpu_launches": rec["gpu_launches"], "config": rec["config"]}
             continue
         k = len(also)
-        also[m] = also_in_child(args, "ours", "ddp", k, True) if m == "ddp_recompute" else also_in_child(args, "ours", m, k, args.recompute)
+        rm, rr = ("ddp", True) if m == "ddp_recompute" else (m, args.recompute)
+        r = also_in_child(args, "ours", rm, k, rr)
+        also[m] = ours_one(args, rm, rr) if r == "fallback" else r
     if also:
         rec["also"] = also
     if rank == 0:
@@ -385,7 +406,8 @@ def run_reference(args):
             also[m] = {"same_run_as": "ddp", "value": rec["value"], "unit": rec["unit"], "ms_per_step": rec["ms_per_step"],
                        "e2e": rec["e2e"], "clocks": rec["clocks"], "gpu_launches": 0, "config": rec["config"]}
             continue
-        also[m] = also_in_child(args, "reference", m, len(also) + 10)
+        r = also_in_child(args, "reference", m, len(also) + 10)
+        also[m] = reference_one(args, ref, m) if r == "fallback" else r
     if also:
         rec["also"] = also
     if rank == 0:

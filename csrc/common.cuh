@@ -337,6 +337,24 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
 }
+// Stochastic rounding of an optimizer update to bf16 (b200_set_update_rounding): with no fp32 master copy, a
+// round-to-nearest update smaller than half a bf16 ulp of the weight vanishes (the reference's LR = 1e-5 on weights of
+// ~2e-2 moves them by ~1e-3 ulp per step); rounding up with probability (discarded bits / 2^16) keeps the EXPECTED update
+// exact.  The random bits are a hash of (seed, element-pair index): every replica rounds identically.
+__device__ __forceinline__ uint32_t hash32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ uint32_t bf16_bits_sr(float v, uint32_t rnd16) {
+    uint32_t b = __float_as_uint(v);
+    if ((b & 0x7f800000u) != 0x7f800000u) b += rnd16;          // finite: add 16 random bits below the kept mantissa, then truncate
+    return b >> 16;
+}
+// element index `idx` must be even (first element of the pair)
+__device__ __forceinline__ uint32_t pack_bf16x2_sr(float lo, float hi, uint32_t seed, unsigned long long idx) {
+    const uint32_t r = hash32(seed ^ hash32((uint32_t)(idx >> 1) * 0x9e3779b9u + (uint32_t)(idx >> 33)));
+    return bf16_bits_sr(lo, r & 0xffffu) | (bf16_bits_sr(hi, r >> 16) << 16);
+}
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
 
@@ -354,4 +372,5 @@ int encode_tmap_bf16_2d(CUtensorMap* map, const void* base, uint64_t inner, uint
 int num_sms();
 void* driver_entry(const char* name);   // cudaGetDriverEntryPoint wrapper; nullptr + last_error on failure
 unsigned int* device_error_slot();   // pinned host memory, device-mapped (UVA): pass to kernels
+unsigned int update_rounding_seed();  // 0 = round to nearest; else the stochastic-rounding seed for optimizer updates
 }  // namespace b200

@@ -39,7 +39,20 @@ __device__ __forceinline__ void load_grad8(const void* g, long long i8, bool f32
 }
 
 // ------------------------------------------------------------------ SGD
-__global__ void __launch_bounds__(EW_THREADS) sgd_kernel(__nv_bfloat16* p, const void* g, long long n, float lr, int grad_f32) {
+__device__ __forceinline__ uint4 pack8_rounded(const float (&f)[8], uint32_t seed, unsigned long long e0) {
+    if (seed == 0u) return pack8(f);
+    uint4 o;
+    o.x = pack_bf16x2_sr(f[0], f[1], seed, e0); o.y = pack_bf16x2_sr(f[2], f[3], seed, e0 + 2);
+    o.z = pack_bf16x2_sr(f[4], f[5], seed, e0 + 4); o.w = pack_bf16x2_sr(f[6], f[7], seed, e0 + 6);
+    return o;
+}
+__device__ __forceinline__ __nv_bfloat16 bf16_rounded(float f, uint32_t seed, unsigned long long e) {
+    if (seed == 0u) return __float2bfloat16_rn(f);
+    const uint32_t r = hash32(seed ^ hash32((uint32_t)(e >> 1) * 0x9e3779b9u + (uint32_t)(e >> 33)));
+    return __ushort_as_bfloat16((unsigned short)bf16_bits_sr(f, (e & 1ull) ? (r >> 16) : (r & 0xffffu)));
+}
+
+__global__ void __launch_bounds__(EW_THREADS) sgd_kernel(__nv_bfloat16* p, const void* g, long long n, float lr, int grad_f32, uint32_t sr_seed) {
     const long long n8 = n / 8;
     const long long stride = (long long)gridDim.x * blockDim.x;
     uint4* pv = reinterpret_cast<uint4*>(p);
@@ -49,12 +62,12 @@ __global__ void __launch_bounds__(EW_THREADS) sgd_kernel(__nv_bfloat16* p, const
         load_grad8(g, i, grad_f32 != 0, gr);
 #pragma unroll
         for (int j = 0; j < 8; ++j) w[j] -= lr * gr[j];
-        pv[i] = pack8(w);
+        pv[i] = pack8_rounded(w, sr_seed, (unsigned long long)i * 8ull);
     }
     // scalar tail
     for (long long i = n8 * 8 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         float gr = grad_f32 ? reinterpret_cast<const float*>(g)[i] : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(g)[i]);
-        p[i] = __float2bfloat16_rn(__bfloat162float(p[i]) - lr * gr);
+        p[i] = bf16_rounded(__bfloat162float(p[i]) - lr * gr, sr_seed, (unsigned long long)i);
     }
 }
 
@@ -67,7 +80,7 @@ __device__ __forceinline__ float adam_one(float w, float gr, float& m, float& v,
     return w - lr * ((m / bc1) / (sqrtf(v / bc2) + eps));
 }
 __global__ void __launch_bounds__(EW_THREADS) adam_kernel(__nv_bfloat16* p, const void* g, float* m, float* v, long long n, float lr,
-                                                          float b1, float b2, float eps, float bc1, float bc2, int grad_f32) {
+                                                          float b1, float b2, float eps, float bc1, float bc2, int grad_f32, uint32_t sr_seed) {
     const long long n8 = n / 8;
     const long long stride = (long long)gridDim.x * blockDim.x;
     uint4* pv = reinterpret_cast<uint4*>(p);
@@ -84,12 +97,12 @@ __global__ void __launch_bounds__(EW_THREADS) adam_kernel(__nv_bfloat16* p, cons
         for (int j = 0; j < 8; ++j) w[j] = adam_one(w[j], gr[j], mm[j], vs[j], lr, b1, b2, eps, bc1, bc2);
         mv[2 * i] = make_float4(mm[0], mm[1], mm[2], mm[3]); mv[2 * i + 1] = make_float4(mm[4], mm[5], mm[6], mm[7]);
         vv[2 * i] = make_float4(vs[0], vs[1], vs[2], vs[3]); vv[2 * i + 1] = make_float4(vs[4], vs[5], vs[6], vs[7]);
-        pv[i] = pack8(w);
+        pv[i] = pack8_rounded(w, sr_seed, (unsigned long long)i * 8ull);
     }
     for (long long i = n8 * 8 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {   // scalar tail
         const float gr = grad_f32 ? reinterpret_cast<const float*>(g)[i] : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(g)[i]);
         float mi = m[i], vi = v[i];
-        p[i] = __float2bfloat16_rn(adam_one(__bfloat162float(p[i]), gr, mi, vi, lr, b1, b2, eps, bc1, bc2));
+        p[i] = bf16_rounded(adam_one(__bfloat162float(p[i]), gr, mi, vi, lr, b1, b2, eps, bc1, bc2), sr_seed, (unsigned long long)i);
         m[i] = mi;
         v[i] = vi;
     }
@@ -345,7 +358,7 @@ extern "C" int b200_sgd_bf16(void* param, const void* grad, long long n, float l
     if (n <= 0) return 0;
     if (int rc = check_ptr16(param, "sgd param")) return rc;
     if (int rc = check_ptr16(grad, "sgd grad")) return rc;
-    sgd_kernel<<<ew_grid(n / 8 + 1), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(param), grad, n, lr, grad_f32);
+    sgd_kernel<<<ew_grid(n / 8 + 1), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(param), grad, n, lr, grad_f32, update_rounding_seed());
     return check_cuda(cudaGetLastError(), "sgd launch");
 }
 
@@ -358,7 +371,7 @@ extern "C" int b200_adam_bf16(void* param, const void* grad, float* m, float* v,
     if (int rc = check_ptr16(m, "adam m")) return rc;
     if (int rc = check_ptr16(v, "adam v")) return rc;
     const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
-    adam_kernel<<<ew_grid(n / 8 + 1), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(param), grad, m, v, n, lr, beta1, beta2, eps, bc1, bc2, grad_f32);
+    adam_kernel<<<ew_grid(n / 8 + 1), EW_THREADS, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(param), grad, m, v, n, lr, beta1, beta2, eps, bc1, bc2, grad_f32, update_rounding_seed());
     return check_cuda(cudaGetLastError(), "adam launch");
 }
 

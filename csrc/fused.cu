@@ -61,6 +61,7 @@ struct FusedParams {
     const __nv_bfloat16* part_mc;    // the same block through its multicast address (multimem.ld_reduce sums all ranks' copies)
     __nv_bfloat16* out_mc;           // the output through its multicast address (multimem.st stores into every replica)
     int part_cap;
+    uint32_t sr_seed;                // optimizer forms: 0 = round the new weight to nearest, else stochastic rounding (common.cuh)
 };
 
 // Adam variant (OPT = 1): the owner of a tile also owns its optimizer state - fp32 moments in a compact per-owned-tile
@@ -389,8 +390,14 @@ struct FusedEpiT {
                     acc[6] = bf16_lo(ww.w) - p.alpha * acc[6]; acc[7] = bf16_hi(ww.w) - p.alpha * acc[7];
                 }
                 uint4 o;
-                o.x = pack_bf16x2(acc[0], acc[1]); o.y = pack_bf16x2(acc[2], acc[3]);
-                o.z = pack_bf16x2(acc[4], acc[5]); o.w = pack_bf16x2(acc[6], acc[7]);
+                if ((OPT == 1 || p.op == FOP_SGD) && p.sr_seed != 0u) {
+                    const unsigned long long e0 = (unsigned long long)grow * (unsigned long long)p.ldo + (unsigned long long)col;
+                    o.x = pack_bf16x2_sr(acc[0], acc[1], p.sr_seed, e0); o.y = pack_bf16x2_sr(acc[2], acc[3], p.sr_seed, e0 + 2);
+                    o.z = pack_bf16x2_sr(acc[4], acc[5], p.sr_seed, e0 + 4); o.w = pack_bf16x2_sr(acc[6], acc[7], p.sr_seed, e0 + 6);
+                } else {
+                    o.x = pack_bf16x2(acc[0], acc[1]); o.y = pack_bf16x2(acc[2], acc[3]);
+                    o.z = pack_bf16x2(acc[4], acc[5]); o.w = pack_bf16x2(acc[6], acc[7]);
+                }
                 if (p.broadcast) {
                     for (int d = 0; d < p.world; ++d) {
                         const int q = (p.rank + d) % p.world;        // local first, then peers, staggered
@@ -528,6 +535,8 @@ static int fused_build(const FusedCall& c, FusedParams* out, int* grid_out) {
     p.part_mc = reinterpret_cast<const __nv_bfloat16*>(c.part_mc);
     p.out_mc = reinterpret_cast<__nv_bfloat16*>(c.out_mc);
     p.part_cap = c.ready_cap;
+    // weight updates only (alpha > 0); the in-place ADD form of the activations (alpha = -1) always rounds to nearest
+    p.sr_seed = (c.adam != nullptr || (c.op == FOP_SGD && c.alpha > 0.0f)) ? update_rounding_seed() : 0u;
     if (nvls && tm * tn > c.ready_cap) { set_last_error("gemm_allreduce_nvls: partial-tile capacity %d < %d tiles", c.ready_cap, tm * tn); return B200_ERR_ARG; }
     for (int i = 0; i < c.world; ++i) {
         p.inbox[i] = nvls ? nullptr : c.inbox_peers[i];

@@ -79,7 +79,7 @@ extern "C" int b200_gemm_bf16(const void* A, long long lda, int a_major, const v
     if (epilogue == EPI_RELU_BWD_MASK && (aux == nullptr || (reinterpret_cast<uintptr_t>(aux) & 15) || (ldaux % 16) || ldaux * 8 < ((N + 127) / 128) * 128)) {
         set_last_error("gemm: RELU_BWD_MASK needs aux = uint8 mask[M, ldaux] with ldaux %% 16 == 0 and ldaux >= ceil(N/128)*16 bytes"); return B200_ERR_ARG;
     }
-    LocalEpiParams ep{C, ldc, reinterpret_cast<const __nv_bfloat16*>(aux), ldaux, reinterpret_cast<__nv_bfloat16*>(C2), ldc2, bias, alpha};
+    LocalEpiParams ep{C, ldc, reinterpret_cast<const __nv_bfloat16*>(aux), ldaux, reinterpret_cast<__nv_bfloat16*>(C2), ldc2, bias, alpha, epilogue == EPI_SGD ? update_rounding_seed() : 0u};
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (epilogue) {
         case EPI_STORE:     return launch_gemm<LocalEpi<EPI_STORE>>(o, ep, max_ctas, st);
@@ -88,7 +88,8 @@ extern "C" int b200_gemm_bf16(const void* A, long long lda, int a_major, const v
         case EPI_RELU_BWD:  return launch_gemm<LocalEpi<EPI_RELU_BWD>>(o, ep, max_ctas, st);
         case EPI_GELU_BWD:  return launch_gemm<LocalEpi<EPI_GELU_BWD>>(o, ep, max_ctas, st);
         case EPI_ADD:       return launch_gemm<LocalEpi<EPI_ADD>>(o, ep, max_ctas, st);
-        case EPI_SGD:       return launch_gemm<LocalEpi<EPI_SGD>>(o, ep, max_ctas, st);
+        case EPI_SGD:       return ep.sr_seed != 0u ? launch_gemm<LocalEpi<EPI_SGD_SR>>(o, ep, max_ctas, st)
+                                                    : launch_gemm<LocalEpi<EPI_SGD>>(o, ep, max_ctas, st);
         case EPI_STORE_F32: return launch_gemm<LocalEpi<EPI_STORE_F32>>(o, ep, max_ctas, st);
         case EPI_RELU_MASK: return launch_gemm<LocalEpi<EPI_RELU_MASK>>(o, ep, max_ctas, st);
         case EPI_RELU_BWD_MASK: return launch_gemm<LocalEpi<EPI_RELU_BWD_MASK>>(o, ep, max_ctas, st);

@@ -539,7 +539,8 @@ enum EpiKind : int {
     EPI_STORE_F32 = 7,  // C(fp32) = alpha * acc
     EPI_RELU_MASK = 8,      // RELU, plus a packed sign mask (1 bit per element, C2 as uint8 [M, ldc2 bytes]) for the backward
     EPI_RELU_BWD_MASK = 9,  // C = acc where the mask bit is set, else 0 (aux = the uint8 mask, ldaux in bytes)
-    EPI_COUNT = 10,
+    EPI_SGD_SR = 10,        // EPI_SGD with stochastic rounding of the new weight (internal: chosen by b200_set_update_rounding)
+    EPI_COUNT = 11,
 };
 
 struct LocalEpiParams {
@@ -551,6 +552,7 @@ struct LocalEpiParams {
     long long ldc2;
     const float* bias;
     float alpha;
+    uint32_t sr_seed;      // EPI_SGD: 0 = round the new weight to nearest, else stochastic rounding with this seed
 };
 
 __device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
@@ -618,7 +620,8 @@ struct LocalEpi {
     struct ProducerState {};
     static __device__ __forceinline__ int kblock(const Params&, const GemmCore&, int kb, int, ProducerState&) { return kb; }
     // a second bf16 [M,N] operand is read by these epilogues: aux, or (SGD) the weight tile itself
-    static constexpr bool READS = (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD || KIND == EPI_SGD);
+    static constexpr bool IS_SGD = (KIND == EPI_SGD || KIND == EPI_SGD_SR);
+    static constexpr bool READS = (KIND == EPI_RELU_BWD || KIND == EPI_GELU_BWD || KIND == EPI_ADD || IS_SGD);
     struct State {};
     static __device__ __forceinline__ void init(const Params&, const GemmCore&, const EpiCtx&, State&) {}
     static __device__ __forceinline__ void after_tile(const Params&, const GemmCore&, const EpiCtx&, State&) {}
@@ -630,8 +633,8 @@ struct LocalEpi {
         const int row0 = ctx.m0 + ctx.q * 32;                        // first of this warp's 32 rows
         const int colbase = ctx.n0 + ctx.half * (BN / 2);
         uint4* stage = reinterpret_cast<uint4*>(ctx.stage);
-        const __nv_bfloat16* rd = KIND == EPI_SGD ? reinterpret_cast<const __nv_bfloat16*>(p.C) : p.aux;
-        const long long rd_ld = KIND == EPI_SGD ? p.ldc : p.ldaux;
+        const __nv_bfloat16* rd = IS_SGD ? reinterpret_cast<const __nv_bfloat16*>(p.C) : p.aux;
+        const long long rd_ld = IS_SGD ? p.ldc : p.ldaux;
 
         if constexpr (KIND == EPI_STORE_F32) {                       // fp32 rows are 128 B per 32 columns already
             const int row = row0 + lane;
@@ -664,14 +667,14 @@ struct LocalEpi {
             }
         }
         uint4 rd_next[8];
-        if constexpr (READS) coalesced_load_rows<KIND != EPI_SGD>(rd_next, lane, rd, rd_ld, row0, colbase, g.M, g.N);
+        if constexpr (READS) coalesced_load_rows<!IS_SGD>(rd_next, lane, rd, rd_ld, row0, colbase, g.M, g.N);
 #pragma unroll 1
         for (int cp = 0; cp < 2; ++cp) {                             // 64 columns = one 128-byte line per row
             const int col0 = colbase + cp * 64;
             uint4 rdrow[8];
             if constexpr (READS) {
                 stage_to_row_owner(stage, lane, rd_next, rdrow);
-                if (cp == 0) coalesced_load_rows<KIND != EPI_SGD>(rd_next, lane, rd, rd_ld, row0, col0 + 64, g.M, g.N);   // prefetch the next 64 columns
+                if (cp == 0) coalesced_load_rows<!IS_SGD>(rd_next, lane, rd, rd_ld, row0, col0 + 64, g.M, g.N);   // prefetch the next 64 columns
             }
             uint32_t a0[32], a1[32];
             tmem_ld_32x32(taddr + cp * 64, a0);
@@ -728,8 +731,14 @@ struct LocalEpi {
                         }
                     }
                 }
-                outv[pc].x = pack_bf16x2(f[0], f[1]); outv[pc].y = pack_bf16x2(f[2], f[3]);
-                outv[pc].z = pack_bf16x2(f[4], f[5]); outv[pc].w = pack_bf16x2(f[6], f[7]);
+                if constexpr (KIND == EPI_SGD_SR) {
+                    const unsigned long long e0 = (unsigned long long)(row0 + lane) * (unsigned long long)p.ldc + (unsigned long long)(col0 + pc * 8);
+                    outv[pc].x = pack_bf16x2_sr(f[0], f[1], p.sr_seed, e0); outv[pc].y = pack_bf16x2_sr(f[2], f[3], p.sr_seed, e0 + 2);
+                    outv[pc].z = pack_bf16x2_sr(f[4], f[5], p.sr_seed, e0 + 4); outv[pc].w = pack_bf16x2_sr(f[6], f[7], p.sr_seed, e0 + 6);
+                } else {
+                    outv[pc].x = pack_bf16x2(f[0], f[1]); outv[pc].y = pack_bf16x2(f[2], f[3]);
+                    outv[pc].z = pack_bf16x2(f[4], f[5]); outv[pc].w = pack_bf16x2(f[6], f[7]);
+                }
             }
             if constexpr (KIND == EPI_GELU)
                 stage_store_rows(stage, lane, prev, p.C2, p.ldc2, row0, col0, g.M, g.N);

@@ -89,9 +89,20 @@ unsigned int* device_error_slot() {
     return g_err_slot;
 }
 
+static unsigned int g_update_rounding_seed = 0;
+unsigned int update_rounding_seed() { return g_update_rounding_seed; }
+
 }  // namespace b200
 
 using namespace b200;
+
+// Rounding of every optimizer update launched AFTER this call (process-wide): 0 = round to nearest (default), anything
+// else = stochastic rounding of the new bf16 weight with that seed.  Change the seed every step; use the same seed on
+// every rank (replicas then round identically).
+extern "C" int b200_set_update_rounding(unsigned int seed) {
+    g_update_rounding_seed = seed;
+    return 0;
+}
 
 extern "C" const char* b200_last_error(void) { return g_last_error; }
 extern "C" int b200_version(void) { return 100; }

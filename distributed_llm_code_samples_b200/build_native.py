@@ -1,7 +1,8 @@
 """Build the in-tree native library ``csrc/*.cu -> distributed_llm_code_samples_b200/_native/libb200ffn.so``.
 
 nvcc cross-compiles sm_100a without a GPU, so this runs on the CPU dev box; the resulting ``.so`` is
-git-ignored but travels with ``gpurun`` snapshots.  Objects are rebuilt only when a source or header is newer.
+git-ignored but travels with ``gpurun`` snapshots.  Everything is rebuilt whenever the SHA-256 of the sources,
+headers and flags differs from the one recorded with the objects (``_native/fingerprint.txt``).
 
     python -m distributed_llm_code_samples_b200.build_native [--force] [--verbose]
 """
@@ -38,9 +39,18 @@ def find_nvcc() -> str:
     return nvcc
 
 
-def _newest_header_mtime() -> float:
-    hs = list(CSRC.glob("*.cuh")) + list(CSRC.glob("*.h")) + list(INCLUDE.glob("*.h"))
-    return max((h.stat().st_mtime for h in hs), default=0.0)
+def source_fingerprint(defines: tuple = ()) -> str:
+    """SHA-256 over every source / header the library is built from plus the compiler flags.  The build is up to date
+    iff the fingerprint recorded next to the objects matches - modification times say nothing about objects that arrived
+    with a snapshot of the tree (``build()`` "reused" stale objects)."""
+    import hashlib
+    h = hashlib.sha256()
+    files = sorted(CSRC.glob("*.cu")) + sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.h")) + sorted(INCLUDE.glob("*.h"))
+    for f in files:
+        h.update(f.name.encode())
+        h.update(f.read_bytes())
+    h.update(" ".join(NVCC_FLAGS[:-4] + list(defines)).encode())        # flags without the absolute -I paths
+    return h.hexdigest()
 
 
 def _compile_one(nvcc: str, src: Path, obj: Path, verbose: bool, defines: tuple = ()) -> str:
@@ -62,14 +72,15 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     srcs = sorted(CSRC.glob("*.cu"))
     if not srcs:
         raise RuntimeError(f"no CUDA sources under {CSRC}")
-    hdr_m = _newest_header_mtime()
+    stamp = OUT_DIR / "fingerprint.txt"
+    fp = source_fingerprint()
+    fresh = stamp.exists() and stamp.read_text().strip() == fp and LIB_PATH.exists()
     jobs = []
     objs = []
     for src in srcs:
         obj = OUT_DIR / (src.stem + ".o")
         objs.append(obj)
-        stale = force or not obj.exists() or obj.stat().st_mtime < max(src.stat().st_mtime, hdr_m)
-        if stale:
+        if force or not fresh or not obj.exists():      # any source, header or flag changed: rebuild everything (seconds)
             jobs.append((src, obj))
     if jobs:
         with cf.ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 4)) as ex:
@@ -81,7 +92,12 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         p = subprocess.run(cmd, capture_output=True, text=True)
         if p.returncode != 0:
             raise RuntimeError(f"link failed:\n{p.stdout}{p.stderr}")
+        stamp.write_text(fp + "\n")
+    build.last_compiled = len(jobs)
     return LIB_PATH
+
+
+build.last_compiled = 0
 
 
 def build_variant(tag: str, defines: tuple) -> Path:

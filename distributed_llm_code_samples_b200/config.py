@@ -56,6 +56,8 @@ class TrainConfig:
                                            # fused = inside the consuming GEMMs, forward and backward (parallel/fused_fsdp_t.py)
     mp_input: str = "full"                 # Engine.train under MP all-reduce form: full = every rank stages the whole batch (:294, :324);
                                            # sharded = 1/world over PCIe + NVLink all-gather (ShardedPrefetcher)
+    stochastic_rounding: bool = False      # bf16 weights have no fp32 master copy: round optimizer updates stochastically so that
+                                           # updates far below a bf16 ulp (the reference's LR = 1e-5, :29) still train in expectation
     nvls: str = "auto"                     # fused MP all-reduce: auto = sum inside the NVSwitch where the box has NVLS; off = peer pushes
     master_port: int = 29500               # train_ffns.py:124
     save_path: Optional[str] = None

@@ -127,6 +127,7 @@ def _optional_declare(lib) -> None:
         "b200_gather_gemm_bf16": ([pp, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp], i),
         "b200_debug_gather_chunk": ([i, i, i, i, ll, C.POINTER(ll)], i),
         "b200_fused_config": ([i, i], i),
+        "b200_set_update_rounding": ([u], i),
         "b200_fused_partial_bytes": ([i], ll),
         "b200_nvls_collective": ([i, i, vp, vp, ll, pp, i, i, u, i, vp], i),
         "b200_gemm_allreduce_nvls_bf16": ([vp, ll, i, vp, ll, i, i, i, i, pp, ll, i, vp, vp, vp, pp, i, i, i, i, u, i, i, i, f, i, vp], i),
@@ -335,6 +336,11 @@ def sumsq_static(x: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
     _check(load().b200_sumsq_bf16_static(out.data_ptr(), x.data_ptr(), x.numel(), _stream()), "b200_sumsq_bf16_static")
     launch_count += 1
     return out
+
+
+def set_update_rounding(seed: int) -> None:
+    """0 = round optimizer updates to nearest; else stochastic rounding with this seed (see include/b200ffn.h)."""
+    load().b200_set_update_rounding(int(seed) & 0xFFFFFFFF)
 
 
 def fill_zero_(buf: torch.Tensor) -> None:

@@ -121,11 +121,14 @@ def _write_back(method: str, trainer, comm, out_params: Sequence[Params]) -> Non
 
 def _rank_main(rank: int, world: int, device: torch.device, method: str, cfg_dict: dict,
                layers_params: Sequence[Params], seeds: torch.Tensor, tokens: int, model_size: int,
-               out_params: Sequence[Params], stats: torch.Tensor) -> None:
+               out_params: Sequence[Params], stats: torch.Tensor, opt_io: Optional[dict] = None) -> None:
     cfg = TrainConfig(**cfg_dict)
     ops = get_ops(cfg.impl, device)
     comm = make_comm() if world > 1 else LocalComm()
     trainer = build_trainer(method, ops, comm, cfg, layers_params, device)
+    if opt_io is not None and opt_io.get("t_in", 0) > 0:             # resume: Adam moments from the checkpoint's full layout
+        from .opt_state import import_state
+        import_state(method if world > 1 else "single", trainer, comm, opt_io["m_in"], opt_io["v_in"], opt_io["t_in"])
     my_seeds = split_seeds(seeds, world)[rank] if method in ("ddp", "fsdp") else seeds
     if cfg.data == "device" and device.type == "cuda":
         batches = device_mock_data(my_seeds, tokens, model_size, cfg.torch_dtype, device)
@@ -169,11 +172,16 @@ def _rank_main(rank: int, world: int, device: torch.device, method: str, cfg_dic
         # model FLOPs: 6 GEMMs of 2*T*D*F per block-step (the reference executes a 7th, recomputing h, train_ffns.py:63)
         stats[2] = 12.0 * global_tokens * cfg.model_size * cfg.ffn_dim * cfg.layers * steps / (ms * 1e-3) / 1e12 if ms > 0 else 0.0
         stats[3] = torch.cuda.max_memory_allocated(device) / 2 ** 30 if device.type == "cuda" else 0.0
-    _write_back(method, trainer, comm, out_params)
+    if opt_io is not None:
+        from .opt_state import export_state
+        t_done = export_state(method if world > 1 else "single", trainer, comm, opt_io["m_out"], opt_io["v_out"])
+        if rank == 0:
+            stats[4] = t_done
+    _write_back(method if world > 1 else "single", trainer, comm, out_params)
 
 
 def _run(method: str, layers_params: Sequence[Params], seeds: torch.Tensor, tokens: int, model_size: int,
-         cfg: Optional[TrainConfig]) -> List[Params]:
+         cfg: Optional[TrainConfig], opt_state: Optional[dict] = None) -> List[Params]:
     cfg = copy.deepcopy(cfg) if cfg is not None else TrainConfig(model_size=model_size)
     cfg.model_size = model_size
     cfg.batch_size, cfg.seq_len = tokens, 1          # the drivers take the token count directly (train_ffns.py:379)
@@ -186,8 +194,16 @@ def _run(method: str, layers_params: Sequence[Params], seeds: torch.Tensor, toke
         raise AssertionError(f"len(seeds)={len(seeds)} must be divisible by the world size {world}")   # :175, :263
     shared_in = [[p.detach().clone().share_memory_() for p in lp] for lp in layers_params]
     out = [[torch.empty_like(p).share_memory_() for p in lp] for lp in layers_params]
-    stats = torch.zeros(4, dtype=torch.float64).share_memory_()
-    args = (method, cfg.to_dict(), shared_in, seeds, tokens, model_size, out, stats)
+    stats = torch.zeros(5, dtype=torch.float64).share_memory_()
+    opt_io = None
+    if cfg.optimizer == "adam":          # optimizer state travels in the parameters' full layout (parallel/opt_state.py)
+        from .opt_state import empty_like_params
+        opt_io = {"m_out": empty_like_params(layers_params), "v_out": empty_like_params(layers_params), "t_in": 0}
+        if opt_state and opt_state.get("kind") == "adam" and opt_state.get("t", 0) > 0:
+            opt_io["m_in"] = [[t.detach().float().clone().share_memory_() for t in l] for l in opt_state["m"]]
+            opt_io["v_in"] = [[t.detach().float().clone().share_memory_() for t in l] for l in opt_state["v"]]
+            opt_io["t_in"] = int(opt_state["t"])
+    args = (method, cfg.to_dict(), shared_in, seeds, tokens, model_size, out, stats, opt_io)
     if world == 1:
         dev = torch.device("cuda", 0) if device == "cuda" else torch.device("cpu")
         _rank_main(0, 1, dev, *args)
@@ -195,10 +211,20 @@ def _run(method: str, layers_params: Sequence[Params], seeds: torch.Tensor, toke
         launch(world, _rank_main, args, backend=backend, device=device, port=cfg.master_port if cfg.master_port != 29500 else 0)
     _run.last_stats = {"ms": float(stats[0]), "tokens_per_s": float(stats[1]), "model_tflops": float(stats[2]),
                        "max_mem_gib": float(stats[3]), "world": world}
+    _run.last_opt = {"kind": cfg.optimizer, "t": int(stats[4])}
+    if opt_io is not None:
+        _run.last_opt.update(m=[list(l) for l in opt_io["m_out"]], v=[list(l) for l in opt_io["v_out"]])
     return [list(lp) for lp in out]
 
 
 _run.last_stats = {}
+_run.last_opt = {}
+
+
+def last_optimizer_state() -> dict:
+    """Optimizer state of the most recent driver call in the checkpoint's full layout: ``{"kind", "t"}`` plus, for Adam,
+    ``m`` / ``v`` shaped like the parameters.  Pass it back as ``opt_state=`` (any strategy) to resume."""
+    return dict(_run.last_opt)
 
 
 def last_stats() -> dict:
@@ -206,17 +232,17 @@ def last_stats() -> dict:
     return dict(_run.last_stats)
 
 
-def train_1gpu(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None):
-    return _run("single", layers_params, seeds, batch_size, model_size, cfg)
+def train_1gpu(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None, opt_state: Optional[dict] = None):
+    return _run("single", layers_params, seeds, batch_size, model_size, cfg, opt_state)
 
 
-def train_ddp(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None):
-    return _run("ddp", layers_params, seeds, batch_size, model_size, cfg)
+def train_ddp(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None, opt_state: Optional[dict] = None):
+    return _run("ddp", layers_params, seeds, batch_size, model_size, cfg, opt_state)
 
 
-def train_fsdp(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None):
-    return _run("fsdp", layers_params, seeds, batch_size, model_size, cfg)
+def train_fsdp(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None, opt_state: Optional[dict] = None):
+    return _run("fsdp", layers_params, seeds, batch_size, model_size, cfg, opt_state)
 
 
-def train_tp(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None):
-    return _run("mp", layers_params, seeds, batch_size, model_size, cfg)
+def train_tp(layers_params, seeds, batch_size, model_size, cfg: Optional[TrainConfig] = None, opt_state: Optional[dict] = None):
+    return _run("mp", layers_params, seeds, batch_size, model_size, cfg, opt_state)

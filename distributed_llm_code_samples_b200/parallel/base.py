@@ -13,12 +13,21 @@ def block_opts(cfg: TrainConfig) -> BlockOpts:
     return BlockOpts(activation=cfg.activation, residual=cfg.residual, recompute=cfg.recompute)
 
 
+def set_update_rounding(cfg: TrainConfig, ops, step: int) -> None:
+    """Select the rounding of this step's bf16 weight updates on the native kernels (``b200_set_update_rounding``): a fresh
+    seed per step when ``cfg.stochastic_rounding``, round-to-nearest otherwise.  Same seed on every rank."""
+    if getattr(ops, "name", "") != "native":
+        return
+    from ..ops import native as nv
+    nv.set_update_rounding(((0x9E3779B1 * (step + 1)) & 0xFFFFFFFF) | 1 if cfg.stochastic_rounding else 0)
+
+
 class Optimizer:
     """SGD (the reference's ``param.add_(-LR*grad)``, ``train_ffns.py:172``) or Adam with fp32 moments.
     ``grad_scale`` multiplies the summed gradient (reference: 1.0 = plain SUM over ranks, ``:165``)."""
 
     def __init__(self, ops, cfg: TrainConfig):
-        self.ops, self.kind = ops, cfg.optimizer
+        self.ops, self.kind, self.cfg = ops, cfg.optimizer, cfg
         self.lr = cfg.lr * cfg.grad_scale
         self.beta1, self.beta2, self.eps = 0.9, 0.999, 1e-8
         self.state: Dict[int, Tuple[torch.Tensor, torch.Tensor]] = {}
@@ -26,6 +35,7 @@ class Optimizer:
 
     def begin_step(self) -> None:
         self.t += 1
+        set_update_rounding(self.cfg, self.ops, self.t)
 
     def update(self, key: int, p: torch.Tensor, g: Optional[torch.Tensor]) -> None:
         if g is None:                      # already applied inside the GEMM that produced it

@@ -20,7 +20,7 @@ import torch
 from ..config import TrainConfig
 from ..models.ffn import Params
 from ..ops import native as nv
-from .base import Optimizer, block_opts
+from .base import Optimizer, block_opts, set_update_rounding
 from .symm import CollChannel, SymmBuffer, SymmWorld, _Handle, get_symm_world
 
 OWN_INTERLEAVED, OWN_ROW_SHARDED = 0, 1
@@ -140,6 +140,35 @@ class GatherChannel:
         return out
 
 
+def _owned_tiles(M: int, N: int, world: int, rank: int, owner_mode: int) -> List[Tuple[int, int]]:
+    """(m_blk, n_blk) of this rank's owned tiles in inbox-slot order - the Python mirror of ``owned_tile_coords`` in
+    csrc/fused.cu (checked against the C mirror ``b200_debug_fused_map`` in tests/test_native_maps_cpu.py)."""
+    tm, tn = (M + TILE_M - 1) // TILE_M, (N + TILE_N - 1) // TILE_N
+    if owner_mode == OWN_ROW_SHARDED:
+        mpo = tm // world
+        return [(rank * mpo + k // tn, k % tn) for k in range(mpo * tn)]
+    total = tm * tn
+    return [divmod(lin, tn) for lin in range(rank, total, world)]
+
+
+def _export_tiles(state: torch.Tensor, dst: torch.Tensor, M: int, N: int, world: int, rank: int, owner_mode: int, row0: int = 0) -> None:
+    """Compact per-owned-tile moments ``[slot][128][256]`` -> the owned tiles of a dense CPU tensor (rows offset by row0)."""
+    tiles = state.view(-1, TILE_M, TILE_N).cpu()
+    for k, (mb, nb) in enumerate(_owned_tiles(M, N, world, rank, owner_mode)):
+        r0, c0 = mb * TILE_M, nb * TILE_N
+        r1, c1 = min(r0 + TILE_M, M), min(c0 + TILE_N, N)
+        dst[r0 - row0:r1 - row0, c0:c1].copy_(tiles[k, :r1 - r0, :c1 - c0])
+
+
+def _import_tiles(state: torch.Tensor, src: torch.Tensor, M: int, N: int, world: int, rank: int, owner_mode: int, row0: int = 0) -> None:
+    tiles = torch.zeros(state.numel() // (TILE_M * TILE_N), TILE_M, TILE_N, dtype=torch.float32)
+    for k, (mb, nb) in enumerate(_owned_tiles(M, N, world, rank, owner_mode)):
+        r0, c0 = mb * TILE_M, nb * TILE_N
+        r1, c1 = min(r0 + TILE_M, M), min(c0 + TILE_N, N)
+        tiles[k, :r1 - r0, :c1 - c0].copy_(src[r0 - row0:r1 - row0, c0:c1])
+    state.copy_(tiles.reshape(-1).to(state.device))
+
+
 class _ReplicatedBiases:
     """Biases of a data-parallel stack under the fused trainers: replicated fp32 vectors (a few KiB per layer) in ONE
     contiguous tensor, their gradients (native column sums of ``dh`` / ``dy``) in one symmetric fp32 buffer, so a step
@@ -165,6 +194,23 @@ class _ReplicatedBiases:
         self.lr = cfg.lr * cfg.grad_scale
         if self.adam:
             self.m, self.v = torch.zeros_like(self.values), torch.zeros_like(self.values)
+
+    def export_state(self, m_out, v_out) -> None:
+        if self.adam and self.sw.rank == 0:
+            for l in range(self.L):
+                for j, (b, off) in enumerate(((self.b1[l], 0), (self.b2[l], self.b1[l].numel()))):
+                    o = self.b1[l].data_ptr() - self.values.data_ptr()
+                    lo = o // 4 + off
+                    m_out[l][2 + j].copy_(self.m[lo:lo + b.numel()].cpu())
+                    v_out[l][2 + j].copy_(self.v[lo:lo + b.numel()].cpu())
+
+    def import_state(self, m_in, v_in) -> None:
+        if self.adam:
+            for l in range(self.L):
+                for j, (b, off) in enumerate(((self.b1[l], 0), (self.b2[l], self.b1[l].numel()))):
+                    lo = (self.b1[l].data_ptr() - self.values.data_ptr()) // 4 + off
+                    self.m[lo:lo + b.numel()].copy_(m_in[l][2 + j].to(self.m.device))
+                    self.v[lo:lo + b.numel()].copy_(v_in[l][2 + j].to(self.v.device))
 
     def accumulate(self, l: int, dh: torch.Tensor, dy: torch.Tensor) -> None:
         """This rank's bias gradients of layer ``l``: db1 = dh.sum(0), db2 = dy.sum(0) (native column sums)."""
@@ -233,6 +279,7 @@ class FusedDDPTrainer:
         cfg, ops = self.cfg, self.ops
         D, F = cfg.model_size, cfg.ffn_dim
         self.t += 1
+        set_update_rounding(cfg, ops, self.t)
         y, acts = tlayers_ffn_fwd(ops, self.params, x, self.opts)
         d = dloss_dx
         T = x.shape[0]
@@ -261,6 +308,34 @@ class FusedDDPTrainer:
 
     def full_params(self) -> List[Params]:
         return self.params
+
+    # ---- optimizer state in the checkpoint's full layout (parallel/opt_state.py) -------------------------------
+    def export_opt_state(self, m_out, v_out) -> int:
+        """Every rank writes the moments of the tiles it OWNS (disjoint, interleaved) into the shared full tensors."""
+        if self.adam:
+            cfg = self.cfg
+            shapes = [(cfg.ffn_dim, cfg.model_size), (cfg.model_size, cfg.ffn_dim)]
+            for i in range(len(self.params)):
+                for k in range(2):
+                    m, v = self.state[i][k]
+                    _export_tiles(m, m_out[i][k], *shapes[k], self.sw.world, self.sw.rank, OWN_INTERLEAVED)
+                    _export_tiles(v, v_out[i][k], *shapes[k], self.sw.world, self.sw.rank, OWN_INTERLEAVED)
+            if self.biases:
+                self.biases.export_state(m_out, v_out)
+        return self.t
+
+    def import_opt_state(self, m_in, v_in, t: int) -> None:
+        self.t = int(t)
+        if self.adam:
+            cfg = self.cfg
+            shapes = [(cfg.ffn_dim, cfg.model_size), (cfg.model_size, cfg.ffn_dim)]
+            for i in range(len(self.params)):
+                for k in range(2):
+                    m, v = self.state[i][k]
+                    _import_tiles(m, m_in[i][k], *shapes[k], self.sw.world, self.sw.rank, OWN_INTERLEAVED)
+                    _import_tiles(v, v_in[i][k], *shapes[k], self.sw.world, self.sw.rank, OWN_INTERLEAVED)
+            if self.biases:
+                self.biases.import_state(m_in, v_in)
 
 
 # =================================================================================================== FSDP
@@ -351,6 +426,7 @@ class FusedFSDPTrainer:
         D, F = cfg.model_size, cfg.ffn_dim
         T = x.shape[0]
         self.t += 1
+        set_update_rounding(cfg, ops, self.t)
         acts = []
         y = x
         self._start_gather(0)
@@ -406,6 +482,33 @@ class FusedFSDPTrainer:
         return out
 
 
+    # ---- optimizer state in the checkpoint's full layout: row-sharded owners = this rank's dim-0 shard -----------
+    def _state_shapes(self):
+        return [(self.cfg.ffn_dim, self.cfg.model_size), (self.cfg.model_size, self.cfg.ffn_dim)]
+
+    def export_opt_state(self, m_out, v_out) -> int:
+        if self.adam:
+            for i in range(self.L):
+                for k, (M, N) in enumerate(self._state_shapes()):
+                    m, v = self.state[i][k]
+                    _export_tiles(m, m_out[i][k], M, N, self.world, self.rank, OWN_ROW_SHARDED)
+                    _export_tiles(v, v_out[i][k], M, N, self.world, self.rank, OWN_ROW_SHARDED)
+            if self.biases:
+                self.biases.export_state(m_out, v_out)
+        return self.t
+
+    def import_opt_state(self, m_in, v_in, t: int) -> None:
+        self.t = int(t)
+        if self.adam:
+            for i in range(self.L):
+                for k, (M, N) in enumerate(self._state_shapes()):
+                    m, v = self.state[i][k]
+                    _import_tiles(m, m_in[i][k], M, N, self.world, self.rank, OWN_ROW_SHARDED)
+                    _import_tiles(v, v_in[i][k], M, N, self.world, self.rank, OWN_ROW_SHARDED)
+            if self.biases:
+                self.biases.import_state(m_in, v_in)
+
+
 # =================================================================================================== MP
 class FusedMPTrainer:
     """Megatron MP with the collectives inside the row-parallel GEMMs.
@@ -443,6 +546,10 @@ class FusedMPTrainer:
         self.device = device
         self.T = 0
         self.chan: Optional[FusedChannel] = None
+
+    def opt_key(self, i: int, j: int, p: torch.Tensor):
+        """Key of parameter (layer i, index j) in ``self.opt.state`` (parallel/opt_state.py)."""
+        return p.data_ptr()
 
     def update_local(self, W: torch.Tensor, dy: torch.Tensor, x: torch.Tensor) -> None:
         """``W -= update(dy^T @ x)`` on this rank's shard; no communication."""

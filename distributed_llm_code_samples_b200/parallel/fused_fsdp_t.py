@@ -28,6 +28,7 @@ from typing import Optional
 import torch
 
 from ..ops import native as nv
+from .base import set_update_rounding
 from .fused import FOP_SGD, OWN_ROW_SHARDED, FusedFSDPTrainer, GatherChannel
 
 K_, MN_ = nv.MAJOR_K, nv.MAJOR_MN
@@ -133,4 +134,5 @@ class FusedFSDPGatherTrainer(FusedFSDPTrainer):
 
     def step(self, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         self.t += 1
+        set_update_rounding(self.cfg, self.ops, self.t)
         return fsdp_t_step(self, x, dloss_dx)

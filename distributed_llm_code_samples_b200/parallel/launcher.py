@@ -81,6 +81,19 @@ def _entry(rank: int, world: int, backend: str, port: int, device: str, fn: Call
 
 def launch(world: int, fn: Callable, args: Sequence[Any], backend: str = "auto", device: str = "auto",
            port: int = 0, join_timeout_s: int = 3600) -> None:
+    """``_launch_once`` with one retry when the rendezvous port picked by ``free_port`` was taken between the probe and
+    the bind (EADDRINUSE; seen once in ~100 launches on the GPU boxes)."""
+    try:
+        _launch_once(world, fn, args, backend, device, port, join_timeout_s)
+    except RuntimeError as e:
+        if port == 0 and "EADDRINUSE" in str(e):
+            _launch_once(world, fn, args, backend, device, 0, join_timeout_s)
+        else:
+            raise
+
+
+def _launch_once(world: int, fn: Callable, args: Sequence[Any], backend: str = "auto", device: str = "auto",
+                 port: int = 0, join_timeout_s: int = 3600) -> None:
     """Run ``fn(rank, world, device, *args)`` in ``world`` spawned processes and wait for them.
 
     Raises ``RuntimeError`` with the first failing rank's traceback if any rank exits non-zero."""
@@ -140,7 +153,9 @@ def under_torchrun() -> bool:
 
 
 def init_from_env(device: str = "auto", backend: str = "auto", timeout_s: int = 600) -> tuple[int, int, torch.device]:
-    """Initialise from torchrun's environment (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_*)."""
+    """Initialise from torchrun's environment (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_*).  ``B200_INIT_TIMEOUT_S``
+    overrides the rendezvous / collective timeout."""
+    timeout_s = int(os.environ.get("B200_INIT_TIMEOUT_S", timeout_s))
     device = pick_device(device)
     backend = pick_backend(backend, device)
     rank = int(os.environ.get("RANK", "0"))

@@ -28,6 +28,13 @@ int b200_device_error(unsigned int* out);
 int b200_clear_device_error(void);
 int b200_num_sms(void);
 
+/* Rounding of the new bf16 weight in EVERY optimizer update launched after this call (GEMM SGD epilogue, fused
+ * all-reduce / reduce-scatter + SGD / Adam, b200_sgd_bf16, b200_adam_bf16): 0 = round to nearest (default); any other
+ * value = stochastic rounding seeded with it (random bits = hash(seed, element index), so replicas agree).  Without an
+ * fp32 master copy an update below half a bf16 ulp of the weight rounds away - at the reference's LR = 1e-5
+ * (train_ffns.py:29) that is every update; stochastic rounding keeps its expectation.  Use a new seed each step. */
+int b200_set_update_rounding(unsigned int seed);
+
 /* ---- GEMM: D[M,N] = sum_k A(m,k) * B(n,k), bf16 in, fp32 accumulate in TMEM -------------------------------
  * a_major / b_major: 0 = K-major (row-major [MN,K]; ld = row pitch in elements)
  *                    1 = MN-major (row-major [K,MN])
@@ -107,7 +114,9 @@ int b200_sumsq_bf16(float* out, const void* x, long long n, void* scratch, long 
  *     current); make that first call before starting any stream capture.
  *   - no cudaMalloc / cudaFree / allocating library call is made, on the first call or later.
  *   - every call on a device uses the same array: the arrival counter is reset on the stream before each launch,
- *     but two calls whose kernels overlap on the GPU (different streams) corrupt each other - serialise them. */
+ *     but two calls whose kernels overlap on the GPU (different streams) corrupt each other - serialise them.
+ *   - the looked-up address is cached per device ordinal for the life of the process; cudaDeviceReset() on that device
+ *     invalidates it (the module is reloaded at a new address) - do not reset a device this entry point has used. */
 long long b200_sumsq_static_max_elems(void);
 int b200_sumsq_bf16_static(float* out, const void* x, long long n, void* stream);
 /* Writes `bytes` of zeros (L2 flush between timed iterations). */

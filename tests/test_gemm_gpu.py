@@ -271,3 +271,36 @@ def test_fp32_param_optimizers_and_bias_kernels(cuda_device):
     assert torch.equal(out, bias.to(torch.bfloat16).expand(T, N))
     nv.bias_rows_(out, None, res)
     assert torch.equal(out, res)
+
+
+def test_stochastic_rounding_keeps_sub_ulp_updates(cuda_device):
+    """bf16 weights have no fp32 master copy: with round-to-nearest an update of 1/16 ulp vanishes entirely (ADVICE r1);
+    with b200_set_update_rounding(seed) the new weight is rounded up with probability 1/16, so the MEAN update is exact.
+    Checked on the elementwise SGD kernel and on the SGD epilogue of the dW GEMM; replicas (same seed) agree bit for bit."""
+    n = 1 << 20
+    ulp = 2.0 ** -7                                         # bf16 ulp at 1.0
+    try:
+        for kind in ("kernel", "gemm"):
+            outs = []
+            for seed in (0, 12345, 12345, 999):
+                nv.set_update_rounding(seed)
+                if kind == "kernel":
+                    p = torch.ones(n, dtype=torch.bfloat16, device=cuda_device)
+                    g = torch.full((n,), ulp / 16, dtype=torch.float32, device=cuda_device)
+                    nv.sgd_(p, g, 1.0)
+                else:                                       # W[1024,1024] -= 1 * dy^T x with dy^T x == ulp/16 everywhere (K = 64)
+                    p = torch.ones(1024, 1024, dtype=torch.bfloat16, device=cuda_device)
+                    dy = torch.full((64, 1024), 2.0 ** -6, dtype=torch.bfloat16, device=cuda_device)
+                    x = torch.full((64, 1024), ulp / 16 / 64 * 2.0 ** 6, dtype=torch.bfloat16, device=cuda_device)
+                    nv.gemm(dy, 1, x, 1, p, 1024, 1024, 64, nv.EPI_SGD, alpha=1.0)
+                torch.cuda.synchronize()
+                outs.append(p.float().flatten().clone())
+            rn, sr_a, sr_b, sr_c = outs
+            assert bool((rn == 1.0).all()), "round-to-nearest drops a 1/16-ulp update (the limitation being addressed)"
+            frac = (sr_a < 1.0).float().mean().item()          # 1 - ulp/16 lies between 1 - ulp/2 (next bf16 below 1) and 1
+            assert abs(frac - 0.125) < 0.01, (kind, frac)       # below 1.0 the spacing is ulp/2: P(round down) = (ulp/16)/(ulp/2)
+            assert abs((1.0 - sr_a.mean().item()) - ulp / 16) < 0.1 * ulp / 16, "mean update must equal the exact update"
+            assert torch.equal(sr_a, sr_b), "same seed -> identical rounding (replicas stay in sync)"
+            assert not torch.equal(sr_a, sr_c), "a different seed rounds different elements"
+    finally:
+        nv.set_update_rounding(0)

@@ -220,6 +220,28 @@ def test_fused_north_star_block_matches_nccl(method, mp_mode, optimizer):
         assert _rel(a, b) < 0.25, (j, _rel(a, b))
 
 
+def test_fused_adam_state_resumes_across_strategies():
+    """The fused trainers keep Adam's moments in a compact per-owned-tile layout (1/world per rank); a checkpoint holds
+    them in the parameters' full layout.  One fused-DDP step, export, one fused-FSDP step resumed from it, must match two
+    uninterrupted steps of the unfused NCCL DDP trainer - and must NOT match a resume that drops the moments."""
+    from distributed_llm_code_samples_b200.models import ffn
+    from distributed_llm_code_samples_b200.parallel import api
+    g = torch.Generator().manual_seed(45)
+    lp = [[p.to(torch.bfloat16).float() if j < 2 else p.normal_(0, 0.05, generator=g) for j, p in enumerate(l)]
+          for l in ffn.init_stack(3, DM, 4 * DM, g, bias=True)]
+    seeds = torch.arange(2 * WORLD)
+    kw = dict(optimizer="adam", bias=True, lr=1e-3)
+    straight = api.train_ddp(lp, seeds, 512, DM, _cfg(comm="nccl", **kw))
+    half = api.train_ddp(lp, seeds[:WORLD], 512, DM, _cfg(comm="fused", **kw))
+    st = api.last_optimizer_state()
+    assert st["t"] == 1 and all(m.abs().sum() > 0 for l in st["m"] for m in l), "every tile owner must have exported its moments"
+    resumed = api.train_fsdp(half, seeds[WORLD:], 512, DM, _cfg(comm="fused", **kw), st)
+    cold = api.train_fsdp(half, seeds[WORLD:], 512, DM, _cfg(comm="fused", **kw))
+    upd = lambda res: [[p.float() - q for p, q in zip(a, b)] for a, b in zip(res, lp)]
+    assert _rel(upd(resumed), upd(straight)) < 0.2, _rel(upd(resumed), upd(straight))
+    assert _rel(upd(cold), upd(straight)) > 1.5 * _rel(upd(resumed), upd(straight))
+
+
 @pytest.mark.parametrize("method,extra", [("ddp", {"optimizer": "adam"}), ("fsdp", {"bias": True}), ("mp", {"residual": True})])
 def test_unfused_trainers_on_native_collectives_match_nccl(method, extra):
     """--comm native: the plain trainers (so Adam / bias / residual work) with every collective on the peer-memory

@@ -118,3 +118,54 @@ def test_failed_rank_fails_the_launch():
 def _boom(rank, world, dev):
     if rank == 1:
         raise ValueError("injected failure")
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("first,second", [("ddp", "fsdp"), ("fsdp", "mp"), ("mp", "ddp")])
+def test_adam_state_survives_a_cross_strategy_resume(first, second, tmp_path):
+    """Checkpoints carry the optimizer: one Adam step under `first`, save, resume under `second` for the rest
+    == the uninterrupted run.  The moments travel in the parameters' full layout (parallel/opt_state.py), so the resuming
+    strategy re-shards them like the weights.  Without the state the resumed run restarts bias correction and diverges."""
+    from distributed_llm_code_samples_b200.utils.checkpoint import load_checkpoint, save_checkpoint
+    lp, seeds = _init(bias=True)
+    fns = {"ddp": api.train_ddp, "fsdp": api.train_fsdp, "mp": api.train_tp}
+    per_step = lambda m: 1 if m == "mp" else 2                 # seeds consumed per optimizer step at world 2
+    cfg = _cfg(optimizer="adam", bias=True, activation="gelu", residual=True)
+    cfg.lr = 1e-2
+    # uninterrupted: the data of step 1 under `first`, then of step 2 under `second`, in one optimizer history
+    s1, s2 = seeds[:per_step(first)], seeds[2:2 + per_step(second)]
+    a = fns[first](lp, s1, T, D, cfg)
+    st = api.last_optimizer_state()
+    assert st["kind"] == "adam" and st["t"] == 1 and all(m.abs().sum() > 0 for l in st["m"] for m in l)
+    path = str(tmp_path / "ck.pt")
+    save_checkpoint(path, a, step=1, args=cfg.to_dict(), seeds=seeds, optimizer=st)
+    ck = load_checkpoint(path)
+    resumed = fns[second](ck["layers_params"], s2, T, D, cfg, ck["optimizer"])
+    assert api.last_optimizer_state()["t"] == 2
+    # reference: both steps under single-device Adam on the same global batches (sum of the per-seed gradients)
+    cold = fns[second](ck["layers_params"], s2, T, D, cfg)              # same weights, moments restarted: must differ
+    one = api.train_1gpu(lp, s1[:1], T, D, cfg) if per_step(first) == 1 else None
+    if one is not None and per_step(second) == 1:
+        straight = api.train_1gpu(one, s2, T, D, cfg, api.last_optimizer_state())
+        for la, lb in zip(straight, resumed):
+            for p, q in zip(la, lb):
+                assert torch.allclose(p, q, atol=5e-5), (p - q).abs().max()
+    diff = max((p - q).abs().max().item() for la, lb in zip(cold, resumed) for p, q in zip(la, lb))
+    assert diff > 1e-4, "resuming with the saved moments must differ from restarting them"
+    for l in resumed:
+        for p in l:
+            assert torch.isfinite(p).all()
+
+
+@pytest.mark.timeout(600)
+def test_adam_ddp_then_fsdp_equals_uninterrupted_ddp():
+    """Two Adam steps under DDP == one under DDP + one under FSDP resumed from the exported state (exact same math)."""
+    lp, seeds = _init(bias=True)
+    cfg = _cfg(optimizer="adam", bias=True)
+    cfg.lr = 1e-2
+    straight = api.train_ddp(lp, seeds, T, D, cfg)
+    half = api.train_ddp(lp, seeds[:2], T, D, cfg)
+    resumed = api.train_fsdp(half, seeds[2:], T, D, cfg, api.last_optimizer_state())
+    for la, lb in zip(straight, resumed):
+        for p, q in zip(la, lb):
+            assert torch.allclose(p, q, atol=2e-5), (p - q).abs().max()

@@ -20,6 +20,10 @@ fn = {
     "G1": lambda: nv.gemm(x, 0, w1, 0, h, T, F, D, nv.EPI_RELU),
     "G2": lambda: nv.gemm(a, 0, w2, 0, y, T, D, F),
     "G5": lambda: nv.gemm(dy, 0, w2, 1, h, T, F, D, nv.EPI_RELU_BWD, aux=a),
+    "G1m": None, "G5m": None,
+    "G7": lambda: nv.gemm(a, 0, w1, 1, y, T, D, F),                                  # NN: B operand MN-major
+    "G6": lambda: nv.gemm(a, 1, x, 1, w1, F, D, T, nv.EPI_SGD, alpha=1e-6),          # NT + SGD epilogue (K = tokens)
+    "fused_mp_1cta": None, "emu8_dw": None, "emu8_mp": None, "philox": None, "colsum": None,
     "G4": lambda: nv.gemm(dy, 1, a, 1, dw, D, F, T),
     "cublas_G1": lambda: torch.matmul(x, w1.T, out=h),
     "cublas_G2": lambda: torch.matmul(a, w2.T, out=y),
@@ -33,6 +37,51 @@ fn = {
     "coll_ar": None,
     "coll_ag": None,
 }[case]
+if case in ("G1m", "G5m"):
+    mask = torch.zeros(T, F // 8, dtype=torch.uint8, device=dev)
+    nv.gemm(x, 0, w1, 0, h, T, F, D, nv.EPI_RELU_MASK, out2=mask)
+    fn = (lambda: nv.gemm(x, 0, w1, 0, h, T, F, D, nv.EPI_RELU_MASK, out2=mask)) if case == "G1m" else \
+         (lambda: nv.gemm(dy, 0, w2, 1, h, T, F, D, nv.EPI_RELU_BWD_MASK, aux=mask))
+if case == "fused_mp_1cta":
+    # the double-buffered 1-CTA fused kernel MP uses at 8 GPUs (70B shard shape), in a world of one
+    from distributed_llm_code_samples_b200.parallel.symm import SymmWorld
+    from distributed_llm_code_samples_b200.parallel.fused import FusedChannel, _owned_cap, _tiles
+    nv.load().b200_fused_config(4, 1)
+    Tm, Dm, Fs = 16384, 8192, 3584
+    am = torch.randn(Tm, Fs, device=dev).to(torch.bfloat16)
+    wm = (torch.randn(Dm, Fs, device=dev) * 0.02).to(torch.bfloat16)
+    sw = SymmWorld(0, 1, dev)
+    chan = FusedChannel(sw, _owned_cap([(Tm, Dm)], 1, 0), _tiles(Tm, Dm))
+    yb = sw.alloc(Tm * Dm * 2 + 4096)
+    _, off = yb.carve((Tm, Dm), torch.bfloat16)
+    tab = yb.peers_at(off)
+    fn = lambda: chan.gemm(am, 0, wm, 0, Tm, Dm, Fs, tab, Dm, 0, 0, 0, True)
+if case in ("emu8_dw", "emu8_mp"):
+    # EIGHT emulated ranks in one cooperative launch (parallel/emu.py): the real 8-rank protocol - owner maps, inbox slots
+    # per source, flags, broadcast of reduced tiles - with local memory in place of NVLink; 18 CTAs per rank
+    from distributed_llm_code_samples_b200.parallel.emu import EmuFused
+    lib = nv.load()
+    W = 8
+    if case == "emu8_dw":
+        M_, N_, K_, am_, bm_ = 4096, 4096, 4096, 1, 1
+        A = [torch.randn(K_, M_, device=dev).to(torch.bfloat16) for _ in range(W)]
+        B = [torch.randn(K_, N_, device=dev).to(torch.bfloat16) for _ in range(W)]
+        op = 1
+    else:
+        M_, N_, K_, am_, bm_ = 4096, 4096, 3584, 0, 0
+        A = [torch.randn(M_, K_, device=dev).to(torch.bfloat16) for _ in range(W)]
+        B = [(torch.randn(N_, K_, device=dev) * 0.02).to(torch.bfloat16) for _ in range(W)]
+        op = 0
+        lib.b200_fused_config(4, 1)
+    tiles = (M_ // 128) * (N_ // 256)
+    em = EmuFused(W, int(lib.b200_fused_owned_tiles(M_, N_, W, 0)), tiles, dev)
+    out = [torch.zeros(M_, N_, dtype=torch.bfloat16, device=dev) for _ in range(W)]
+    fn = lambda: em.gemm(A, am_, B, bm_, M_, N_, K_, out, 0, op, True, alpha=1e-6)
+if case == "philox":
+    buf = torch.empty(T * D, dtype=torch.bfloat16, device=dev)
+    fn = lambda: nv.randn_(buf, 1234, 1.0)
+if case == "colsum":
+    fn = lambda: nv.colsum(a)
 if case == "fused_dw":
     # the fused GEMM + collective kernel in a world of ONE: pushes to its own inbox, side warps reduce + apply SGD
     import ctypes as C

@@ -50,6 +50,7 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--mp_mode', default='ar', choices=['ar', 'sp', 'spf'])
     p.add_argument('--fsdp_gather', default='dma', choices=['dma', 'fused'], help='fused FSDP: copy-engine prefetch, or all-gather inside the consuming GEMMs')
     p.add_argument('--mp_input', default='full', choices=['full', 'sharded'])
+    p.add_argument('--stochastic_rounding', action='store_true', help='bf16: round optimizer updates stochastically (no fp32 master weights)')
     p.add_argument('--nvls', default='auto', choices=['auto', 'off'], help='fused MP all-reduce: sum inside the NVSwitch (multimem) where available')
     p.add_argument('--master_port', type=int, default=29500)
     p.add_argument('--save_path', default=None)
@@ -65,6 +66,9 @@ def main(argv=None) -> int:
     args = build_parser().parse_args(argv)
     cfg_kwargs = {k: v for k, v in vars(args).items() if v is not None}
     cfg = TrainConfig(**cfg_kwargs)
+    if cfg.dtype == 'bf16' and not cfg.stochastic_rounding and cfg.lr * cfg.grad_scale < 1e-3:
+        print(f'note: bf16 weights are updated in place without an fp32 master copy; at lr={cfg.lr} most updates are below half a '
+              'bf16 ulp of the weight and round away. Pass --stochastic_rounding (or use --dtype fp32, the reference\'s dtype).')
     ffn = cfg.ffn_dim
 
     print(f'ARGS:\n num_steps: {args.num_steps}\n BS: {args.batch_size}\n N: {args.seq_len}\n D: {args.model_size}\n FFN: {ffn}\n')
@@ -77,10 +81,14 @@ def main(argv=None) -> int:
     seeds = make_seeds(args.num_steps, gen)
     layers_params = init_stack(args.layers, args.model_size, ffn, gen, bias=args.bias)
     start_step = 0
+    opt_state = None
     if args.load_path:
         ck = load_checkpoint(args.load_path)
         layers_params = ck["layers_params"]
         start_step = ck.get("step", 0)
+        opt_state = ck.get("optimizer") or None       # Adam moments + step count, full layout: resumes under any strategy
+        if args.optimizer == "adam" and not (opt_state and opt_state.get("kind") == "adam"):
+            print("warning: resuming an Adam run from a checkpoint without Adam state - the moments restart at zero")
         if ck.get("seeds") is not None and len(ck["seeds"]) == len(seeds):
             seeds = ck["seeds"]
         print(f'resumed from {args.load_path} at step {start_step}')
@@ -97,7 +105,7 @@ def main(argv=None) -> int:
     for i, fn in enumerate(fns):
         if args.method == 0 or args.method == i + 1:
             t0 = time.time()
-            out = fn(layers_params, run_seeds, args.batch_size * args.seq_len, args.model_size, cfg)
+            out = fn(layers_params, run_seeds, args.batch_size * args.seq_len, args.model_size, cfg, opt_state)
             t1 = time.time()
             fns_layers_params.append(out)
             st = api.last_stats()
@@ -109,7 +117,7 @@ def main(argv=None) -> int:
             print(f'final {fn.__name__} layers_params[0]', out[0][0][:5, :5], out[0][1][:5, :5])
             if args.save_path:
                 path = args.save_path if args.method != 0 else f'{args.save_path}.{fn.__name__}'
-                save_checkpoint(path, out, step=len(seeds), args=cfg.to_dict(), seeds=seeds)
+                save_checkpoint(path, out, step=len(seeds), args=cfg.to_dict(), seeds=seeds, optimizer=api.last_optimizer_state())
                 print(f'saved {path}')
 
     if args.method == 0:   # compare DDP against FSDP (train_ffns.py:386-391)
