@@ -149,6 +149,7 @@ struct FusedEpiT {
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
     static constexpr int EXTRA_WARPS = SIDE_WARPS;   // side warps reduce/broadcast owned tiles under the MMAs
     static constexpr int LAUNCH_BOUND_PAD = PAD;
+    static constexpr int PRODUCTS = 1;
     struct State {
         int k_local;               // inbox slot of the tile being pushed
         int owner;

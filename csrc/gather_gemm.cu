@@ -98,6 +98,7 @@ struct GatherEpi {
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
     static constexpr int EXTRA_WARPS = GATHER_SIDE_WARPS;
     static constexpr int LAUNCH_BOUND_PAD = 0;       // 384 threads: the epilogue warps keep 168 registers
+    static constexpr int PRODUCTS = 1;
 
     static __device__ __forceinline__ void init(const Params& p, const GemmCore& g, const EpiCtx& c, State& s) { Local::init(p.base, g, c, s); }
     static __device__ __forceinline__ void process_tile(const Params& p, const GemmCore& g, const EpiCtx& c, uint32_t taddr, State& s) {

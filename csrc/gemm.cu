@@ -44,13 +44,19 @@ int make_core_and_maps(const GemmOperands& o, GemmCore* core, CUtensorMap* tmA, 
     core->group_m = 16;
     core->tile_offset = 0;
     core->err = device_error_slot();
+    core->a_plane = (int)o.a_plane; core->b_plane = (int)o.b_plane;
+    const long long a_rows = (o.a_major == MAJOR_K ? o.M : o.K) + (long long)(o.planes - 1) * o.a_plane;   // storage rows incl. the stacked planes
+    const long long b_rows = (o.b_major == MAJOR_K ? o.N : o.K) + (long long)(o.planes - 1) * o.b_plane;
+    if (o.planes > 1 && ((o.a_major == MAJOR_MN || o.b_major == MAJOR_MN) && (o.K % BK))) {
+        set_last_error("gemm (split operands): K must be a multiple of 64 when an operand is MN-major (K=%d)", o.K); return B200_ERR_ARG;
+    }
     // K-major boxes: the pair kernel stages 256 A rows and 128 B rows per CTA, the 1-CTA kernel 128 and 256
-    if (o.a_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmA, o.A, o.K, o.M, o.lda, BK, pair ? 256 : BM);
-    else                      rc = encode_tmap_bf16_2d(tmA, o.A, o.M, o.K, o.lda, 64, BK);
+    if (o.a_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmA, o.A, o.K, a_rows, o.lda, BK, pair ? 256 : BM);
+    else                      rc = encode_tmap_bf16_2d(tmA, o.A, o.M, a_rows, o.lda, 64, BK);
     if (rc != 0) return rc;
     // the pair kernel stages 128 B rows per CTA, the 1-CTA kernel all 256
-    if (o.b_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmB, o.B, o.K, o.N, o.ldb, BK, pair ? 128 : BN);
-    else                      rc = encode_tmap_bf16_2d(tmB, o.B, o.N, o.K, o.ldb, 64, BK);
+    if (o.b_major == MAJOR_K) rc = encode_tmap_bf16_2d(tmB, o.B, o.K, b_rows, o.ldb, BK, pair ? 128 : BN);
+    else                      rc = encode_tmap_bf16_2d(tmB, o.B, o.N, b_rows, o.ldb, 64, BK);
     return rc;
 }
 

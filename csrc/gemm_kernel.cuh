@@ -45,7 +45,16 @@ struct GemmCore {
     // gridDim; the single-launch multi-rank emulation (emu kernels below) gives every emulated rank its own slice of one
     // cooperative grid, so the bodies and the epilogue policies must never read blockIdx.x / gridDim.x themselves.
     int cta, ncta;
+    // Split-operand GEMMs (fp32 emulation, Epi::PRODUCTS > 1): each operand is `3` bf16 planes stacked along its storage
+    // rows, plane p starting a_plane / b_plane rows after plane p-1 (0 for ordinary single-plane operands).
+    int a_plane, b_plane;
 };
+
+// fp32 x fp32 from bf16 tensor cores: a = a0 + a1 + a2 (bf16 each, 24 mantissa bits in all), likewise b; the six products
+// whose magnitude is >= 2^-16 of the result are accumulated in the fp32 TMEM accumulator, SMALLEST FIRST.
+//   (1,1) (0,2) (2,0) (0,1) (1,0) (0,0)
+__device__ __forceinline__ int split_plane_a(int pr) { return (0x102010 >> (4 * (5 - pr))) & 0xf; }   // 1,0,2,0,1,0
+__device__ __forceinline__ int split_plane_b(int pr) { return (0x120100 >> (4 * (5 - pr))) & 0xf; }   // 1,2,0,1,0,0
 
 // tile index -> (m_blk, n_blk) with grouped rasterisation so the ~148 tiles in flight share A/B panels in L2
 __host__ __device__ __forceinline__ void tile_coords(const GemmCore& g, int tile, int& m_blk, int& n_blk) {
@@ -182,26 +191,35 @@ __device__ __forceinline__ void gemm_1cta_body(const CUtensorMap& tmA, const CUt
             tile_coords(g, tile, m_blk, n_blk);
             const int m0 = m_blk * BM, n0 = n_blk * BN;
             Epi::before_loads(ep, g, m_blk, 1);
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int kbe = Epi::kblock(ep, g, kb, num_kb, pst);     // which k-block this iteration loads (kb itself by default)
-                mbar_wait(&sm.empty[s], phase ^ 1, g.err, 0x100 + s);
-                mbar_arrive_expect_tx(&sm.full[s], STAGE_BYTES);
-                const int k0 = kbe * BK;
-                if (g.a_major == MAJOR_K) {
-                    tma_load_2d(sm.a(s), &tmA, &sm.full[s], k0, m0);          // box {64 k, 128 m}
-                } else {
-#pragma unroll
-                    for (int j = 0; j < BM / 64; ++j)                          // box {64 m, 64 k} per atom
-                        tma_load_2d(sm.a(s) + j * (BK * 128), &tmA, &sm.full[s], m0 + j * 64, k0);
+#pragma unroll 1
+            for (int pr = 0; pr < Epi::PRODUCTS; ++pr) {                 // 1, or the 6 plane products of the fp32 emulation
+                int am = m0, ak = 0, bn = n0, bk = 0;                    // plane offsets along the operand's storage rows
+                if constexpr (Epi::PRODUCTS > 1) {
+                    const int pa = split_plane_a(pr) * g.a_plane, pb = split_plane_b(pr) * g.b_plane;
+                    if (g.a_major == MAJOR_K) am += pa; else ak = pa;
+                    if (g.b_major == MAJOR_K) bn += pb; else bk = pb;
                 }
-                if (g.b_major == MAJOR_K) {
-                    tma_load_2d(sm.b(s), &tmB, &sm.full[s], k0, n0);          // box {64 k, 256 n}
-                } else {
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int kbe = Epi::kblock(ep, g, kb, num_kb, pst);     // which k-block this iteration loads (kb itself by default)
+                    mbar_wait(&sm.empty[s], phase ^ 1, g.err, 0x100 + s);
+                    mbar_arrive_expect_tx(&sm.full[s], STAGE_BYTES);
+                    const int k0 = kbe * BK;
+                    if (g.a_major == MAJOR_K) {
+                        tma_load_2d(sm.a(s), &tmA, &sm.full[s], k0, am);          // box {64 k, 128 m}
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < BN / 64; ++j)
-                        tma_load_2d(sm.b(s) + j * (BK * 128), &tmB, &sm.full[s], n0 + j * 64, k0);
+                        for (int j = 0; j < BM / 64; ++j)                          // box {64 m, 64 k} per atom
+                            tma_load_2d(sm.a(s) + j * (BK * 128), &tmA, &sm.full[s], am + j * 64, k0 + ak);
+                    }
+                    if (g.b_major == MAJOR_K) {
+                        tma_load_2d(sm.b(s), &tmB, &sm.full[s], k0, bn);          // box {64 k, 256 n}
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_2d(sm.b(s) + j * (BK * 128), &tmB, &sm.full[s], bn + j * 64, k0 + bk);
+                    }
+                    if (++s == STAGES) { s = 0; phase ^= 1; }
                 }
-                if (++s == STAGES) { s = 0; phase ^= 1; }
             }
         }
     } else if (threadIdx.x == 32) {
@@ -226,7 +244,8 @@ __device__ __forceinline__ void gemm_1cta_body(const CUtensorMap& tmA, const CUt
             mbar_wait(&sm.tmem_empty[as], aphase ^ 1, g.err, 0x200 + as);
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + (uint32_t)(as * BN);
-            for (int kb = 0; kb < num_kb; ++kb) {
+            const int kb_total = num_kb * Epi::PRODUCTS;             // all plane products accumulate into the same tile
+            for (int kb = 0; kb < kb_total; ++kb) {
                 mbar_wait(&sm.full[s], phase, g.err, 0x300 + s);
                 tc_fence_after();
                 const uint32_t a_base = smem_u32(sm.a(s));
@@ -238,7 +257,7 @@ __device__ __forceinline__ void gemm_1cta_body(const CUtensorMap& tmA, const CUt
                     umma_bf16(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
                 }
                 umma_commit(&sm.empty[s]);                       // smem slot free once these MMAs retire
-                if (kb == num_kb - 1) umma_commit(&sm.tmem_full[as]);
+                if (kb == kb_total - 1) umma_commit(&sm.tmem_full[as]);
                 if (++s == STAGES) { s = 0; phase ^= 1; }
             }
             if (++as == 2) { as = 0; aphase ^= 1; }
@@ -372,29 +391,38 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap& tmA, const CUt
             const int m0 = (pm * 4 + (int)rank * 2) * BM;        // my 256 rows of A
             const int n0 = n_blk * BN + (int)rank * 128;         // my 128 rows of B
             Epi::before_loads(ep, g, pm * 4 + (int)rank * 2, 2);
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int kbe = Epi::kblock(ep, g, kb, num_kb, pst);
-                mbar_wait(&empty[s], phase ^ 1, g.err, 0x100 + s);
-                // The peer's bytes may land before this arrival: the transaction count just goes negative for a
-                // moment, and the phase cannot complete until the one pending arrival (this one) has happened.
-                if (rank == 0) mbar_arrive_expect_tx(&full[s], 2 * P_STAGE_BYTES);
-                const int k0 = kbe * BK;
-                uint8_t* a_dst = sA + s * P_A_STAGE_BYTES;
-                uint8_t* b_dst = sB + s * P_B_STAGE_BYTES;
-                if (g.a_major == MAJOR_K) {
-                    tma_load_2d_pair(a_dst, &tmA, &full[s], k0, m0);                       // box {64 k, 256 m}
-                } else {
+#pragma unroll 1
+            for (int pr = 0; pr < Epi::PRODUCTS; ++pr) {                 // 1, or the 6 plane products of the fp32 emulation
+                int am = m0, ak = 0, bn = n0, bk = 0;
+                if constexpr (Epi::PRODUCTS > 1) {
+                    const int pa = split_plane_a(pr) * g.a_plane, pb = split_plane_b(pr) * g.b_plane;
+                    if (g.a_major == MAJOR_K) am += pa; else ak = pa;
+                    if (g.b_major == MAJOR_K) bn += pb; else bk = pb;
+                }
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int kbe = Epi::kblock(ep, g, kb, num_kb, pst);
+                    mbar_wait(&empty[s], phase ^ 1, g.err, 0x100 + s);
+                    // The peer's bytes may land before this arrival: the transaction count just goes negative for a
+                    // moment, and the phase cannot complete until the one pending arrival (this one) has happened.
+                    if (rank == 0) mbar_arrive_expect_tx(&full[s], 2 * P_STAGE_BYTES);
+                    const int k0 = kbe * BK;
+                    uint8_t* a_dst = sA + s * P_A_STAGE_BYTES;
+                    uint8_t* b_dst = sB + s * P_B_STAGE_BYTES;
+                    if (g.a_major == MAJOR_K) {
+                        tma_load_2d_pair(a_dst, &tmA, &full[s], k0, am);                       // box {64 k, 256 m}
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)                                            // 4 x box {64 m, 64 k}
-                        tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, &full[s], m0 + j * 64, k0);
+                        for (int j = 0; j < 4; ++j)                                            // 4 x box {64 m, 64 k}
+                            tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, &full[s], am + j * 64, k0 + ak);
+                    }
+                    if (g.b_major == MAJOR_K) {
+                        tma_load_2d_pair(b_dst, &tmB, &full[s], k0, bn);                       // box {64 k, 128 n}
+                    } else {
+                        tma_load_2d_pair(b_dst, &tmB, &full[s], bn, k0 + bk);
+                        tma_load_2d_pair(b_dst + BK * 128, &tmB, &full[s], bn + 64, k0 + bk);
+                    }
+                    if (++s == P_STAGES) { s = 0; phase ^= 1; }
                 }
-                if (g.b_major == MAJOR_K) {
-                    tma_load_2d_pair(b_dst, &tmB, &full[s], k0, n0);                       // box {64 k, 128 n}
-                } else {
-                    tma_load_2d_pair(b_dst, &tmB, &full[s], n0, k0);
-                    tma_load_2d_pair(b_dst + BK * 128, &tmB, &full[s], n0 + 64, k0);
-                }
-                if (++s == P_STAGES) { s = 0; phase ^= 1; }
             }
         }
     } else if (threadIdx.x == 32 && rank == 0) {
@@ -409,8 +437,9 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap& tmA, const CUt
         int s = 0;
         uint32_t phase = 0;
         uint32_t tphase = 0;
+        const int kb_total = num_kb * Epi::PRODUCTS;                 // all plane products accumulate into the same tile
         for (int it = pair; it < num_tiles; it += num_pairs) {
-            for (int kb = 0; kb < num_kb; ++kb) {
+            for (int kb = 0; kb < kb_total; ++kb) {
                 mbar_wait(&full[s], phase, g.err, 0x300 + s);
                 tc_fence_after();
                 const uint32_t a_base = smem_u32(sA + s * P_A_STAGE_BYTES);
@@ -429,7 +458,7 @@ __device__ __forceinline__ void gemm_pair_body(const CUtensorMap& tmA, const CUt
                     }
                 }
                 umma_commit_pair(&empty[s]);                         // frees the slot in BOTH CTAs
-                if (kb == num_kb - 1) umma_commit_pair(&tmem_full[0]);
+                if (kb == kb_total - 1) umma_commit_pair(&tmem_full[0]);
                 if (++s == P_STAGES) { s = 0; phase ^= 1; }
             }
             tphase ^= 1;
@@ -615,6 +644,7 @@ struct LocalEpi {
     static constexpr int SMEM_BYTES = GEMM_SMEM_BYTES_STAGED;
     static constexpr int EXTRA_WARPS = 0;
     static constexpr int LAUNCH_BOUND_PAD = 0;
+    static constexpr int PRODUCTS = 1;
     static __device__ __forceinline__ void side_loop(const Params&, const GemmCore&, int, int, uint32_t*) {}
     static __device__ __forceinline__ void before_loads(const Params&, const GemmCore&, int, int) {}
     struct ProducerState {};
@@ -758,6 +788,8 @@ struct GemmOperands {
     const void* A; long long lda; int a_major;
     const void* B; long long ldb; int b_major;
     int M, N, K;
+    int planes = 1;                       // 3: split fp32 operands (three bf16 planes stacked along the storage rows)
+    long long a_plane = 0, b_plane = 0;   // storage rows between consecutive planes
 };
 
 int validate_operands(const GemmOperands& o);

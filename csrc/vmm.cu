@@ -417,7 +417,8 @@ static int nvls_launch(int mode, bool allow_one_shot, bool f32, void* mc_ptr, vo
     if (mode == 1) {
         blocks = (int)((V + NVLS_THREADS * NVLS_UNROLL - 1) / (NVLS_THREADS * NVLS_UNROLL));
     } else if (blocks <= 0) {
-        const long long want = (V / world + NVLS_THREADS * NVLS_UNROLL - 1) / (NVLS_THREADS * NVLS_UNROLL);
+        // one vector per thread until every SM has a CTA (mid sizes are latency-bound: spread them), then deeper loops
+        const long long want = (V / world + NVLS_THREADS - 1) / NVLS_THREADS;
         blocks = (int)(want < 1 ? 1 : (want > NVLS_MAX_BLOCKS ? NVLS_MAX_BLOCKS : want));
     }
     if (blocks > NVLS_MAX_BLOCKS) blocks = NVLS_MAX_BLOCKS;

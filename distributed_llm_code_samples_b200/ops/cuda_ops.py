@@ -1,8 +1,10 @@
 """Op interface on the hand-written sm_100a kernels (``libb200ffn.so``).
 
 bf16 tensors whose shapes meet the TMA constraints go to the tcgen05 GEMM with the elementwise work fused in
-its epilogue; anything else (fp32 parity mode, toy widths such as the CLI default ``model_size=4``) goes to the
-``TorchOps`` path and is counted in ``fallbacks`` so benchmarks can assert it stayed at zero."""
+its epilogue.  fp32 tensors (the reference's dtype and the CLI default) go to the SAME mainloop through split operands:
+three bf16 planes per matrix, six plane products accumulated in fp32 (``csrc/gemm_f32.cu``), fp32 epilogues.  Anything
+else (toy widths such as the CLI default ``model_size=4``) goes to the ``TorchOps`` path and is counted in ``fallbacks``
+so benchmarks can assert it stayed at zero."""
 from __future__ import annotations
 
 from typing import Optional, Tuple
@@ -45,10 +47,31 @@ class CudaOps(TorchOps):
         self.fallbacks += 1
         return super()
 
+    # ---- fp32 (reference-parity) path: split operands, six bf16 tensor-core products, fp32 epilogues ------------------
+    @staticmethod
+    def _ok32(*tensors: torch.Tensor) -> bool:
+        for t in tensors:
+            if t is None:
+                continue
+            if (not t.is_cuda or t.dtype != torch.float32 or t.dim() != 2 or t.stride(1) != 1
+                    or t.stride(0) % 8 or t.shape[1] % 8 or t.data_ptr() % 16):
+                return False
+        return True
+
+    @staticmethod
+    def _is32(*tensors: torch.Tensor) -> bool:
+        return all(t is None or t.dtype == torch.float32 for t in tensors)
+
     # ---- forward -----------------------------------------------------------------------------------------
     def linear_act(self, x, W, act, bias=None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
         T, K = x.shape
         N = W.shape[0]
+        if self._is32(x, W) and self._ok32(x, W):
+            a = torch.empty(T, N, dtype=torch.float32, device=x.device)
+            pre = torch.empty_like(a) if act == "gelu" else None
+            nv.gemm_f32(nv.split3(x), nv.MAJOR_K, nv.split3(W), nv.MAJOR_K, a, T, N, K, nv.EPI_RELU if act == "relu" else nv.EPI_GELU,
+                        out2=pre, bias=self._bias32(bias), max_ctas=self.max_ctas)
+            return a, pre
         if not self._ok(x, W) or N % 8:
             return self._fb().linear_act(x, W, act, bias)
         a = torch.empty(T, N, dtype=torch.bfloat16, device=x.device)
@@ -68,6 +91,11 @@ class CudaOps(TorchOps):
     def linear(self, a, W, bias=None, residual=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         T, K = a.shape
         N = W.shape[0]
+        if self._is32(a, W, residual) and self._ok32(a, W, residual):
+            y = torch.empty(T, N, dtype=torch.float32, device=a.device) if out is None else out
+            nv.gemm_f32(nv.split3(a), nv.MAJOR_K, nv.split3(W), nv.MAJOR_K, y, T, N, K, nv.EPI_ADD if residual is not None else nv.EPI_STORE,
+                        aux=residual, bias=self._bias32(bias), max_ctas=self.max_ctas)
+            return y
         if not self._ok(a, W, residual) or N % 8:
             return self._fb().linear(a, W, bias, residual)
         y = torch.empty(T, N, dtype=torch.bfloat16, device=a.device) if out is None else out
@@ -83,6 +111,17 @@ class CudaOps(TorchOps):
         T, K = dy.shape           # K = out features of the layer
         N = W.shape[1]            # in features
         mask_aux = aux is not None and aux.dtype == torch.uint8
+        if self._is32(dy, W, aux, add) and self._ok32(dy, W, aux, add) and not (act is not None and add is not None):
+            dx = torch.empty(T, N, dtype=torch.float32, device=dy.device) if out is None else out
+            epi, ax = nv.EPI_STORE, None
+            if act == "relu":
+                epi, ax = nv.EPI_RELU_BWD, aux
+            elif act == "gelu":
+                epi, ax = nv.EPI_GELU_BWD, aux
+            elif add is not None:
+                epi, ax = nv.EPI_ADD, add
+            nv.gemm_f32(nv.split3(dy), nv.MAJOR_K, nv.split3(W), nv.MAJOR_MN, dx, T, N, K, epi, aux=ax, max_ctas=self.max_ctas)
+            return dx
         if not self._ok(dy, W, None if mask_aux else aux, add) or N % 8 or (act is not None and add is not None):
             if mask_aux:
                 raise nv.NativeError("grad_input: a packed ReLU mask can only be consumed by the native kernel")
@@ -103,6 +142,10 @@ class CudaOps(TorchOps):
     def grad_weight(self, dy, x, out_dtype=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         T, M = dy.shape
         N = x.shape[1]
+        if self._is32(dy, x) and self._ok32(dy, x) and T % 64 == 0 and out_dtype in (None, torch.float32):
+            dW = out if out is not None else torch.empty(M, N, dtype=torch.float32, device=dy.device)
+            nv.gemm_f32(nv.split3(dy), nv.MAJOR_MN, nv.split3(x), nv.MAJOR_MN, dW, M, N, T, nv.EPI_STORE, max_ctas=self.max_ctas)
+            return dW
         if not self._ok(dy, x) or N % 8 or M % 8:
             return self._fb().grad_weight(dy, x, out_dtype)
         f32 = out_dtype == torch.float32
@@ -115,6 +158,9 @@ class CudaOps(TorchOps):
         """``W -= lr * dy^T @ x`` in ONE kernel: the gradient tile never leaves TMEM/registers."""
         T, M = dy.shape
         N = x.shape[1]
+        if self._is32(dy, x, W) and self._ok32(dy, x, W) and T % 64 == 0:
+            nv.gemm_f32(nv.split3(dy), nv.MAJOR_MN, nv.split3(x), nv.MAJOR_MN, W, M, N, T, nv.EPI_SGD, alpha=lr, max_ctas=self.max_ctas)
+            return
         if not self._ok(dy, x, W) or N % 8 or M % 8:
             return self._fb().grad_weight_sgd_(W, dy, x, lr)
         nv.gemm(dy, nv.MAJOR_MN, x, nv.MAJOR_MN, W, M, N, T, nv.EPI_SGD, alpha=lr, max_ctas=self.max_ctas)

@@ -127,6 +127,8 @@ def _optional_declare(lib) -> None:
         "b200_gather_gemm_bf16": ([pp, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp], i),
         "b200_debug_gather_chunk": ([i, i, i, i, ll, C.POINTER(ll)], i),
         "b200_fused_config": ([i, i], i),
+        "b200_split_f32": ([vp, vp, ll, i, ll, vp], i),
+        "b200_gemm_f32": ([vp, ll, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, i, vp], i),
         "b200_set_update_rounding": ([u], i),
         "b200_fused_partial_bytes": ([i], ll),
         "b200_nvls_collective": ([i, i, vp, vp, ll, pp, i, i, u, i, vp], i),
@@ -191,6 +193,32 @@ def gemm(A: torch.Tensor, a_major: int, B: torch.Tensor, b_major: int, out: torc
         M, N, K, epilogue, _ptr(aux), aux.stride(0) if aux is not None else 0, _ptr(out2),
         out2.stride(0) if out2 is not None else 0, _ptr(bias), float(alpha), int(max_ctas), _stream())
     _check(rc, "b200_gemm_bf16")
+    launch_count += 1
+    return out
+
+
+def split3(x: torch.Tensor) -> torch.Tensor:
+    """fp32 ``[rows, cols]`` -> its three bf16 planes ``[3, rows, cols]`` (x = p0 + p1 + p2 to the last fp32 ulp)."""
+    global launch_count
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    rows, cols = x.shape
+    out = torch.empty(3, rows, cols, dtype=torch.bfloat16, device=x.device)
+    _check(load().b200_split_f32(out.data_ptr(), x.data_ptr(), rows, cols, x.stride(0), _stream()), "b200_split_f32")
+    launch_count += 1
+    return out
+
+
+def gemm_f32(A3: torch.Tensor, a_major: int, B3: torch.Tensor, b_major: int, out: torch.Tensor, M: int, N: int, K: int,
+             epilogue: int = EPI_STORE, aux: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None,
+             bias: Optional[torch.Tensor] = None, alpha: float = 1.0, max_ctas: int = 0) -> torch.Tensor:
+    """fp32 ``out[M,N] = epilogue(A . B)`` from the split planes of A and B (``split3``): six bf16 tensor-core products
+    accumulated in fp32 (csrc/gemm_f32.cu).  Epilogues STORE, RELU, GELU, RELU_BWD, GELU_BWD, ADD, SGD; all tensors fp32."""
+    global launch_count
+    assert A3.dtype == torch.bfloat16 and B3.dtype == torch.bfloat16 and A3.dim() == 3 and B3.dim() == 3 and out.dtype == torch.float32
+    rc = load().b200_gemm_f32(A3.data_ptr(), A3.shape[2], a_major, B3.data_ptr(), B3.shape[2], b_major, out.data_ptr(), out.stride(0),
+                              M, N, K, epilogue, _ptr(aux), aux.stride(0) if aux is not None else 0, _ptr(out2),
+                              out2.stride(0) if out2 is not None else 0, _ptr(bias), float(alpha), int(max_ctas), _stream())
+    _check(rc, "b200_gemm_f32")
     launch_count += 1
     return out
 

@@ -220,7 +220,10 @@ class SymmComm:
     def _reduce(self, op: int, buf, off: int, nbytes: int, f32: bool, chan: "CollChannel", e: int, s, fallback) -> None:
         """All-reduce (op 0) / reduce-scatter (op 1) of ``nbytes`` at ``off`` of symmetric block ``buf``: inside the
         NVSwitch when the block is multicast-bound (multimem.ld_reduce / multimem.st), else on the peer-pointer kernels."""
-        if getattr(buf, "mc_ptr", None):
+        # Two ranks gain nothing from the switch on large messages (measured, profiles/bench/r2/coll_sweep_n2_nvls.jsonl: the
+        # peer-pointer two-shot moves the same bytes with one barrier less); from four ranks on NVLS halves the traffic.
+        use_nvls = getattr(buf, "mc_ptr", None) and (self.world >= 4 or nbytes <= (512 << 10))
+        if use_nvls:
             nv._check(self.lib.b200_nvls_collective(op, int(f32), buf.mc_ptr + off, buf.ptr + off, nbytes, chan.flags.peers_c,
                                                     self.rank, self.world, e, 0, s), "b200_nvls_collective")
         else:

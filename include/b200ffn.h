@@ -68,6 +68,18 @@ int b200_gemm_bf16(const void* A, long long lda, int a_major, const void* B, lon
                    void* C, long long ldc, int M, int N, int K, int epilogue, const void* aux, long long ldaux,
                    void* C2, long long ldc2, const float* bias, float alpha, int max_ctas, void* stream);
 
+/* ---- fp32 GEMM on the bf16 tensor cores (reference-parity mode; csrc/gemm_f32.cu) ------------------------------------
+ * The reference trains in fp32 (train_ffns.py:36, :149).  b200_split_f32 turns an fp32 matrix [rows, cols] (row pitch
+ * ld_in) into three bf16 planes [3][rows][cols] whose sum is the matrix to the last fp32 ulp; b200_gemm_f32 multiplies
+ * two such operands with six plane products accumulated in the fp32 TMEM accumulator (smallest first): fp32-accurate
+ * results at 6x the bf16 MMA work.  Majors / M,N,K as b200_gemm_bf16 (lda / ldb = cols of the split matrix); every other
+ * tensor (C, aux, C2, bias) is fp32.  Epilogues: STORE (C = alpha*acc + bias), RELU, GELU (+C2 = pre-activation),
+ * RELU_BWD, GELU_BWD, ADD, SGD (C -= alpha*acc).  cols % 8 == 0; MN-major operands need K % 64 == 0. */
+int b200_split_f32(void* planes_out, const float* in, long long rows, int cols, long long ld_in, void* stream);
+int b200_gemm_f32(const void* A3, long long lda, int a_major, const void* B3, long long ldb, int b_major,
+                  float* C, long long ldc, int M, int N, int K, int epilogue, const float* aux, long long ldaux,
+                  float* C2, long long ldc2, const float* bias, float alpha, int max_ctas, void* stream);
+
 /* ---- elementwise / optimizer / data --------------------------------------------------------------------- */
 /* p -= lr * g  (:114, :172, :259, :312).  grad_f32 != 0: g is fp32, else bf16.  n % 8 == 0 not required. */
 int b200_sgd_bf16(void* param, const void* grad, long long n, float lr, int grad_f32, void* stream);

@@ -304,3 +304,61 @@ def test_stochastic_rounding_keeps_sub_ulp_updates(cuda_device):
             assert not torch.equal(sr_a, sr_c), "a different seed rounds different elements"
     finally:
         nv.set_update_rounding(0)
+
+
+@pytest.mark.parametrize("layout", ["tn", "nn", "nt"])
+@pytest.mark.parametrize("M,N,K", [(256, 512, 256), (200, 264, 192), (1024, 768, 2048)])
+def test_gemm_f32_split_operands(cuda_device, layout, M, N, K):
+    """fp32 GEMM on the bf16 tensor cores (3 planes per operand, 6 plane products, fp32 accumulate): error against an fp64
+    oracle must be at fp32 level - orders of magnitude below a bf16 or TF32 GEMM - in every operand layout."""
+    g = torch.Generator(device="cpu").manual_seed(3)
+    a = torch.randn(M, K, generator=g).to(cuda_device)
+    b = (torch.randn(N, K, generator=g) * 0.1).to(cuda_device)
+    ref = a.double() @ b.double().T
+    out = torch.empty(M, N, device=cuda_device)
+    if layout == "tn":
+        nv.gemm_f32(nv.split3(a), 0, nv.split3(b), 0, out, M, N, K)
+    elif layout == "nn":
+        nv.gemm_f32(nv.split3(a), 0, nv.split3(b.T.contiguous()), 1, out, M, N, K)
+    else:
+        nv.gemm_f32(nv.split3(a.T.contiguous()), 1, nv.split3(b.T.contiguous()), 1, out, M, N, K)
+    torch.cuda.synchronize()
+    scale = (a.double().abs() @ b.double().abs().T).max().item()          # sum_k |a||b|: the natural error scale of a dot product
+    err = (out.double() - ref).abs().max().item()
+    assert err <= 4e-6 * scale, (layout, err, scale)                       # bf16 would be ~4e-3, TF32 ~5e-4
+    planes = nv.split3(a)
+    assert (planes.double().sum(0) - a.double()).abs().max().item() <= 2 ** -23 * a.abs().max().item()
+
+
+def test_gemm_f32_epilogues(cuda_device):
+    M, N, K = 384, 512, 320
+    g = torch.Generator(device="cpu").manual_seed(4)
+    x, w = torch.randn(M, K, generator=g).to(cuda_device), (torch.randn(N, K, generator=g) * 0.1).to(cuda_device)
+    aux, bias = torch.randn(M, N, generator=g).to(cuda_device), torch.randn(N, generator=g).to(cuda_device)
+    ref = (x.double() @ w.double().T)
+    X, W = nv.split3(x), nv.split3(w)
+    out, out2 = torch.empty(M, N, device=cuda_device), torch.empty(M, N, device=cuda_device)
+    tol = 1e-4
+
+    def close(o, r, what):
+        assert (o.double() - r).abs().max().item() <= tol * max(1.0, r.abs().max().item()), what
+
+    nv.gemm_f32(X, 0, W, 0, out, M, N, K, nv.EPI_RELU, bias=bias)
+    close(out, torch.relu(ref + bias.double()), "relu+bias")
+    nv.gemm_f32(X, 0, W, 0, out, M, N, K, nv.EPI_GELU, out2=out2)
+    close(out, torch.nn.functional.gelu(ref), "gelu")
+    close(out2, ref, "gelu pre-activation")
+    nv.gemm_f32(X, 0, W, 0, out, M, N, K, nv.EPI_RELU_BWD, aux=aux)
+    close(out, ref * (aux.double() > 0), "relu_bwd")
+    nv.gemm_f32(X, 0, W, 0, out, M, N, K, nv.EPI_GELU_BWD, aux=aux)
+    a64 = aux.double().requires_grad_(True)
+    torch.nn.functional.gelu(a64).sum().backward()
+    close(out, ref * a64.grad, "gelu_bwd")
+    nv.gemm_f32(X, 0, W, 0, out, M, N, K, nv.EPI_ADD, aux=aux, bias=bias)
+    close(out, ref + aux.double() + bias.double(), "add")
+    wgt = torch.randn(M, N, generator=g).to(cuda_device)
+    w0 = wgt.double().clone()
+    nv.gemm_f32(X, 0, W, 0, wgt, M, N, K, nv.EPI_SGD, alpha=0.05)
+    close(wgt, w0 - 0.05 * ref, "sgd")
+    nv.gemm_f32(X, 0, W, 0, out, M, N, K, nv.EPI_STORE, alpha=0.5)
+    close(out, 0.5 * ref, "store*alpha")

@@ -87,6 +87,36 @@ def test_north_star_block_native_no_fallbacks(cuda_device, optimizer):
             assert rel <= (0.12 if j < 2 else 0.05), (j, rel)      # biases are fp32 on both sides
 
 
+@pytest.mark.parametrize("act,residual", [("relu", False), ("gelu", True)])
+def test_fp32_parity_mode_runs_on_native_kernels(cuda_device, act, residual):
+    """--dtype fp32 (the reference's dtype, train_ffns.py:36,:149, and this CLI's default) must NOT fall back to cuBLAS/ATen:
+    every GEMM runs on tcgen05 through split bf16 operands (csrc/gemm_f32.cu), and the result matches the PyTorch fp32 path
+    to fp32 accuracy - tight enough for the reference's own DDP==FSDP allclose (rtol 1e-5) to be meaningful."""
+    from distributed_llm_code_samples_b200.config import TrainConfig
+    from distributed_llm_code_samples_b200.ops import get_ops
+    from distributed_llm_code_samples_b200.parallel.base import place
+    from distributed_llm_code_samples_b200.parallel.single import SingleTrainer
+    lp, x, dy = _setup(cuda_device)
+    cfg = TrainConfig(model_size=256, ffn_dim=1024, dtype="fp32", lr=0.05, activation=act, residual=residual)
+    nat = SingleTrainer(get_ops("native", cuda_device), cfg, place(lp, cuda_device, torch.float32))
+    ora = SingleTrainer(get_ops("torch", cuda_device), cfg, place(lp, cuda_device, torch.float32))
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        xb, dyb = x.to(cuda_device), dy.to(cuda_device)
+        for _ in range(2):
+            y = nat.step(xb, dyb)
+            yo = ora.step(xb, dyb)
+        torch.cuda.synchronize()
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    assert nat.ops.fallbacks == 0, "fp32 mode fell back to PyTorch ops"
+    assert torch.allclose(y, yo, rtol=1e-4, atol=1e-5), (y - yo).abs().max()
+    for a, b in zip(nat.params, ora.params):
+        for p, q in zip(a, b):
+            assert torch.allclose(p, q, rtol=1e-4, atol=1e-6), (p - q).abs().max()
+
+
 def test_smoke_entry(cuda_device):
     import __graft_entry__ as ge
     ge.smoke()

@@ -133,6 +133,15 @@ def bench(dev, which: str) -> None:
         ("G4 dW2=dy^T@a NT", lambda: nv.gemm(dy, 1, a, 1, dw2, D, F, T), lambda: dy.T @ a, 2 * T * F * D),
         ("G6 dW1=dh^T@x NT +sgd", lambda: nv.gemm(a, 1, x, 1, dw1, F, D, T, nv.EPI_SGD, alpha=1e-5), lambda: w1.add_(a.T @ x, alpha=-1e-5), 2 * T * F * D),
     ]
+    # fp32 parity mode: split operands, six bf16 plane products (csrc/gemm_f32.cu) vs torch's fp32 GEMM (TF32 off)
+    x32, w32 = x.float(), w1.float()
+    h32 = torch.empty(T, F, dtype=torch.float32, device=dev)
+    X3, W3 = nv.split3(x32), nv.split3(w32)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    cases.append(("F32 h=relu(x@W1^T) fp32 via 6 bf16 plane products (planes pre-split)", lambda: nv.gemm_f32(X3, 0, W3, 0, h32, T, F, D, nv.EPI_RELU),
+                  lambda: torch.relu(x32 @ w32.T), 2 * T * F * D))
+    cases.append(("F32 same incl. splitting both operands", lambda: nv.gemm_f32(nv.split3(x32), 0, nv.split3(w32), 0, h32, T, F, D, nv.EPI_RELU),
+                  lambda: torch.relu(x32 @ w32.T), 2 * T * F * D))
     recs = []
     for name, mine, ref, flops in cases:
         tm = time_fn(mine, flush=flush)

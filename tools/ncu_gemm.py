@@ -23,7 +23,7 @@ fn = {
     "G1m": None, "G5m": None,
     "G7": lambda: nv.gemm(a, 0, w1, 1, y, T, D, F),                                  # NN: B operand MN-major
     "G6": lambda: nv.gemm(a, 1, x, 1, w1, F, D, T, nv.EPI_SGD, alpha=1e-6),          # NT + SGD epilogue (K = tokens)
-    "fused_mp_1cta": None, "emu8_dw": None, "emu8_mp": None, "philox": None, "colsum": None,
+    "fused_mp_1cta": None, "emu8_dw": None, "emu8_mp": None, "philox": None, "colsum": None, "f32": None,
     "G4": lambda: nv.gemm(dy, 1, a, 1, dw, D, F, T),
     "cublas_G1": lambda: torch.matmul(x, w1.T, out=h),
     "cublas_G2": lambda: torch.matmul(a, w2.T, out=y),
@@ -77,6 +77,10 @@ if case in ("emu8_dw", "emu8_mp"):
     em = EmuFused(W, int(lib.b200_fused_owned_tiles(M_, N_, W, 0)), tiles, dev)
     out = [torch.zeros(M_, N_, dtype=torch.bfloat16, device=dev) for _ in range(W)]
     fn = lambda: em.gemm(A, am_, B, bm_, M_, N_, K_, out, 0, op, True, alpha=1e-6)
+if case == "f32":
+    X3, W3 = nv.split3(x.float()), nv.split3(w1.float())
+    h32 = torch.empty(T, F, dtype=torch.float32, device=dev)
+    fn = lambda: nv.gemm_f32(X3, 0, W3, 0, h32, T, F, D, nv.EPI_RELU)
 if case == "philox":
     buf = torch.empty(T * D, dtype=torch.bfloat16, device=dev)
     fn = lambda: nv.randn_(buf, 1234, 1.0)

@@ -3,6 +3,9 @@
 # Raw counter pages are exported on the box; only three .ncu-rep files travel back (size limit).
 O=gpurun_out/r2ncu
 mkdir -p $O
+# (first, without any profiler: the new single-GPU tests and the isolated GEMM timings)
+timeout 600 python -m pytest tests -q -m gpu --deselect tests/test_multigpu.py > $O/suite_1gpu.log 2>&1; echo "suite rc=$?"; tail -4 $O/suite_1gpu.log | cut -c1-300
+timeout 200 python tools/gemm_diag.py 2>&1 | grep "^{\"case" | cut -c1-260 > $O/gemm_bench.jsonl; cat $O/gemm_bench.jsonl
 KEEP="fused_dw G5m emu8_dw"
 cap() {  # case, kernel regex, launches to skip
   local c=$1 k=$2 s=$3
@@ -34,4 +37,5 @@ cap sumsq sumsq_kernel 3
 cap philox randn_kernel 3
 cap colsum colsum_partial 3
 cap coll_ar coll_kernel 3
+cap f32 gemm_tcgen05 3
 ls -la $O | head -60
