@@ -79,7 +79,7 @@ class CudaOps(TorchOps):
         if act == "relu":
             if self.relu_mask and N % 128 == 0:
                 # also emit the packed sign mask (1 bit/element): the backward reads 1/16 of the bytes of `a`
-                mask = torch.empty(T, N // 8, dtype=torch.uint8, device=x.device)
+                mask = nv.relu_mask_empty(T, N, x.device)
                 nv.gemm(x, nv.MAJOR_K, W, nv.MAJOR_K, a, T, N, K, nv.EPI_RELU_MASK, out2=mask, bias=b32, max_ctas=self.max_ctas)
                 return a, mask
             nv.gemm(x, nv.MAJOR_K, W, nv.MAJOR_K, a, T, N, K, nv.EPI_RELU, bias=b32, max_ctas=self.max_ctas)

@@ -174,6 +174,34 @@ def num_sms() -> int:
     return int(load().b200_num_sms())
 
 
+# --------------------------------------------------------------------------------------------- ReLU sign masks
+# The RELU_MASK / RELU_BWD_MASK epilogues exchange 1 bit per element in a tile-blocked layout (csrc/gemm_kernel.cuh): the 16
+# bytes of (row, 128-column chunk cc) sit at ((row // 128) * n_chunks + cc) * 2048 + (row % 128) * 16, so a warp's 32 rows
+# are 512 contiguous bytes.  The buffer is a uint8 tensor of shape [ceil(M/128)*128, n_chunks*16] (the bytes of a row-major
+# mask padded to whole tiles; only their ORDER differs).
+def relu_mask_empty(M: int, N: int, device) -> torch.Tensor:
+    return torch.empty((M + 127) // 128 * 128, (N + 127) // 128 * 16, dtype=torch.uint8, device=device)
+
+
+def unpack_relu_mask(mask: torch.Tensor, M: int, N: int) -> torch.Tensor:
+    """Blocked mask buffer -> bool ``[M, N]`` (tests, debugging)."""
+    tm, ncc = (M + 127) // 128, (N + 127) // 128
+    v = mask.reshape(-1)[: tm * ncc * 2048].view(tm, ncc, 128, 16)
+    bits = (v.unsqueeze(-1) >> torch.arange(8, device=mask.device, dtype=torch.uint8)) & 1
+    return bits.permute(0, 2, 1, 3, 4).reshape(tm * 128, ncc * 128)[:M, :N].bool()
+
+
+def pack_relu_mask(keep: torch.Tensor) -> torch.Tensor:
+    """bool ``[M, N]`` -> blocked mask buffer (tests)."""
+    M, N = keep.shape
+    tm, ncc = (M + 127) // 128, (N + 127) // 128
+    full = torch.zeros(tm * 128, ncc * 128, dtype=torch.bool, device=keep.device)
+    full[:M, :N] = keep
+    w = (1 << torch.arange(8, device=keep.device, dtype=torch.int32))
+    by = (full.view(tm, 128, ncc, 16, 8).int() * w).sum(-1).to(torch.uint8)          # [tm, 128, ncc, 16]
+    return by.permute(0, 2, 1, 3).contiguous().view(tm * 128, ncc * 16)
+
+
 # --------------------------------------------------------------------------------------------- GEMM
 def gemm_supported(M: int, N: int, K: int, *lds: int) -> bool:
     """Shapes the tcgen05 kernel accepts (TMA pitch and the 16-byte epilogue vectors need multiples of 8)."""

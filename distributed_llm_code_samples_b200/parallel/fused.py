@@ -747,7 +747,7 @@ class FusedMPTrainer:
         out = torch.empty(T, N, dtype=torch.bfloat16, device=self.device)
         peers = self.abuf.peers_at(self.abuf.offset_of(buf))
         if kind == "relu" and N % 128 == 0:
-            mask = torch.empty(T, N // 8, dtype=torch.uint8, device=self.device)
+            mask = nv.relu_mask_empty(T, N, self.device)
             self.gchan.gemm(peers, W, b_major, out, T, N, D, nv.EPI_RELU_MASK, out2=mask, bias=bias)
             return out, mask
         if kind == "relu":

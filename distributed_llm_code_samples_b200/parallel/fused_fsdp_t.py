@@ -105,7 +105,7 @@ class FusedFSDPGatherTrainer(FusedFSDPTrainer):
         out = torch.empty(M, N, dtype=torch.bfloat16, device=self.device)
         out2 = None
         if epi == nv.EPI_RELU_MASK:
-            out2 = torch.empty(M, N // 8, dtype=torch.uint8, device=self.device)
+            out2 = nv.relu_mask_empty(M, N, self.device)
         elif epi == nv.EPI_GELU:
             out2 = torch.empty_like(out)
         self.gchan.gemm(self._peers_of_weight(l, k, full), B, MN_, out, M, N, K, epi, aux=aux, out2=out2)

@@ -49,9 +49,11 @@ int b200_set_update_rounding(unsigned int seed);
  *   1 RELU       C = relu(acc + bias)                 5 ADD       C = acc + aux (+bias)
  *   2 GELU       C = gelu(acc+bias), C2 = acc+bias    6 SGD       C = C - alpha*acc   (in place on the weight)
  *   3 RELU_BWD   C = acc * (aux > 0)                  7 STORE_F32 C(fp32) = alpha*acc
- *   8 RELU_MASK      as RELU, and C2 (uint8 [M, ldc2 BYTES], ldc2 % 16 == 0) receives one sign bit per element
- *   9 RELU_BWD_MASK  C = acc where the bit in aux (that mask, ldaux in BYTES) is set, else 0 - the backward of
- *                    ReLU (:50-52) from 1 bit/element instead of re-reading the bf16 activation
+ *   8 RELU_MASK      as RELU, and C2 receives one sign bit per element (uint8 buffer, tile-blocked: the 16 bytes of
+ *                    (row, 128-column chunk cc) at ((row/128) * ceil(N/128) + cc) * 2048 + (row%128) * 16; size
+ *                    ceil(M/128)*128 rows x ceil(N/128)*16 bytes; ldc2 = bytes per row of that shape, % 16 == 0)
+ *   9 RELU_BWD_MASK  C = acc where the bit in aux (that mask, same layout, ldaux in BYTES) is set, else 0 - the backward
+ *                    of ReLU (:50-52) from 1 bit/element instead of re-reading the bf16 activation
  * Preconditions: 16-byte aligned bases; lda, ldb, ldc, ldaux, ldc2 and N multiples of 8 elements.
  * max_ctas: 0 = one CTA per SM; >0 caps the persistent grid (leaves SMs for a concurrent comm kernel). */
 #define B200_EPI_STORE 0

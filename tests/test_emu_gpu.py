@@ -236,7 +236,7 @@ def test_emu_gather_gemm_row_sharded(cuda_device, world, epi):
         out = [torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=cuda_device) for _ in range(world)]
         out2 = None
         if epi == "relu_mask":
-            out2 = [torch.zeros((M, N // 8), dtype=torch.uint8, device=cuda_device) for _ in range(world)]
+            out2 = [nv.relu_mask_empty(M, N, cuda_device).zero_() for _ in range(world)]
         elif epi == "gelu":
             out2 = [torch.empty((M, N), dtype=torch.bfloat16, device=cuda_device) for _ in range(world)]
         ch.gemm(bufs, nv.MAJOR_K, B, nv.MAJOR_K, out, M, N, K, kind, out2=out2)
@@ -248,8 +248,7 @@ def test_emu_gather_gemm_row_sharded(cuda_device, world, epi):
             ref = h if epi == "store" else (torch.relu(h) if epi == "relu_mask" else torch.nn.functional.gelu(h))
             assert _tile_err(out[r], ref) <= 1e-2, (it, r)
             if epi == "relu_mask":
-                bits = (out2[r].unsqueeze(-1) >> torch.arange(8, device=cuda_device, dtype=torch.uint8)) & 1
-                got = bits.reshape(M, N).bool()
+                got = nv.unpack_relu_mask(out2[r], M, N)
                 assert torch.equal(got, out[r] > 0), (it, r, "sign mask disagrees with the activation")
 
 

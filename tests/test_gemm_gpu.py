@@ -91,10 +91,11 @@ def test_relu_bitmask_epilogues(cuda_device, M, N, K):
     x, w = _rand((M, K), cuda_device, seed=31), _rand((N, K), cuda_device, 0.1, seed=32)
     ref = x.float() @ w.float().T
     a = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
-    mask = torch.zeros(M, N // 8, dtype=torch.uint8, device=cuda_device)
+    mask = nv.relu_mask_empty(M, N, cuda_device)
     nv.gemm(x, 0, w, 0, a, M, N, K, nv.EPI_RELU_MASK, out2=mask)
     _check(a, torch.relu(ref), K, "relu+mask")
-    bits = ((mask.unsqueeze(-1) >> torch.arange(8, device=cuda_device, dtype=torch.uint8)) & 1).reshape(M, N).bool()
+    bits = nv.unpack_relu_mask(mask, M, N)
+    assert torch.equal(nv.unpack_relu_mask(nv.pack_relu_mask(bits), M, N), bits)          # the helpers mirror the kernels' layout
     assert torch.equal(bits, a > 0)
     dy, w2 = _rand((M, K), cuda_device, seed=33), _rand((K, N), cuda_device, 0.1, seed=34)
     out = torch.empty(M, N, dtype=torch.bfloat16, device=cuda_device)
@@ -125,10 +126,10 @@ def test_gemm_benchmark_size(cuda_device, layout):
             if layout == "tn":
                 nv.gemm(a, 0, b, 0, out, M, N, K)
             else:
-                mask = torch.zeros(M, N // 8, dtype=torch.uint8, device=cuda_device)
+                mask = nv.relu_mask_empty(M, N, cuda_device)
                 nv.gemm(a, 0, b, 0, out, M, N, K, nv.EPI_RELU_MASK, out2=mask)
                 ref = torch.relu(ref)
-                bits = ((mask.unsqueeze(-1) >> torch.arange(8, device=cuda_device, dtype=torch.uint8)) & 1).reshape(M, N).bool()
+                bits = nv.unpack_relu_mask(mask, M, N)
                 assert torch.equal(bits, out > 0)
         elif layout in ("nn", "relu_bwd_mask"):
             a, b = _rand((M, K), cuda_device, seed=43), _rand((K, N), cuda_device, 0.1, seed=44)
@@ -137,8 +138,7 @@ def test_gemm_benchmark_size(cuda_device, layout):
                 nv.gemm(a, 0, b, 1, out, M, N, K)
             else:
                 keep = torch.rand(M, N, device=cuda_device) > 0.5
-                w = (1 << torch.arange(8, device=cuda_device, dtype=torch.int32))
-                mask = (keep.reshape(M, N // 8, 8).int() * w).sum(-1).to(torch.uint8)
+                mask = nv.pack_relu_mask(keep)
                 nv.gemm(a, 0, b, 1, out, M, N, K, nv.EPI_RELU_BWD_MASK, aux=mask)
                 ref = ref * keep
         else:

@@ -106,7 +106,7 @@ def case_ag(T, D, Fs, name):
     x.normal_(0, 1)
     w1 = (torch.randn(Fs, D, device=dev) * 0.02).to(torch.bfloat16)
     a = torch.empty(T, Fs, dtype=torch.bfloat16, device=dev)
-    mask = torch.empty(T, Fs // 8, dtype=torch.uint8, device=dev)
+    mask = nv.relu_mask_empty(T, Fs, dev)
     gch = GatherChannel(sw, T)
     coll = CollChannel(sw)
     peers = xb.peers_at(off)

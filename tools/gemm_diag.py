@@ -122,7 +122,7 @@ def bench(dev, which: str) -> None:
     y = torch.empty(T, D, dtype=torch.bfloat16, device=dev)
     dw1 = torch.empty(F, D, dtype=torch.bfloat16, device=dev)
     dw2 = torch.empty(D, F, dtype=torch.bfloat16, device=dev)
-    mask = torch.zeros(T, F // 8, dtype=torch.uint8, device=dev)
+    mask = nv.relu_mask_empty(T, F, dev)
     cases = [
         ("G1m h=relu(x@W1^T) TN + sign bitmask (the step's default)", lambda: nv.gemm(x, 0, w1, 0, h, T, F, D, nv.EPI_RELU_MASK, out2=mask), lambda: torch.relu(x @ w1.T), 2 * T * F * D),
         ("G5m da=dy@W2 NN + relu_bwd from bitmask (the step's default)", lambda: nv.gemm(dy, 0, w2, 1, h, T, F, D, nv.EPI_RELU_BWD_MASK, aux=mask), lambda: (dy @ w2).masked_fill_(a <= 0, 0), 2 * T * F * D),

@@ -38,7 +38,7 @@ fn = {
     "coll_ag": None,
 }[case]
 if case in ("G1m", "G5m"):
-    mask = torch.zeros(T, F // 8, dtype=torch.uint8, device=dev)
+    mask = nv.relu_mask_empty(T, F, dev)
     nv.gemm(x, 0, w1, 0, h, T, F, D, nv.EPI_RELU_MASK, out2=mask)
     fn = (lambda: nv.gemm(x, 0, w1, 0, h, T, F, D, nv.EPI_RELU_MASK, out2=mask)) if case == "G1m" else \
          (lambda: nv.gemm(dy, 0, w2, 1, h, T, F, D, nv.EPI_RELU_BWD_MASK, aux=mask))

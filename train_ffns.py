@@ -121,11 +121,18 @@ def main(argv=None) -> int:
                 print(f'saved {path}')
 
     if args.method == 0:   # compare DDP against FSDP (train_ffns.py:386-391)
+        worst_abs, worst_ulp = 0.0, 0.0
+        mant = 8 if cfg.dtype == 'bf16' else 24              # mantissa bits of the storage dtype
         for l in range(args.layers):
             for k in range(2):
                 a, b = fns_layers_params[1][l][k], fns_layers_params[2][l][k]
                 if not torch.allclose(a, b):
                     print(f"SoftAssertionError: L {l} ddp[{k}] {a} fsdp[{k}] {b}")
+                d = (a.double() - b.double()).abs()
+                worst_abs = max(worst_abs, d.max().item())
+                spacing = torch.exp2(torch.floor(torch.log2(a.double().abs().clamp_min(1e-30))) - (mant - 1))
+                worst_ulp = max(worst_ulp, (d / spacing).max().item())
+        print(f'DDP vs FSDP: max |difference| {worst_abs:.3e} = {worst_ulp:.2f} ulp of the {cfg.dtype} weights')
     return 0
 
 
