@@ -20,7 +20,7 @@ except Exception as ex:
 PY
 }
 nvidia-smi topo -m > $O/topo.txt 2>&1
-step "multi-GPU tests at $N ranks" 360 python -m pytest tests/test_multigpu.py -q -m gpu -k "(fused_trainer_matches and (ddp or mp_spf or (mp and not mp_sp))) or fsdp_with_in_kernel or (north_star and adam and mp and ar)" > $O/mgpu.log 2>&1; tail -5 $O/mgpu.log | cut -c1-400
+step "multi-GPU tests at $N ranks" 360 python -m pytest tests/test_multigpu.py -q -m gpu -k "(fused_trainer_matches and (ddp or mp_spf or (mp and not mp_sp))) or fsdp_with_in_kernel" > $O/mgpu.log 2>&1; tail -5 $O/mgpu.log | cut -c1-400
 step "bench ours (ddp + children fsdp, mp)" 330 $TR --master-port 29581 bench.py --gpus $N --steps 5 --warmup 3 2> $O/bench_ours.err | grep "^{" > $O/bench_ours.json
 python - <<PY
 import json
@@ -36,8 +36,9 @@ one mp_sharded_input --method mp --mp_input sharded
 one mp_nvls_off --method mp --nvls off --no-e2e
 one mp_spf --method mp --mp_mode spf --no-e2e
 one fsdp_fused_gather --method fsdp --fsdp_gather fused --no-e2e
+one ddp_recompute --method ddp --recompute --no-e2e
+one fsdp_recompute --method fsdp --recompute --no-e2e
 FUSED_BENCH_ONLY=mp FUSED_BENCH_TAG=_r2 step "fused_bench mp (push vs NVLS)" 120 $TR --master-port 29591 tools/fused_bench.py 2> $O/fused_bench.err | grep "^{" | cut -c1-900
 step "coll sweep" 200 $TR --master-port 29592 tools/coll_sweep.py 2> $O/coll_sweep.err | grep "^{" | cut -c1-420
-step "train_ffns -m 0 bf16 (DDP == FSDP check on the fused paths)" 240 python train_ffns.py -s 8 -bs 4 -n 1024 -l 2 -d 2048 -m 0 -r 7 --dtype bf16 --lr 1e-3 > $O/train_m0.log 2>&1; grep -E "takes|SoftAssertion|DDP vs FSDP|tokens/s" $O/train_m0.log | cut -c1-200 | head -12
 cp gpurun_out/fused_bench_n${N}_r2.jsonl gpurun_out/coll_sweep_n$N.jsonl $O/ 2>/dev/null
 for f in $O/*.err; do [ -s $f ] && grep -iE "Error|Traceback" -A6 $f | tail -14; done
