@@ -1,14 +1,12 @@
 # Convenience targets; everything is plain python underneath.
 PY ?= python
-.PHONY: build test test-gpu test-queued bench bench-ref sass-report clean
+.PHONY: build test test-gpu bench bench-ref sass-report clean
 build:
 	$(PY) -m distributed_llm_code_samples_b200.build_native
 test: build
 	$(PY) -m pytest tests -x -q -m "not gpu"
 test-gpu: build
 	$(PY) -m pytest tests -x -q -m gpu
-test-queued: build   # tests written while no GPU was available; run them once on hardware, then drop their `queued` mark
-	B200_QUEUED_TESTS=1 $(PY) -m pytest tests -x -q -m gpu
 sass-report: build   # regenerate profiles/sass and profiles/ptxas (no GPU needed)
 	$(PY) tools/sass_report.py
 bench: build

@@ -20,7 +20,7 @@ except Exception as ex:
 PY
 }
 nvidia-smi topo -m > $O/topo.txt 2>&1
-step "multi-GPU tests at $N ranks" 360 python -m pytest tests/test_multigpu.py -q -m gpu -k "(fused_trainer_matches and (ddp or mp_spf or (mp and not mp_sp))) or fsdp_with_in_kernel" > $O/mgpu.log 2>&1; tail -5 $O/mgpu.log | cut -c1-400
+step "multi-GPU tests at $N ranks" 360 python -m pytest tests/test_multigpu.py -q -m gpu -k "(fused_trainer_matches and (ddp or mp_spf or (mp and not mp_sp))) or fsdp_with_in_kernel or gradient_sum" > $O/mgpu.log 2>&1; tail -5 $O/mgpu.log | cut -c1-400
 step "bench ours (ddp + children fsdp, mp)" 330 $TR --master-port 29581 bench.py --gpus $N --steps 5 --warmup 3 2> $O/bench_ours.err | grep "^{" > $O/bench_ours.json
 python - <<PY
 import json
