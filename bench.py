@@ -277,8 +277,11 @@ def run_ours(args):
             continue
         k = len(also)
         rm, rr = ("ddp", True) if m == "ddp_recompute" else (m, args.recompute)
-        r = also_in_child(args, "ours", rm, k, rr)
-        also[m] = ours_one(args, rm, rr) if r == "fallback" else r
+        try:
+            r = also_in_child(args, "ours", rm, k, rr)
+            also[m] = ours_one(args, rm, rr) if r == "fallback" else r
+        except Exception as ex:  # noqa: BLE001 - an extra strategy must never cost the headline line
+            also[m] = {"error": f"{type(ex).__name__}: {ex}"[:400]}
     if also:
         rec["also"] = also
     if rank == 0:
@@ -406,8 +409,11 @@ def run_reference(args):
             also[m] = {"same_run_as": "ddp", "value": rec["value"], "unit": rec["unit"], "ms_per_step": rec["ms_per_step"],
                        "e2e": rec["e2e"], "clocks": rec["clocks"], "gpu_launches": 0, "config": rec["config"]}
             continue
-        r = also_in_child(args, "reference", m, len(also) + 10)
-        also[m] = reference_one(args, ref, m) if r == "fallback" else r
+        try:
+            r = also_in_child(args, "reference", m, len(also) + 10)
+            also[m] = reference_one(args, ref, m) if r == "fallback" else r
+        except Exception as ex:  # noqa: BLE001
+            also[m] = {"error": f"{type(ex).__name__}: {ex}"[:400]}
     if also:
         rec["also"] = also
     if rank == 0:

@@ -16,6 +16,7 @@
 #include <cerrno>
 #include <cstring>
 #include <sys/socket.h>
+#include <sys/time.h>
 #include <sys/un.h>
 #include <unistd.h>
 
@@ -51,6 +52,9 @@ extern "C" int b200_fd_listen(const char* path) {
         close(s);
         return B200_ERR_STATE;
     }
+    // a peer that failed before sending must not leave this rank blocked in recvmsg for ever: b200_fd_recv gives up after 60 s
+    timeval tv{60, 0};
+    setsockopt(s, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof(tv));
     return s;
 }
 

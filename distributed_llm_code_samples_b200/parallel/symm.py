@@ -125,11 +125,23 @@ class SymmWorld:
         """Collective: every rank must call with the same size in the same order.  ``multicast=True`` (where the box has
         NVLS) returns a cuMem VMM block bound to a multicast object (``.mc_ptr``), else a cudaMalloc + CUDA-IPC block."""
         nbytes = (nbytes + 255) // 256 * 256
+        b = None
         if multicast and self.multicast_supported():
             from .vmm import VmmBuffer
             self._vmm_count += 1
-            b = VmmBuffer(self.rank, self.world, self.device, nbytes, multicast=True, group=self.group, tag=f"sw{self._vmm_count}_")
-        else:
+            err = None
+            try:
+                b = VmmBuffer(self.rank, self.world, self.device, nbytes, multicast=True, group=self.group, tag=f"sw{self._vmm_count}_")
+            except Exception as e:  # noqa: BLE001 - a box without working NVLS falls back to IPC blocks, on EVERY rank
+                err = e
+            ok = torch.tensor([0 if (err is not None or b is None or not b.mc_ptr) else 1], device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+            if not bool(ok.item()):
+                import warnings
+                warnings.warn(f"NVLS multicast block unavailable ({err}); falling back to CUDA-IPC symmetric memory")
+                self._mc_ok = False
+                b = None
+        if b is None:
             b = SymmBuffer(self, nbytes)
         self.buffers.append(b)
         return b
