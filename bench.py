@@ -43,8 +43,8 @@ def parse_args():
     ap.add_argument("--recompute", action="store_true", help="reference-style activation recompute in backward")
     ap.add_argument("--mp_mode", default="ar", choices=["ar", "sp", "spf"],
                     help="MP form: ar = the reference's all-reduce form (default, the benchmarked one); sp / spf = sequence-parallel variants")
-    ap.add_argument("--fsdp_gather", default="dma", choices=["dma", "fused"])
-    ap.add_argument("--mp_input", default="full", choices=["full", "sharded"])
+    ap.add_argument("--fsdp_gather", default="fused", choices=["dma", "fused"])
+    ap.add_argument("--mp_input", default="sharded", choices=["full", "sharded"])
     ap.add_argument("--nvls", default="auto", choices=["auto", "off"])
     ap.add_argument("--also", default="auto",
                     help="extra strategies measured in the same process and reported under `also` (comma list of fsdp, mp, "
@@ -254,7 +254,8 @@ def ours_one(args, method, recompute):
               "gemms_per_block_step": 7 if recompute else 6,
               "comm": getattr(eng.trainer, "comm_name", "nccl" if world > 1 else "none"), "ops": args.ops,
               "torch_fallback_ops": getattr(eng.ops, "fallbacks", None),
-              "peak_mem_gib": round(torch.cuda.max_memory_allocated(dev) / 2 ** 30, 2)}
+              "peak_mem_gib": round(torch.cuda.max_memory_allocated(dev) / 2 ** 30, 2),     # torch's allocator only
+              "device_mem_used_gib": round((lambda fr_to: (fr_to[1] - fr_to[0]) / 2 ** 30)(torch.cuda.mem_get_info(dev)), 2)}   # + symmetric blocks, NCCL, context
     rec = record("ours", method, world, args, value, ms, clocks, e2e, launches,
                  base_config(method if world > 1 else "single", world, d, f, l, args, eng.tokens_per_step_global), detail)
     eng.close()
@@ -377,7 +378,8 @@ def reference_one(args, ref, method):
               "comm": "NCCL via torch.distributed" if world > 1 else "none", "ops": "cuBLAS + ATen (torch)",
               "note": "unmodified baseline/_ref/train_ffns.py per-rank function; mock_data yields the bf16 benchmark batches",
               "final_param_finite": bool(torch.isfinite(state["params"][-1][0].float()).all().item()),
-              "peak_mem_gib": round(torch.cuda.max_memory_allocated(dev) / 2 ** 30, 2)}
+              "peak_mem_gib": round(torch.cuda.max_memory_allocated(dev) / 2 ** 30, 2),
+              "device_mem_used_gib": round((lambda fr_to: (fr_to[1] - fr_to[0]) / 2 ** 30)(torch.cuda.mem_get_info(dev)), 2)}
     rec = record("reference", method, world, args, value, ms, clocks, e2e, 0,
                  base_config(method if world > 1 else "single", world, d, f, l, args, per_step_tokens), detail)
     del state, dev_pool, host_pool

@@ -165,6 +165,35 @@ __global__ void __launch_bounds__(EW_THREADS) colsum_final_kernel(float* out, co
     out[c] = t;
 }
 
+// ------------------------------------------------------------------ transpose (bf16 [R, C] -> [C, R])
+// 64 x 64 tiles through shared memory: 128-byte row segments on both the read and the write side.  Used where a trainer
+// keeps activations feature-major (FSDP with the parameter all-gather inside the GEMMs, parallel/fused_fsdp_t.py).
+__global__ void __launch_bounds__(256) transpose_kernel(__nv_bfloat16* out, long long ldo, const __nv_bfloat16* in, long long ldi, int R, int C) {
+    __shared__ __nv_bfloat16 tile[64][66];
+    const int r0 = blockIdx.y * 64, c0 = blockIdx.x * 64;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;            // 32 x 8
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int r = r0 + ty + i * 8, c = c0 + tx * 2;
+        __nv_bfloat162 v = __floats2bfloat162_rn(0.f, 0.f);
+        if (r < R && c + 1 < C) v = *reinterpret_cast<const __nv_bfloat162*>(in + (long long)r * ldi + c);
+        else if (r < R && c < C) v.x = in[(long long)r * ldi + c];
+        tile[ty + i * 8][tx * 2] = v.x;
+        tile[ty + i * 8][tx * 2 + 1] = v.y;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = c0 + ty + i * 8, r = r0 + tx * 2;                // output row = input column
+        if (c >= C) continue;
+        __nv_bfloat162 v;
+        v.x = tile[tx * 2][ty + i * 8];
+        v.y = tile[tx * 2 + 1][ty + i * 8];
+        if (r + 1 < R) *reinterpret_cast<__nv_bfloat162*>(out + (long long)c * ldo + r) = v;
+        else if (r < R) out[(long long)c * ldo + r] = v.x;
+    }
+}
+
 // ------------------------------------------------------------------ out[t, :] = bias (+ residual[t, :])
 // Pre-fills the output of a fused row-parallel GEMM + all-reduce whose in-place mode then adds the cross-rank sum.
 __global__ void __launch_bounds__(EW_THREADS) bias_rows_kernel(__nv_bfloat16* out, long long ldo, const __nv_bfloat16* res, long long ldr,
@@ -415,6 +444,16 @@ extern "C" int b200_colsum_bf16(float* out, const void* x, long long ld, int T, 
     if (int rc = check_cuda(cudaGetLastError(), "colsum partial launch")) return rc;
     colsum_final_kernel<<<(N + EW_THREADS - 1) / EW_THREADS, EW_THREADS, 0, ST(stream)>>>(out, reinterpret_cast<const float*>(scratch), N, chunks, accumulate);
     return check_cuda(cudaGetLastError(), "colsum final launch");
+}
+
+extern "C" int b200_transpose_bf16(void* out, long long ldo, const void* in, long long ldi, int R, int C, void* stream) {
+    if (R <= 0 || C <= 0) return 0;
+    if (out == nullptr || in == nullptr || (reinterpret_cast<uintptr_t>(out) & 3) || (reinterpret_cast<uintptr_t>(in) & 3) || (ldo % 2) || (ldi % 2) || ldo < R || ldi < C) {
+        set_last_error("transpose: 4-byte aligned pointers, even pitches, ldo >= R and ldi >= C required"); return B200_ERR_ARG;
+    }
+    dim3 grid((C + 63) / 64, (R + 63) / 64);
+    transpose_kernel<<<grid, 256, 0, ST(stream)>>>(reinterpret_cast<__nv_bfloat16*>(out), ldo, reinterpret_cast<const __nv_bfloat16*>(in), ldi, R, C);
+    return check_cuda(cudaGetLastError(), "transpose launch");
 }
 
 extern "C" int b200_bias_rows_bf16(void* out, long long ldo, const void* residual, long long ldr, const float* bias, int T, int N, void* stream) {

@@ -52,10 +52,12 @@ class TrainConfig:
     comm: str = "auto"                     # auto | fused (collective inside the GEMM) | native (peer-memory collectives) | nccl
     recompute: bool = False                # reference recomputes h in backward (:63); we keep it by default
     mp_mode: str = "ar"                    # ar = reference all-reduce form (:303,:309); sp = AG/RS sequence-parallel; spf = sp with the AG inside the GEMM
-    fsdp_gather: str = "dma"               # fused FSDP parameter all-gather: dma = copy-engine prefetch one layer ahead (:236-249);
-                                           # fused = inside the consuming GEMMs, forward and backward (parallel/fused_fsdp_t.py)
-    mp_input: str = "full"                 # Engine.train under MP all-reduce form: full = every rank stages the whole batch (:294, :324);
-                                           # sharded = 1/world over PCIe + NVLink all-gather (ShardedPrefetcher)
+    fsdp_gather: str = "fused"               # fused FSDP parameter all-gather: fused = inside the consuming GEMMs, forward and backward
+                                           # (parallel/fused_fsdp_t.py; default: ties the prefetch at 8 GPUs, 325.4 vs 325.0 ms/step);
+                                           # dma = copy-engine prefetch one layer ahead (:236-249); biases need dma (chosen automatically)
+    mp_input: str = "sharded"                 # Engine.train under MP all-reduce form: sharded = 1/world over PCIe + NVLink all-gather
+                                           # (ShardedPrefetcher; default: 87.4 vs 96.6 ms/step end to end at 8 GPUs); full = every
+                                           # rank stages the whole batch like the reference (:294, :324)
     stochastic_rounding: bool = False      # bf16 weights have no fp32 master copy: round optimizer updates stochastically so that
                                            # updates far below a bf16 ulp (the reference's LR = 1e-5, :29) still train in expectation
     nvls: str = "auto"                     # fused MP all-reduce: auto = sum inside the NVSwitch where the box has NVLS; off = peer pushes

@@ -88,7 +88,8 @@ class Engine:
             ts = self.cfg.tokens // self.world
             rows = slice(self.rank * ts, (self.rank + 1) * ts)
         sw = getattr(self.trainer, "sw", None)
-        if self.method == "mp" and self.world > 1 and rows is None and sw is not None and self.cfg.mp_input == "sharded":
+        if self.method == "mp" and self.world > 1 and rows is None and sw is not None and self.cfg.mp_input == "sharded" \
+                and self.cfg.tokens % self.world == 0:
             # all-reduce form: every rank needs the whole batch - stage 1/world of it over PCIe, gather the rest over NVLink
             pf = ShardedPrefetcher(host_batches, self.device, sw, self.rank, self.world)
         else:

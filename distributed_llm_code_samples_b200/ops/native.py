@@ -127,6 +127,7 @@ def _optional_declare(lib) -> None:
         "b200_gather_gemm_bf16": ([pp, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, pp, vp, i, i, u, i, vp], i),
         "b200_debug_gather_chunk": ([i, i, i, i, ll, C.POINTER(ll)], i),
         "b200_fused_config": ([i, i], i),
+        "b200_transpose_bf16": ([vp, ll, vp, ll, i, i, vp], i),
         "b200_split_f32": ([vp, vp, ll, i, ll, vp], i),
         "b200_gemm_f32": ([vp, ll, i, vp, ll, i, vp, ll, i, i, i, i, vp, ll, vp, ll, vp, f, i, vp], i),
         "b200_set_update_rounding": ([u], i),
@@ -315,6 +316,17 @@ def bias_rows_(out: torch.Tensor, bias: Optional[torch.Tensor], residual: Option
     T, N = out.shape
     _check(load().b200_bias_rows_bf16(out.data_ptr(), out.stride(0), _ptr(residual), residual.stride(0) if residual is not None else 0,
                                       _ptr(bias), T, N, _stream()), "b200_bias_rows_bf16")
+    launch_count += 1
+    return out
+
+
+def transpose(x: torch.Tensor) -> torch.Tensor:
+    """Contiguous ``x.T`` of a bf16 matrix on the native tiled-transpose kernel."""
+    global launch_count
+    assert x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
+    R, Cc = x.shape
+    out = torch.empty(Cc, R, dtype=torch.bfloat16, device=x.device)
+    _check(load().b200_transpose_bf16(out.data_ptr(), out.stride(0), x.data_ptr(), x.stride(0), R, Cc, _stream()), "b200_transpose_bf16")
     launch_count += 1
     return out
 

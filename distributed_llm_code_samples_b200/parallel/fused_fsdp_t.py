@@ -41,11 +41,12 @@ def fsdp_t_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
       ``B`` is ``[K, N]`` (MN-major); returns ``(out [rows(W), N], out2)`` and leaves the full ``W`` for the backward pass
     * ``t.bwd_w_gemm(l, k, B, N, epi, aux)``   ``epi(W[l][k]^T @ B)``: ``W`` read MN-major, sharded along the contracted
       dimension; gathered in the kernel unless it is still complete from the forward pass; returns ``out [cols(W), N]``
+    * ``t.transpose(x)``   contiguous ``x.T`` (native tiled transpose on the GPU)
     * ``t.update(l, k, A, B)``   ``W[l][k] shard -= lr * (rows of A @ B^T summed over ranks)``, A ``[M, T]``, B ``[N, T]``
     """
     act, residual, L = t.opts.activation, t.opts.residual, t.L
     T = x.shape[0]
-    xT = x.t().contiguous()                                               # [D, T]
+    xT = t.transpose(x)                                                   # [D, T]
     saved = []
     for l in range(L):
         fwd = {"relu": nv.EPI_RELU_MASK if T % 128 == 0 else nv.EPI_RELU, "gelu": nv.EPI_GELU}[act]
@@ -55,8 +56,8 @@ def fsdp_t_step(t, x: torch.Tensor, dloss_dx: torch.Tensor) -> torch.Tensor:
         yT, _ = t.gather_w_gemm(l, 1, aT, T, nv.EPI_ADD if residual else nv.EPI_STORE, xT if residual else None)   # [D, T]
         saved.append((xT, aT, aux))
         xT = yT
-    y = xT.t().contiguous()
-    dT = dloss_dx.t().contiguous()                                        # [D, T]
+    y = t.transpose(xT)
+    dT = t.transpose(dloss_dx)                                            # [D, T]
     for i in reversed(range(L)):
         xin, aT, aux = saved[i]
         bwd = (nv.EPI_RELU_BWD_MASK if aux.dtype == torch.uint8 else nv.EPI_RELU_BWD) if act == "relu" else nv.EPI_GELU_BWD
@@ -122,6 +123,9 @@ class FusedFSDPGatherTrainer(FusedFSDPTrainer):
         full[self.rank * rows:(self.rank + 1) * rows].copy_(sh)
         self.gchan.gemm(self._peers_of_weight(l, k, full), B, MN_, out, M, N, Kd, epi, aux=aux, a_major=MN_)
         return out
+
+    def transpose(self, x: torch.Tensor) -> torch.Tensor:
+        return nv.transpose(x) if (x.is_cuda and x.dtype == torch.bfloat16 and x.stride(1) == 1 and x.stride(0) % 2 == 0) else x.t().contiguous()
 
     def update(self, l: int, k: int, A: torch.Tensor, B: torch.Tensor) -> None:
         M, T = A.shape

@@ -102,6 +102,9 @@ int b200_colsum_bf16(float* out, const void* x, long long ld, int T, int N, int 
  * in-place mode (op 1, alpha = -1) then adds the cross-rank sum - how bias and residual reach the fused MP kernels.
  * bias (fp32 [N]) and residual (bf16) may each be NULL. */
 int b200_bias_rows_bf16(void* out, long long ldo, const void* residual, long long ldr, const float* bias, int T, int N, void* stream);
+/* out[c, r] = in[r, c] for a bf16 [R, C] matrix (pitches in elements, even).  Feature-major activations of the FSDP trainer
+ * whose parameter all-gather runs inside the GEMMs (the weight is then the gathered A operand).  No reference counterpart. */
+int b200_transpose_bf16(void* out, long long ldo, const void* in, long long ldi, int R, int C, void* stream);
 /* out = relu(x) (:47-48) and dy = dy * (x > 0) in place (:50-52), standalone (unfused) forms. */
 int b200_relu_bf16(void* out, const void* x, long long n, void* stream);
 int b200_relu_bwd_bf16(void* dy, const void* x, long long n, void* stream);

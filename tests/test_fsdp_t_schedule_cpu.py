@@ -63,6 +63,9 @@ class _GlooFsdpT:
         W = self._full(l, k)                   # storage [K, M], read MN-major
         return _gemm(W, nv.MAJOR_MN, B, nv.MAJOR_MN, W.shape[1], N, W.shape[0], epi, aux)[0]
 
+    def transpose(self, x):
+        return x.t().contiguous()
+
     def update(self, l, k, A, B):
         G, _ = _gemm(A, nv.MAJOR_K, B, nv.MAJOR_K, A.shape[0], B.shape[0], A.shape[1], nv.EPI_STORE)
         dist.all_reduce(G)

@@ -362,3 +362,11 @@ def test_gemm_f32_epilogues(cuda_device):
     close(wgt, w0 - 0.05 * ref, "sgd")
     nv.gemm_f32(X, 0, W, 0, out, M, N, K, nv.EPI_STORE, alpha=0.5)
     close(out, 0.5 * ref, "store*alpha")
+
+
+@pytest.mark.parametrize("R,C", [(16384, 4096), (200, 264), (65, 2), (64, 64)])
+def test_native_transpose(cuda_device, R, C):
+    x = _rand((R, C), cuda_device, seed=51)
+    assert torch.equal(nv.transpose(x), x.t().contiguous())
+    xs = _rand((R, 2 * C + 4), cuda_device, seed=52)[:, 2:C + 2]                  # strided view with an odd-ish offset
+    assert torch.equal(nv.transpose(xs), xs.t().contiguous())

@@ -184,7 +184,8 @@ def test_fused_trainer_matches_nccl_trainer(method):
     lp, seeds = _init()
     T = 512
     fn = {"ddp": api.train_ddp, "fsdp": api.train_fsdp, "mp": api.train_tp, "mp_sp": api.train_tp, "mp_spf": api.train_tp}[method]
-    extra = {"mp_sp": {"mp_mode": "sp"}, "mp_spf": {"mp_mode": "spf"}}.get(method, {})
+    # (fsdp: the copy-engine prefetch form here; the in-kernel gather, the default, has its own test below)
+    extra = {"mp_sp": {"mp_mode": "sp"}, "mp_spf": {"mp_mode": "spf"}, "fsdp": {"fsdp_gather": "dma"}}.get(method, {})
     if method == "mp_spf":
         T = max(T, 256 * WORLD)    # the all-gather+GEMM kernel needs whole 128-row blocks per token shard (two here)
     if method.startswith("mp"):

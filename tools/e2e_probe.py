@@ -21,8 +21,8 @@ from distributed_llm_code_samples_b200.utils.data import PinnedPrefetcher  # noq
 ap = argparse.ArgumentParser()
 ap.add_argument("--method", default="fsdp")
 ap.add_argument("--steps", type=int, default=4)
-ap.add_argument("--mp_input", default="full")
-ap.add_argument("--fsdp_gather", default="dma")
+ap.add_argument("--mp_input", default="sharded")
+ap.add_argument("--fsdp_gather", default="fused")
 a = ap.parse_args()
 rank, world, local = B.rank_world()
 bargs = argparse.Namespace(method=a.method, model_size=None, ffn_dim=None, layers=None)

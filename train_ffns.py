@@ -48,8 +48,8 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument('--comm', default='auto', choices=['auto', 'fused', 'native', 'nccl'])
     p.add_argument('--recompute', action='store_true')
     p.add_argument('--mp_mode', default='ar', choices=['ar', 'sp', 'spf'])
-    p.add_argument('--fsdp_gather', default='dma', choices=['dma', 'fused'], help='fused FSDP: copy-engine prefetch, or all-gather inside the consuming GEMMs')
-    p.add_argument('--mp_input', default='full', choices=['full', 'sharded'])
+    p.add_argument('--fsdp_gather', default='fused', choices=['dma', 'fused'], help='fused FSDP: copy-engine prefetch, or all-gather inside the consuming GEMMs')
+    p.add_argument('--mp_input', default='sharded', choices=['full', 'sharded'])
     p.add_argument('--stochastic_rounding', action='store_true', help='bf16: round optimizer updates stochastically (no fp32 master weights)')
     p.add_argument('--nvls', default='auto', choices=['auto', 'off'], help='fused MP all-reduce: sum inside the NVSwitch (multimem) where available')
     p.add_argument('--master_port', type=int, default=29500)
