@@ -325,6 +325,7 @@ def transpose(x: torch.Tensor) -> torch.Tensor:
     global launch_count
     assert x.dtype == torch.bfloat16 and x.dim() == 2 and x.stride(1) == 1
     R, Cc = x.shape
+    assert R % 2 == 0 and x.stride(0) % 2 == 0, "transpose: even row count and pitch (4-byte paired accesses)"
     out = torch.empty(Cc, R, dtype=torch.bfloat16, device=x.device)
     _check(load().b200_transpose_bf16(out.data_ptr(), out.stride(0), x.data_ptr(), x.stride(0), R, Cc, _stream()), "b200_transpose_bf16")
     launch_count += 1

@@ -125,7 +125,7 @@ class FusedFSDPGatherTrainer(FusedFSDPTrainer):
         return out
 
     def transpose(self, x: torch.Tensor) -> torch.Tensor:
-        return nv.transpose(x) if (x.is_cuda and x.dtype == torch.bfloat16 and x.stride(1) == 1 and x.stride(0) % 2 == 0) else x.t().contiguous()
+        return nv.transpose(x) if (x.is_cuda and x.dtype == torch.bfloat16 and x.stride(1) == 1 and x.stride(0) % 2 == 0 and x.shape[0] % 2 == 0) else x.t().contiguous()
 
     def update(self, l: int, k: int, A: torch.Tensor, B: torch.Tensor) -> None:
         M, T = A.shape
