@@ -5,9 +5,10 @@
 // x0 = bf16(x), x1 = bf16(x - x0), x2 = bf16(x - x0 - x1)   (3 x 8 = 24 mantissa bits: exact up to the last fp32 ulp),
 // and the product is accumulated from the six plane products of weight >= 2^-16, smallest first, in the fp32 TMEM
 // accumulator:  A.B ~= A1.B1 + A0.B2 + A2.B0 + A0.B1 + A1.B0 + A0.B0.
-// bf16 x bf16 products are exact in fp32, so the only roundings are the accumulator's - which truncates on each of the
-// 6 * K / 16 accumulation steps (measured: within 4e-6 of sum |a||b| at K = 2048; cuBLAS's fp32 FMA chain ~1e-7, TF32 ~5e-4,
-// bf16 ~4e-3) - at 6x the bf16 MMA work, ~5x the speed of cuBLAS's fp32 GEMM on this part.  The mainloop is the ordinary one (gemm_kernel.cuh) walked
+// bf16 x bf16 products are exact in fp32, so the only roundings are the accumulator's (measured, tools/f32_probe.py: within
+// 1.6e-7 of sum |a||b| at K = 256; a three-block forward within 2.6e-6 of its scale against cuBLAS fp32's ~7e-7; TF32 would
+// give ~5e-4, bf16 ~4e-3) - at 6x the bf16 MMA work, ~5x the speed of cuBLAS's fp32 GEMM on this part.
+// The mainloop is the ordinary one (gemm_kernel.cuh) walked
 // six times over plane-shifted TMA coordinates (Epi::PRODUCTS = 6); the epilogues below are the fp32 forms of LocalEpi.
 #include "gemm_kernel.cuh"
 #include "../include/b200ffn.h"

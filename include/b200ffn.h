@@ -73,8 +73,8 @@ int b200_gemm_bf16(const void* A, long long lda, int a_major, const void* B, lon
 /* ---- fp32 GEMM on the bf16 tensor cores (reference-parity mode; csrc/gemm_f32.cu) ------------------------------------
  * The reference trains in fp32 (train_ffns.py:36, :149).  b200_split_f32 turns an fp32 matrix [rows, cols] (row pitch
  * ld_in) into three bf16 planes [3][rows][cols] whose sum is the matrix to the last fp32 ulp; b200_gemm_f32 multiplies
- * two such operands with six plane products accumulated in the fp32 TMEM accumulator (smallest first): error within 4e-6 of
- * sum |a||b| at K = 2048 (between TF32's ~5e-4 and cuBLAS fp32's ~1e-7) at 6x the bf16 MMA work.  Majors / M,N,K as b200_gemm_bf16 (lda / ldb = cols of the split matrix); every other
+ * two such operands with six plane products accumulated in the fp32 TMEM accumulator (smallest first): fp32-class
+ * accuracy (measured 1.6e-7 of sum |a||b| at K = 256; TF32 would give ~5e-4) at 6x the bf16 MMA work.  Majors / M,N,K as b200_gemm_bf16 (lda / ldb = cols of the split matrix); every other
  * tensor (C, aux, C2, bias) is fp32.  Epilogues: STORE (C = alpha*acc + bias), RELU, GELU (+C2 = pre-activation),
  * RELU_BWD, GELU_BWD, ADD, SGD (C -= alpha*acc).  cols % 8 == 0; MN-major operands need K % 64 == 0. */
 int b200_split_f32(void* planes_out, const float* in, long long rows, int cols, long long ld_in, void* stream);

@@ -104,28 +104,29 @@ def test_fp32_parity_mode_runs_on_native_kernels(cuda_device, act, residual):
     o64 = SingleTrainer(get_ops("torch", cuda_device), cfg, [[p.to(cuda_device, torch.float64) for p in l] for l in lp])
     prev = torch.backends.cuda.matmul.allow_tf32
     torch.backends.cuda.matmul.allow_tf32 = False
-    try:
-        xb, dyb = x.to(cuda_device), dy.to(cuda_device)
-        for _ in range(2):
-            y = nat.step(xb, dyb)
-            yo = ora.step(xb, dyb)
-            y64 = o64.step(xb.double(), dyb.double())
-        torch.cuda.synchronize()
-    finally:
-        torch.backends.cuda.matmul.allow_tf32 = prev
-    assert nat.ops.fallbacks == 0, "fp32 mode fell back to PyTorch ops"
 
     def err(t, ref):
         return ((t.double() - ref).abs().max() / ref.abs().max()).item()
 
-    # Accuracy class, measured on B200: after two 3-block steps the output is within 4e-6 of its scale and every weight
-    # within 6e-5 of its own (cuBLAS fp32: 1e-6 / 1e-7; a TF32 GEMM would sit near 5e-4, bf16 near 4e-3).  The operands
-    # lose nothing (3 x 8 mantissa bits); what is left is the tensor core's fp32 accumulator, which truncates on every one
-    # of the 6 * K / 16 accumulation steps where cuBLAS's FMA chain rounds to nearest.
-    assert err(y, y64) < 2e-5, (err(y, y64), err(yo, y64))
-    for a, b, c in zip(nat.params, ora.params, o64.params):
-        for p, q, r in zip(a, b, c):
-            assert err(p, r) < 2e-4, (err(p, r), err(q, r))
+    try:
+        xb, dyb = x.to(cuda_device), dy.to(cuda_device)
+        y, yo, y64 = nat.step(xb, dyb), ora.step(xb, dyb), o64.step(xb.double(), dyb.double())
+        torch.cuda.synchronize()
+        assert nat.ops.fallbacks == 0, "fp32 mode fell back to PyTorch ops"
+        # Measured on B200 (tools/f32_probe.py): output within 2.6e-6 of its scale after three blocks (cuBLAS fp32: ~7e-7), every
+        # weight within 1.5e-7 of its own after the step (cuBLAS: ~1e-7); a TF32 GEMM would sit near 5e-4, bf16 near 4e-3.
+        assert err(y, y64) <= 6 * err(yo, y64) + 2e-6, (err(y, y64), err(yo, y64))
+        for a, b, c in zip(nat.params, ora.params, o64.params):
+            for p, q, r in zip(a, b, c):
+                assert err(p, r) <= 6 * err(q, r) + 1e-6, (err(p, r), err(q, r))
+        # A second step stays finite and close.  (Weights are not compared after it: by then a pre-activation within 1e-6 of
+        # zero can take the other ReLU branch than the fp64 run - one such flip moves a whole weight row by ~5e-4 of the
+        # weight scale.  That is a property of comparing ANY two fp32 runs of a ReLU net, not of these kernels.)
+        y2, y264 = nat.step(xb, dyb), o64.step(xb.double(), dyb.double())
+        torch.cuda.synchronize()
+        assert torch.isfinite(y2).all() and err(y2, y264) < 1e-4
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
 
 
 def test_smoke_entry(cuda_device):
