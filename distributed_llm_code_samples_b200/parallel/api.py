@@ -154,10 +154,19 @@ def _rank_main(rank: int, world: int, device: torch.device, method: str, cfg_dic
                     step(x, dy)
                     if (k + 1) % cfg.save_every == 0:                # periodic checkpoint: full, unsharded layout
                         full = trainer.full_params()                 # collective on every rank
+                        opt_sd = {"kind": cfg.optimizer, "t": k + 1}
+                        if opt_io is not None:                       # Adam: every rank exports its pieces, then rank 0 saves
+                            from .opt_state import export_state
+                            opt_sd["t"] = export_state(method if world > 1 else "single", trainer, comm, opt_io["m_out"], opt_io["v_out"])
+                            comm.barrier()                           # all pieces are in the shared tensors
+                            opt_sd.update(m=[[t_.clone() for t_ in l] for l in opt_io["m_out"]],
+                                          v=[[t_.clone() for t_ in l] for l in opt_io["v_out"]])
                         if rank == 0:
                             from ..utils.checkpoint import save_checkpoint
                             save_checkpoint(f"{cfg.save_path}.step{(k + 1) * seeds_per_step}", full, step=(k + 1) * seeds_per_step,
-                                            args=cfg.to_dict(), seeds=seeds)
+                                            args=cfg.to_dict(), seeds=seeds, optimizer=opt_sd)
+                        if opt_io is not None:
+                            comm.barrier()                           # nobody overwrites the shared tensors while rank 0 reads them
             elif step is not trainer.step:
                 for x, dy in batches:
                     step(x, dy)

@@ -169,3 +169,23 @@ def test_adam_ddp_then_fsdp_equals_uninterrupted_ddp():
     for la, lb in zip(straight, resumed):
         for p, q in zip(la, lb):
             assert torch.allclose(p, q, atol=2e-5), (p - q).abs().max()
+
+
+@pytest.mark.timeout(600)
+def test_periodic_checkpoints_carry_the_optimizer(tmp_path):
+    """--save_every: the intermediate checkpoint holds Adam's moments too; resuming from it (under another strategy) lands on
+    the same weights as the uninterrupted run."""
+    from distributed_llm_code_samples_b200.utils.checkpoint import load_checkpoint
+    lp, seeds = _init()
+    cfg = _cfg(optimizer="adam")
+    cfg.lr = 1e-2
+    cfg.save_path, cfg.save_every = str(tmp_path / "ck"), 1
+    straight = api.train_ddp(lp, seeds, T, D, cfg)                       # 2 optimizer steps at world 2, checkpoint after each
+    ck = load_checkpoint(str(tmp_path / "ck.step2"))                     # after the first optimizer step (2 seeds consumed)
+    assert ck["step"] == 2 and ck["optimizer"]["kind"] == "adam" and ck["optimizer"]["t"] == 1
+    cfg2 = _cfg(optimizer="adam")
+    cfg2.lr = 1e-2
+    resumed = api.train_fsdp(ck["layers_params"], seeds[2:], T, D, cfg2, ck["optimizer"])
+    for la, lb in zip(straight, resumed):
+        for p, q in zip(la, lb):
+            assert torch.allclose(p, q, atol=2e-5), (p - q).abs().max()
