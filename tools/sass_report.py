@@ -27,10 +27,13 @@ PROOF = re.compile(r"^(UTCHMMA|UTCQMMA|UTMALDG|UTMASTG|UTMACCTL|LDTM|STTM|UTCBAR
 KEY = re.compile(r"UTCHMMA|UTMALDG|LDTM|UTCBAR|UTCATOMSWS|SYNCS|STRONG\.SYS|STRONG\.GPU|MEMBAR|FENCE|REDG|LDGMC|UCGABAR|NANOSLEEP|ERRBAR")
 FLAGSHIP = {
     "gemm_pair_relu_mask": ("gemm", "gemm_tcgen05_pair_kernelINS_8LocalEpiILi8E"),
-    "gemm_pair_fused_kernel": ("fused", "gemm_tcgen05_pair_kernelINS_9FusedEpiTILi4ELi0E"),
-    "gemm_1cta_fused_kernel": ("fused", "gemm_tcgen05_kernelINS_9FusedEpiTILi4ELi0E"),
+    "gemm_pair_fused_kernel": ("fused", "gemm_tcgen05_pair_kernelINS_9FusedEpiTILi4ELi32ELi0ELi0E"),
+    "gemm_1cta_fused_kernel": ("fused", "gemm_tcgen05_kernelINS_9FusedEpiTILi4ELi32ELi0ELi0E"),
+    "gemm_1cta_fused_nvls_kernel": ("fused", "gemm_tcgen05_kernelINS_9FusedEpiTILi4ELi32ELi0ELi1E"),
+    "gemm_pair_fused_adam_kernel": ("fused", "gemm_tcgen05_pair_kernelINS_9FusedEpiTILi4ELi32ELi1ELi0E"),
     "gemm_pair_gather_kernel": ("gather_gemm", "gemm_tcgen05_pair_kernelINS_9GatherEpiILi8E"),
-    "nvls_all_reduce_kernel": ("vmm", "nvls_all_reduce_bf16_kernel"),
+    "gemm_pair_f32_split_kernel": ("gemm_f32", "gemm_tcgen05_pair_kernelINS_6F32EpiILi1E"),
+    "nvls_all_reduce_kernel": ("vmm", "nvls_coll_kernelILi0ELb0E"),
 }
 
 
